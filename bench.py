@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""bench.py - DeepSpeech2 training hot path (fwd + bwd + CTC) on N B200s of one node.
+
+Contract: `python bench.py --gpus N --steps K --warmup W [--impl reference]`; for N>1 launched under
+torch.distributed.run, one rank per GPU.  Rank 0 prints ONE JSON line.
+
+workload  : the reference's dummy=1 training step (train.sh config: B=32/GPU, 7 bi-RNN layers, H=1760,
+            32 conv filters) on its longest bucket T=1500 frames (15 s utterances, 480 audio-s / GPU / step),
+            'stacked' wiring (the intended topology), bf16 tensor-core path.
+value     : audio-seconds trained per second, whole job, inputs resident in HBM.
+e2e       : same metric through the public API (deepSpeech_NCHW.inference/loss) with a fresh host batch
+            every step: pinned-host -> device copy of the features + device -> host read of the loss inside
+            the timed region.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from types import SimpleNamespace
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "audio_sec_per_sec_trained_fwd_bwd_ctc"
+UNIT = "audio-s/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=32, help="utterances per GPU (train.sh: 32)")
+    ap.add_argument("--frames", type=int, default=1500, help="input frames per utterance (dummy bucket)")
+    ap.add_argument("--hidden", type=int, default=1760)
+    ap.add_argument("--layers", type=int, default=7)
+    ap.add_argument("--cell", default="relu_clip", choices=["relu_clip", "gru"])
+    ap.add_argument("--fp32", action="store_true", help="fp32 CUDA-core path instead of bf16 tensor cores")
+    ap.add_argument("--no-extras", action="store_true", help="skip CTC sweep / kernel roofline / cpu baseline")
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------- clocks sampler
+class ClockSampler(object):
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([s.strip() for s in out.split(",")])
+            except Exception:
+                return
+            self._stop.wait(0.2)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=10)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        mhz = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(s) > 2 + i and s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": float(self.samples[0][1]) if self.samples[0][1].replace(".", "").isdigit() else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+# ----------------------------------------------------------------------------- FLOP model
+def step_flops(B, T, H, L, nf=32, cell="relu_clip"):
+    T1 = (T - 20) // 2 + 1
+    T2 = (T1 - 10) // 2 + 1
+    G = 3 if cell == "gru" else 1
+    conv = 2.0 * B * nf * T1 * 79 * 100 + 2.0 * B * nf * T2 * 75 * 1600
+    rnn = 0.0
+    for l in range(L):
+        I = 75 * nf if l == 0 else H
+        rnn += 2 * 2.0 * T2 * B * G * H * (I + H)
+    fc = 2.0 * T2 * B * H * 29
+    return 3.0 * (conv + rnn + fc), 3.0 * rnn, T2
+
+
+def reference_arm(args, rank):
+    """The reference's own TF-CPU path is unavailable (no tensorflow, py2 source): time the oracle's fp32
+    torch-CPU port of the same step on this box's host cores (kind 'port')."""
+    if rank != 0:
+        return
+    from oracle import ds2_cpu_baseline as cb
+    threads = os.cpu_count() or 1
+    # bounded sample: pick the dummy bucket so that (K+W) steps end within ~2.5 minutes
+    t0 = time.perf_counter()
+    cb.time_steps(args.batch, 0, 1, 0, threads, args.hidden, args.layers)
+    est100 = time.perf_counter() - t0
+    budget = 150.0 / max(1, args.steps + args.warmup)
+    bucket = 0
+    for b, T in ((1, 200), (3, 400), (7, 800), (14, 1500)):
+        if est100 * (T / 100.0) * 1.1 <= budget:
+            bucket = b
+    val, ms, loss = cb.time_steps(args.batch, bucket, args.steps, args.warmup, threads, args.hidden, args.layers)
+    frames = cb.O.UTT_LENGTHS[bucket]
+    sample = "dummy bucket T=%d frames x B=%d (%.0f audio-s per step), %d warm-up + %d timed steps, fp32 torch-CPU port" % (
+        frames, args.batch, args.batch * frames / 100.0, args.warmup, args.steps)
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "DS2 dummy-data training step (train.sh: B=%d, %d bi-RNN layers, H=%d, 32 filters), CPU sample: %s"
+                       % (args.batch, args.layers, args.hidden, sample)},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "reference TF-1.x CPU path unavailable on this box (no tensorflow; py2-only source): oracle port timed instead"}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        reference_arm(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    from deepspeech_b200 import _lib, deepSpeech_NCHW as ds, ops
+    from deepspeech_b200.deepSpeech_dummy import DummyData, utt_lengths
+    from deepspeech_b200.dp import GradAllReducer
+
+    B, T, H, L = args.batch, args.frames, args.hidden, args.layers
+    params = SimpleNamespace(use_fp16=not args.fp32, num_filters=32, batch_size=B, num_hidden=H, num_rnn_layers=L, engine="mkl",
+                             rnn_type="bi-dir", wiring="stacked", cell=args.cell, seed=1234)
+    model = ds.model(params)
+    reducer = GradAllReducer(model.parameters()) if world > 1 else None
+    bucket = utt_lengths.index(T) if T in utt_lengths else None
+    data = DummyData(B, seed=1234 + rank)
+    if bucket is None:                                       # non-bucket length (e.g. T2=1500 stress): reuse bucket-14 labels
+        raise SystemExit("--frames must be one of the dummy buckets %s" % utt_lengths)
+
+    pinned = [torch.empty((B, T, 161), dtype=torch.float32).pin_memory() for _ in range(2)]
+    feats_dev = torch.empty((B, T, 161), dtype=torch.float32, device=dev)
+
+    def host_batch(slot):
+        feats, idx, vals, shape, lens = data.inputs(bucket)
+        pinned[slot].copy_(torch.from_numpy(feats))
+        return (idx, vals, shape), lens
+
+    def train_step(sparse, lens):
+        model.zero_grad(set_to_none=True)
+        logits = ds.inference(None, feats_dev, lens, params)
+        loss = ds.loss(logits, sparse, lens)
+        loss.backward()
+        if reducer is not None:
+            reducer.finish()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---------------- resident-input timing (value)
+    sparse, lens = host_batch(0)
+    feats_dev.copy_(pinned[0], non_blocking=True)
+    for _ in range(max(args.warmup, 3)):
+        loss = train_step(sparse, lens)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = _lib.lib.ds2_launch_count()
+    with ClockSampler(local_rank) as clk:
+        barrier()
+        ev0.record()
+        for _ in range(args.steps):
+            loss = train_step(sparse, lens)
+        ev1.record()
+        barrier()
+    launches = _lib.lib.ds2_launch_count() - launches0
+    ms_step = max_over_ranks(ev0.elapsed_time(ev1) / args.steps)
+    final_loss = float(loss.item())
+    audio_s_step = world * B * T / 100.0
+    value = audio_s_step / (ms_step * 1e-3)
+
+    # ---------------- end-to-end timing (host batch -> H2D -> step -> loss D2H), double-buffered host prep
+    nxt = host_batch(0)
+    barrier()
+    t_e0, t_e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_e0.record()
+    wall0 = time.perf_counter()
+    for i in range(args.steps):
+        cur = nxt
+        feats_dev.copy_(pinned[i % 2], non_blocking=True)
+        loss = train_step(*cur)
+        if i + 1 < args.steps:
+            nxt = host_batch((i + 1) % 2)                   # overlaps with the GPU step
+        lv = loss.item()                                     # device -> host read of the result
+    t_e1.record()
+    barrier()
+    e2e_ms = max_over_ranks(max(t_e0.elapsed_time(t_e1), (time.perf_counter() - wall0) * 1e3) / args.steps)
+    e2e_value = audio_s_step / (e2e_ms * 1e-3)
+
+    total_flops, rnn_flops, T2 = step_flops(B, T, H, L, 32, args.cell)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_tf = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    peak_src = "measured (MEASURED_PEAKS.json, sustained)" if peaks else "fallback (B200_PROFILING.md)"
+    peak_hbm = float(peaks.get("hbm_gbs", 6650.0))
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32" if args.fp32 else "bf16", "data": "synthetic",
+        "config": {"workload": "DS2 dummy-data training step (fwd+bwd+CTC), train.sh config: B=%d/GPU, %d-layer bi-%s H=%d, 32 conv filters, "
+                               "bucket T=%d frames (T2=%d RNN steps), stacked wiring, no optimizer (metric is fwd+bwd+CTC)"
+                               % (B, L, "GRU" if args.cell == "gru" else "RNN(clipped ReLU)", H, T, T2),
+                   "global_batch": B * world, "frames": T, "parallelism": "dp%d" % world,
+                   "l2": "per-step working set (weights %.0f MB fp32 + activations > 1 GB) exceeds the 126 MB L2; no explicit flush"
+                         % (sum(p.numel() for p in model.parameters()) * 4 / 1e6)},
+        "clocks": clk.summary(),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(B * T * 161 * 4), "d2h_bytes_per_step": 4,
+                "ms_per_step": e2e_ms},
+        "gpu_launches": int(launches),
+        "loss": final_loss,
+        "step_tflops": total_flops / (ms_step * 1e-3) / 1e12 / 1.0,
+        "model_flops_per_step": total_flops,
+    }
+
+    if rank == 0 and not args.no_extras:
+        try:
+            line.update(extras(args, dev, model, ops, _lib, B, T2, H, L, peak_tf, peak_hbm, peak_src, ms_step))
+        except Exception as e:                                # never lose the headline line
+            line["extras_error"] = repr(e)[:300]
+    if world > 1:
+        dist.barrier()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def _time_kernel(fn, iters=10, warm=3):
+    import torch
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def extras(args, dev, model, ops, _lib, B, T2, H, L, peak_tf, peak_hbm, peak_src, ms_step):
+    """Kernel-level numbers next to the headline: recurrent-stack TFLOP/s, the dominant kernel's roofline
+    (measured live with CUDA events on the launching stream), the CTC sweep (config 2) and the CPU baseline."""
+    import torch
+    out = {}
+    x = torch.randn((T2, B, H), device=dev).to(torch.bfloat16 if not args.fp32 else torch.float32)
+    lens = torch.full((B,), T2, dtype=torch.int32, device=dev)
+    lyr = 1 if L > 1 else 0
+    W, U, Bv = model.rnn_W[lyr].detach(), model.rnn_U[lyr].detach(), model.rnn_B[lyr].detach()
+    I = W.shape[1]
+    if args.cell == "relu_clip" and I == H:
+        cdt = ops.rnn_path_dtype(B, H, 2, not args.fp32)
+        Wg, Ug = ops.cast(W, cdt), ops.cast(U, cdt)
+        xg = ops.cast(x, cdt)
+        # (1) batched input projection GEMM
+        ms_gemm = _time_kernel(lambda: ops.gemm_nt(xg.view(T2 * B, H), Wg))
+        gemm_flops = 2.0 * T2 * B * H * 2 * H
+        # (2) the recurrence (persistent kernel on the bf16 path)
+        wx = ops.gemm_nt(xg.view(T2 * B, H), Wg)
+        hs = torch.empty((2, T2, B, H), dtype=cdt, device=dev)
+        wsb = _lib.lib.ds2_rnn_workspace_bytes(T2, B, H, 2, ops._dt(hs))
+        ws = ops._workspace(wsb, dev, "rnn") if wsb else None
+
+        def rec():
+            ops.check(_lib.lib.ds2_rnn_relu_fwd(ops._p(wx), ops.SBN_SCALE, ops._p(Ug), ops._p(Bv), ops._p(lens), ops._p(hs), ops._dt(hs),
+                                                T2, B, H, 2, 2, 20.0, ops._p(ws), wsb, ops._stream()), "rnn_fwd")
+        ms_rec = _time_kernel(rec, iters=5, warm=2)
+        rec_flops = 2 * 2.0 * T2 * B * H * H
+        out["rnn_layer_fwd"] = {"gemm_ms": ms_gemm, "gemm_tflops": gemm_flops / ms_gemm / 1e9, "recurrence_ms": ms_rec,
+                                "recurrence_tflops": rec_flops / ms_rec / 1e9, "us_per_timestep": ms_rec * 1e3 / T2,
+                                "path": "persistent tcgen05 (bf16)" if cdt == torch.bfloat16 else "per-step CUDA-core kernels (fp32)"}
+        dom_gemm = ms_gemm >= ms_rec
+        ach = (gemm_flops / ms_gemm if dom_gemm else rec_flops / ms_rec) / 1e9
+        out["roofline"] = {"kernel": "gemm_tcgen05_kernel (W.x, M=%d N=%d K=%d)" % (T2 * B, 2 * H, H) if dom_gemm
+                           else "recurrent forward kernel (T=%d steps, B=%d, H=%d, 2 directions)" % (T2, B, H),
+                           "bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
+                           "traffic": None, "peak_source": peak_src}
+    total_flops, rnn_flops, _ = step_flops(B, args.frames, H, L, 32, args.cell)
+    out["rnn_tflops_in_step"] = {"note": "all RNN-stack GEMM FLOPs (fwd+bwd) / whole step time (lower bound)",
+                                 "value": rnn_flops / (ms_step * 1e-3) / 1e12}
+    # ---- config 2: standalone CTC sweep, B=64 (+ B=512 bandwidth-regime point)
+    sweep = []
+    for (Tc, Lc, Bc) in [(200, 50, 64), (400, 100, 64), (800, 200, 64), (1600, 400, 64), (400, 100, 512)]:
+        rng = np.random.default_rng(7)
+        xl = torch.tensor(rng.standard_normal((Tc, Bc, 29)), dtype=torch.float32, device=dev)
+        rngl = np.random.default_rng(11)
+        labs = []
+        for b in range(Bc):                                   # adjacent repeats collapsed, as the reference call does
+            r = rngl.integers(0, 28, size=Lc)
+            labs.append([int(v) for i, v in enumerate(r) if i == 0 or v != r[i - 1]])
+        Lm = max(len(r) for r in labs)
+        lab = np.zeros((Bc, Lm), np.int32)
+        for b, r in enumerate(labs):
+            lab[b, :len(r)] = r
+        ll = np.asarray([len(r) for r in labs], np.int32)
+        lab_d = torch.from_numpy(lab).to(dev)
+        ll_d = torch.from_numpy(ll).to(dev)
+        sl_d = torch.full((Bc,), Tc, dtype=torch.int32, device=dev)
+        loss = torch.empty(Bc, device=dev)
+        grad = torch.empty_like(xl)
+        wsb = _lib.lib.ds2_ctc_workspace_bytes(Tc, Bc, 29, Lm)
+        ws = ops._workspace(wsb, dev, "ctc")
+
+        def run():
+            ops.check(_lib.lib.ds2_ctc_loss_fwd_bwd(ops._p(xl), Tc, Bc, 29, ops._p(lab_d), Lm, ops._p(ll_d), ops._p(sl_d), None,
+                                                    ops._p(loss), ops._p(grad), ops._p(ws), wsb, ops._stream()), "ctc")
+        ms = _time_kernel(run, iters=10, warm=3)
+        byts = 2.0 * Tc * Bc * 29 * 4
+        sweep.append({"T": Tc, "L": Lc, "B": Bc, "ms": ms, "algorithmic_GBps": byts / ms / 1e6, "frac_of_hbm": byts / ms / 1e6 / peak_hbm,
+                      "ns_per_lattice_step": ms * 1e6 / Tc})
+    out["ctc_sweep"] = sweep
+    out["ctc_peak_source"] = peak_src.replace("sustained", "hbm copy")
+    # ---- CPU baseline on this box's host cores (bounded sample)
+    if args.gpus == 1:
+        from oracle import ds2_cpu_baseline as cb
+        threads = os.cpu_count() or 1
+        val, ms, _ = cb.time_steps(B, 0, 2, 1, threads, H, L)
+        out["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
+                               "sample": "dummy bucket T=100 frames x B=%d (%.0f audio-s/step), 1 warm-up + 2 timed steps, fp32 torch-CPU "
+                                         "port of the same step (reference TF path unavailable on this box)" % (B, B * 1.0),
+                               "ms_per_step": ms}
+    return out
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,97 @@
+// Error plumbing, device queries and the recurrent-layer dispatch of the C ABI.
+#include <stdarg.h>
+
+#include <atomic>
+
+#include "common.cuh"
+
+namespace ds2 {
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+  return DS2_ERR_CUDA;
+}
+int num_sms() {
+  static int n[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (!n[dev]) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    n[dev] = v;
+  }
+  return n[dev];
+}
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// implemented in ds2_rnn_generic.cu / ds2_rnn_persist.cu
+int rnn_relu_fwd_generic(const float* wx, float scale, const float* u, const float* bias, const int* lens, float* hs, int T,
+                         int B, int H, int ND, int reverse_mask, float cap, cudaStream_t st);
+int rnn_relu_bwd_generic(const float* dout, const float* u, const int* lens, const float* hs, float* dz, int T, int B, int H,
+                         int ND, int reverse_mask, float cap, cudaStream_t st);
+int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, int T, int B,
+                         int H, int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st);
+int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, const void* hs, void* dz, int T, int B, int H, int ND,
+                         int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st);
+size_t rnn_persist_workspace_bytes(int T, int B, int H, int ND);
+int rnn_persist_supported(int B, int H, int ND);
+
+}  // namespace ds2
+
+using namespace ds2;
+
+extern "C" const char* ds2_last_error(void) { return g_err; }
+extern "C" int ds2_version(void) { return 100; }
+extern "C" long long ds2_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+static int rnn_check(const void* a, const void* b, const void* c, const void* d, int T, int B, int H, int ND, int dtype) {
+  DS2_REQUIRE(a && b && c && d, DS2_ERR_BAD_ARG, "ds2_rnn: null pointer");
+  DS2_REQUIRE(T > 0 && B > 0 && H > 0 && (ND == 1 || ND == 2), DS2_ERR_BAD_SHAPE, "ds2_rnn: bad shape T=%d B=%d H=%d ND=%d", T, B, H, ND);
+  DS2_REQUIRE(dtype == DS2_F32 || dtype == DS2_BF16, DS2_ERR_BAD_ARG, "ds2_rnn: bad dtype %d", dtype);
+  return DS2_OK;
+}
+
+extern "C" int ds2_rnn_relu_fwd(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs,
+                                int dtype, int T, int B, int H, int ND, int reverse_mask, float cap, void* workspace,
+                                size_t workspace_bytes, void* stream) {
+  int rc = rnn_check(wx, u, bias, hs, T, B, H, ND, dtype);
+  if (rc) return rc;
+  DS2_REQUIRE(lens, DS2_ERR_BAD_ARG, "ds2_rnn_relu_fwd: lens is null");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == DS2_F32)
+    return rnn_relu_fwd_generic(wx, scale, static_cast<const float*>(u), bias, lens, static_cast<float*>(hs), T, B, H, ND,
+                                reverse_mask, cap, st);
+  DS2_REQUIRE(rnn_persist_supported(B, H, ND), DS2_ERR_UNSUPPORTED,
+              "ds2_rnn_relu_fwd: persistent bf16 kernel does not take B=%d H=%d ND=%d (use DS2_F32)", B, H, ND);
+  return rnn_relu_fwd_persist(wx, scale, u, bias, lens, hs, T, B, H, ND, reverse_mask, cap, workspace, workspace_bytes, st);
+}
+
+extern "C" int ds2_rnn_relu_bwd(const float* dout, const void* u, const int* lens, const void* hs, void* dz, int dtype, int T,
+                                int B, int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes,
+                                void* stream) {
+  int rc = rnn_check(dout, u, hs, dz, T, B, H, ND, dtype);
+  if (rc) return rc;
+  DS2_REQUIRE(lens, DS2_ERR_BAD_ARG, "ds2_rnn_relu_bwd: lens is null");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == DS2_F32)
+    return rnn_relu_bwd_generic(dout, static_cast<const float*>(u), lens, static_cast<const float*>(hs), static_cast<float*>(dz),
+                                T, B, H, ND, reverse_mask, cap, st);
+  DS2_REQUIRE(rnn_persist_supported(B, H, ND), DS2_ERR_UNSUPPORTED,
+              "ds2_rnn_relu_bwd: persistent bf16 kernel does not take B=%d H=%d ND=%d (use DS2_F32)", B, H, ND);
+  return rnn_relu_bwd_persist(dout, u, lens, hs, dz, T, B, H, ND, reverse_mask, cap, workspace, workspace_bytes, st);
+}
+
+extern "C" size_t ds2_rnn_workspace_bytes(int T, int B, int H, int ND, int dtype) {
+  if (dtype != DS2_BF16) return 0;
+  return rnn_persist_workspace_bytes(T, B, H, ND);
+}
+extern "C" int ds2_rnn_relu_persistent_supported(int B, int H, int ND) { return rnn_persist_supported(B, H, ND); }

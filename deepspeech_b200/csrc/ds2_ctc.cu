@@ -1,0 +1,366 @@
+// CTC loss + gradient w.r.t. unnormalised logits, fused with the softmax.
+// Replaces tf.nn.ctc_loss as called at src/deepSpeech_NCHW.py:225 / src/deepSpeech.py:227
+// (blank = K-1, time-major fp32 logits, labels already collapsed by the host shim).
+//
+// Kernel 1 (ctc_chain_kernel): grid (B, 2).  blockIdx.y==0 runs the alpha recursion forward in
+// time, blockIdx.y==1 runs the beta recursion backward in time, concurrently on different SMs,
+// one thread per lattice state, log-space fp32, re-normalised every RENORM steps so stored
+// magnitudes stay small (offsets kept in fp64).  Tables go to a caller-provided scratch.
+// Kernel 2 (ctc_grad_kernel): fully parallel over (t, b): one warp per logits row computes the
+// softmax and subtracts the per-class occupancy sum_s exp(alpha+beta-logp).
+#include "common.cuh"
+
+namespace ds2 {
+
+static constexpr float NEGF = -1e30f;
+static constexpr int RENORM = 16;
+
+struct CtcWs {
+  float* alpha;     // [B][T][Sp]
+  float* beta;      // [B][T][Sp]
+  double* coff;     // [B][2][NB]   cumulative renorm offsets (alpha, beta) per time block
+  double* logp;     // [B]
+  int* perm;        // [B][Lmax]    label positions sorted by class
+  int* cls_off;     // [B][K+1]
+  int Sp, NB;
+};
+
+__host__ __device__ inline size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
+
+static size_t ctc_ws_layout(int T, int B, int K, int Lmax, char* base, CtcWs* ws) {
+  int Sp = (2 * Lmax + 1 + 3) & ~3;
+  int NB = (T + RENORM - 1) / RENORM + 1;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off += align256(bytes); return o; };
+  size_t o_alpha = take(sizeof(float) * (size_t)B * T * Sp);
+  size_t o_beta = take(sizeof(float) * (size_t)B * T * Sp);
+  size_t o_coff = take(sizeof(double) * (size_t)B * 2 * NB);
+  size_t o_logp = take(sizeof(double) * (size_t)B);
+  size_t o_perm = take(sizeof(int) * (size_t)B * (Lmax > 0 ? Lmax : 1));
+  size_t o_cls = take(sizeof(int) * (size_t)B * (K + 1));
+  if (ws) {
+    ws->alpha = reinterpret_cast<float*>(base + o_alpha);
+    ws->beta = reinterpret_cast<float*>(base + o_beta);
+    ws->coff = reinterpret_cast<double*>(base + o_coff);
+    ws->logp = reinterpret_cast<double*>(base + o_logp);
+    ws->perm = reinterpret_cast<int*>(base + o_perm);
+    ws->cls_off = reinterpret_cast<int*>(base + o_cls);
+    ws->Sp = Sp;
+    ws->NB = NB;
+  }
+  return off;
+}
+
+__device__ __forceinline__ float lse3(float a, float b, float c) {
+  float m = fmaxf(a, fmaxf(b, c));
+  return m + __logf(__expf(a - m) + __expf(b - m) + __expf(c - m));
+}
+
+// dynamic smem: float buf[2][Smax+2] | float lse[T] | int lab[Lmax] | float red[32]
+static constexpr int CTC_NSMAX = 4;   // lattice states per thread (S <= 4096)
+static constexpr int CTC_PF = 4;      // emission prefetch distance (time steps)
+
+template <int DIR>
+__device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K, const int* __restrict__ labels, int Lmax,
+                          const int* __restrict__ label_lens, const int* __restrict__ seq_lens, float* __restrict__ loss,
+                          CtcWs ws, float* smem) {
+  const int b = blockIdx.x;
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int lane = tid & 31, warp = tid >> 5, nwarps = nthr >> 5;
+  const int Tb = min(seq_lens[b], T);
+  const int L = label_lens[b];
+  const int S = 2 * L + 1;
+  const int blank = K - 1;
+  const int Smax = 2 * Lmax + 1;
+  float* buf0 = smem;                       // [Smax+2], entries 0,1 are NEG padding
+  float* buf1 = buf0 + (Smax + 2);
+  float* lse = buf1 + (Smax + 2);           // [T]
+  int* lab = reinterpret_cast<int*>(lse + T);   // [Lmax]  (reversed for DIR==1)
+  float* red = reinterpret_cast<float*>(lab + (Lmax > 0 ? Lmax : 1));   // [32]
+  float* tab = (DIR == 0 ? ws.alpha : ws.beta) + (size_t)b * T * ws.Sp;
+  double* coff = ws.coff + ((size_t)b * 2 + DIR) * ws.NB;
+
+  for (int i = tid; i < L; i += nthr) lab[i] = labels[(size_t)b * Lmax + (DIR == 0 ? i : L - 1 - i)];
+  // row log-sum-exp, one warp per row
+  for (int t = warp; t < Tb; t += nwarps) {
+    const float* row = logits + ((size_t)t * B + b) * K;
+    float m = -INFINITY;
+    for (int k = lane; k < K; k += 32) m = fmaxf(m, row[k]);
+    m = warp_max(m);
+    float s = 0.f;
+    for (int k = lane; k < K; k += 32) s += __expf(row[k] - m);
+    s = warp_sum(s);
+    if (lane == 0) lse[t] = m + __logf(s);
+  }
+  if (tid < 2) { buf0[tid] = NEGF; buf1[tid] = NEGF; }
+  __syncthreads();
+  if (DIR == 0 && warp == 0) {
+    // class-sorted (stable) permutation of label positions for the gradient kernel:
+    // lane k owns class k (chunks of 32 classes), counting pass + warp scan + fill pass.
+    int* cls = ws.cls_off + (size_t)b * (K + 1);
+    int* perm = ws.perm + (size_t)b * Lmax;
+    int base = 0;
+    for (int k0 = 0; k0 < K; k0 += 32) {
+      const int k = k0 + lane;
+      int cnt = 0;
+      for (int i = 0; i < L; ++i) cnt += (lab[i] == k);
+      int incl = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      int c = base + incl - cnt;
+      if (k < K) cls[k] = c;
+      for (int i = 0; i < L; ++i)
+        if (lab[i] == k) perm[c++] = i;
+      base += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (lane == 0) cls[K] = base;
+  }
+  if (Tb <= 0) {
+    if (DIR == 0 && tid == 0) { ws.logp[b] = 0.0; loss[b] = 0.f; }
+    return;
+  }
+
+  // Per-thread lattice states s = tid + j*nthr: class and skip-transition flag are loop-invariant.
+  int cls_j[CTC_NSMAX];
+  bool skip_j[CTC_NSMAX], on_j[CTC_NSMAX];
+#pragma unroll
+  for (int j = 0; j < CTC_NSMAX; ++j) {
+    const int s = tid + j * nthr;
+    on_j[j] = s < S;
+    cls_j[j] = (on_j[j] && (s & 1)) ? lab[s >> 1] : blank;
+    skip_j[j] = on_j[j] && (s & 1) && s >= 2 && lab[s >> 1] != lab[(s >> 1) - 1];
+  }
+  // emission prefetch ring (raw logits; the row lse is subtracted at use)
+  float xq[CTC_PF][CTC_NSMAX];
+#pragma unroll
+  for (int u = 0; u < CTC_PF; ++u) {
+    const int step = u;
+    const int t = (DIR == 0) ? step : (Tb - 1 - step);
+#pragma unroll
+    for (int j = 0; j < CTC_NSMAX; ++j)
+      xq[u][j] = (step < Tb && on_j[j]) ? __ldg(logits + ((size_t)t * B + b) * K + cls_j[j]) : 0.f;
+  }
+  double cum = 0.0;                          // cumulative renorm offset (uniform across threads)
+  float* prev = buf0;
+  float* cur = buf1;
+  for (int base = 0; base < Tb; base += CTC_PF) {
+#pragma unroll
+    for (int u = 0; u < CTC_PF; ++u) {
+      const int step = base + u;
+      if (step >= Tb) break;
+      const int t = (DIR == 0) ? step : (Tb - 1 - step);
+      const float l = lse[t];
+#pragma unroll
+      for (int j = 0; j < CTC_NSMAX; ++j) {
+        if (on_j[j]) {
+          const int s = tid + j * nthr;
+          const float ly = xq[u][j] - l;
+          float v;
+          if (step == 0) {
+            v = (s < 2) ? 0.f : NEGF;
+          } else {
+            const float a2 = skip_j[j] ? prev[s] : NEGF;
+            v = lse3(prev[s + 2], prev[s + 1], a2);
+          }
+          // alpha stores the value with the emission, beta stores it without; the running
+          // quantity carried to the next step always includes the emission.
+          const float carried = fmaxf(v + ly, NEGF);
+          cur[s + 2] = carried;
+          const int sidx = (DIR == 0) ? s : (S - 1 - s);
+          tab[(size_t)t * ws.Sp + sidx] = (DIR == 0) ? carried : fmaxf(v, NEGF);
+        }
+      }
+      // refill this ring slot with the emission of step + CTC_PF
+      {
+        const int nstep = step + CTC_PF;
+        const int nt = (DIR == 0) ? nstep : (Tb - 1 - nstep);
+#pragma unroll
+        for (int j = 0; j < CTC_NSMAX; ++j)
+          if (nstep < Tb && on_j[j]) xq[u][j] = __ldg(logits + ((size_t)nt * B + b) * K + cls_j[j]);
+      }
+      __syncthreads();
+      if ((step % RENORM) == RENORM - 1 || step == Tb - 1) {
+        // block max of the carried values -> subtract, accumulate offset in fp64
+        float m = NEGF;
+#pragma unroll
+        for (int j = 0; j < CTC_NSMAX; ++j)
+          if (on_j[j]) m = fmaxf(m, cur[tid + j * nthr + 2]);
+        m = warp_max(m);
+        if (lane == 0) red[warp] = m;
+        __syncthreads();
+        float mm = red[0];
+        for (int w = 1; w < nwarps; ++w) mm = fmaxf(mm, red[w]);
+        if (step == Tb - 1) {
+          if (DIR == 0 && tid == 0) {
+            // log p = logsumexp(alpha_{T-1}(S-1), alpha_{T-1}(S-2)) + offsets
+            const float aL = cur[S - 1 + 2];
+            const float aL1 = (S > 1) ? cur[S - 2 + 2] : NEGF;
+            const float mx = fmaxf(aL, aL1);
+            const double lp = (double)mx + log((double)__expf(aL - mx) + (double)__expf(aL1 - mx)) + cum;
+            ws.logp[b] = lp;
+            loss[b] = (float)(-lp);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < CTC_NSMAX; ++j)
+            if (on_j[j]) cur[tid + j * nthr + 2] = fmaxf(cur[tid + j * nthr + 2] - mm, NEGF);
+          cum += (double)mm;
+          __syncthreads();
+        }
+      }
+      // offset that applies to the rows written from the NEXT step on
+      if (tid == 0 && ((step + 1) % RENORM) == 0) coff[(step + 1) / RENORM] = cum;
+      float* tmp = prev; prev = cur; cur = tmp;
+    }
+  }
+  if (tid == 0) coff[0] = 0.0;
+}
+
+__global__ void __launch_bounds__(1024, 1)
+ctc_chain_kernel(const float* __restrict__ logits, int T, int B, int K, const int* __restrict__ labels, int Lmax,
+                 const int* __restrict__ label_lens, const int* __restrict__ seq_lens, float* __restrict__ loss, CtcWs ws) {
+  extern __shared__ __align__(16) float ctc_smem[];
+  if (blockIdx.y == 0)
+    ctc_chain<0>(logits, T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws, ctc_smem);
+  else
+    ctc_chain<1>(logits, T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws, ctc_smem);
+}
+
+// One warp per (t,b) row.  dynamic smem per warp: float e[Sp]
+__global__ void __launch_bounds__(256)
+ctc_grad_kernel(const float* __restrict__ logits, int T, int B, int K, const int* __restrict__ labels, int Lmax,
+                const int* __restrict__ label_lens, const int* __restrict__ seq_lens, const float* __restrict__ dloss,
+                float* __restrict__ grad, CtcWs ws, int rows_per_warp) {
+  extern __shared__ __align__(16) float gsm[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int b = blockIdx.y;
+  float* e = gsm + (size_t)warp * ws.Sp;
+  const int Tb = min(seq_lens[b], T);
+  const int L = label_lens[b];
+  const int S = 2 * L + 1;
+  const int blank = K - 1;
+  const double logp = ws.logp[b];
+  const float up = dloss ? dloss[b] : 1.f;
+  const int* perm = ws.perm + (size_t)b * Lmax;
+  const int* cls = ws.cls_off + (size_t)b * (K + 1);
+  const int t0 = (blockIdx.x * nwarps + warp) * rows_per_warp;
+  for (int t = t0; t < min(t0 + rows_per_warp, T); ++t) {
+    float* g = grad + ((size_t)t * B + b) * K;
+    if (t >= Tb) {
+      for (int k = lane; k < K; k += 32) g[k] = 0.f;
+      continue;
+    }
+    // alpha rows written at step=t carry offset coff_a[t/RENORM]; beta rows written at
+    // step=Tb-1-t carry coff_b[(Tb-1-t)/RENORM].
+    const double ca = ws.coff[((size_t)b * 2 + 0) * ws.NB + t / RENORM];
+    const double cb = ws.coff[((size_t)b * 2 + 1) * ws.NB + (Tb - 1 - t) / RENORM];
+    const float c = (float)(ca + cb - logp);
+    const float* ar = ws.alpha + ((size_t)b * T + t) * ws.Sp;
+    const float* br = ws.beta + ((size_t)b * T + t) * ws.Sp;
+    float blank_sum = 0.f;
+    for (int s = lane; s < S; s += 32) {
+      const float v = __expf(fminf(ar[s] + br[s] + c, 0.f + 1e-3f));
+      e[s] = v;
+      if (!(s & 1)) blank_sum += v;
+    }
+    blank_sum = warp_sum(blank_sum);
+    __syncwarp();
+    const float* row = logits + ((size_t)t * B + b) * K;
+    float m = -INFINITY;
+    for (int k = lane; k < K; k += 32) m = fmaxf(m, row[k]);
+    m = warp_max(m);
+    float den = 0.f;
+    for (int k = lane; k < K; k += 32) den += __expf(row[k] - m);
+    den = warp_sum(den);
+    const float inv = 1.f / den;
+    for (int k = lane; k < K; k += 32) {
+      float occ;
+      if (k == blank) {
+        occ = blank_sum;
+      } else {
+        occ = 0.f;
+        for (int i = cls[k]; i < cls[k + 1]; ++i) occ += e[2 * perm[i] + 1];
+      }
+      g[k] = (__expf(row[k] - m) * inv - occ) * up;
+    }
+    __syncwarp();
+  }
+}
+
+__global__ void __launch_bounds__(256)
+ctc_scale_grad_kernel(const float* __restrict__ grad, const float* __restrict__ dloss, float* __restrict__ out, long n, int B, int K) {
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+    out[i] = grad[i] * dloss[(i / K) % B];
+}
+
+}  // namespace ds2
+
+using namespace ds2;
+
+extern "C" int ds2_ctc_scale_grad(const float* grad, const float* dloss, float* out, int T, int B, int K, void* stream) {
+  DS2_REQUIRE(grad && dloss && out && T > 0 && B > 0 && K > 0, DS2_ERR_BAD_ARG, "ds2_ctc_scale_grad: bad argument");
+  const long n = (long)T * B * K;
+  long g = (n + 255) / 256;
+  if (g > (long)num_sms() * 16) g = (long)num_sms() * 16;
+  ctc_scale_grad_kernel<<<(int)g, 256, 0, static_cast<cudaStream_t>(stream)>>>(grad, dloss, out, n, B, K);
+  DS2_LAUNCH_CHECK("ctc_scale_grad_kernel");
+  count_launch();
+  return DS2_OK;
+}
+
+extern "C" size_t ds2_ctc_workspace_bytes(int T, int B, int K, int Lmax) {
+  if (T <= 0 || B <= 0 || K <= 1 || Lmax < 0) return 0;
+  return ctc_ws_layout(T, B, K, Lmax, nullptr, nullptr);
+}
+
+namespace ds2 {
+int ctc_launch(const float* logits, int T, int B, int K, const int* labels, int Lmax, const int* label_lens,
+               const int* seq_lens, const float* dloss, float* loss, float* grad, void* workspace, size_t workspace_bytes,
+               cudaStream_t st) {
+  DS2_REQUIRE(logits && labels && label_lens && seq_lens && loss, DS2_ERR_BAD_ARG, "ds2_ctc: null pointer argument");
+  DS2_REQUIRE(T > 0 && B > 0 && K > 1 && Lmax >= 0, DS2_ERR_BAD_SHAPE, "ds2_ctc: bad shape T=%d B=%d K=%d Lmax=%d", T, B, K, Lmax);
+  CtcWs ws;
+  size_t need = ctc_ws_layout(T, B, K, Lmax, reinterpret_cast<char*>(workspace), &ws);
+  DS2_REQUIRE(workspace && workspace_bytes >= need, DS2_ERR_WORKSPACE, "ds2_ctc: workspace too small (%zu < %zu bytes)",
+              workspace_bytes, need);
+  DS2_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, DS2_ERR_BAD_ARG, "ds2_ctc: workspace must be 256-byte aligned");
+  const int Smax = 2 * Lmax + 1;
+  int threads = ((Smax + 31) / 32) * 32;
+  if (threads < 64) threads = 64;
+  if (threads > 1024) threads = 1024;
+  size_t smem = sizeof(float) * (2 * (size_t)(Smax + 2) + T + 32) + sizeof(int) * (size_t)(Lmax > 0 ? Lmax : 1);
+  DS2_REQUIRE(Smax <= 1024 * CTC_NSMAX, DS2_ERR_BAD_SHAPE, "ds2_ctc: Lmax=%d exceeds the supported label length %d", Lmax, (1024 * CTC_NSMAX - 1) / 2);
+  DS2_REQUIRE(smem <= 200 * 1024, DS2_ERR_BAD_SHAPE, "ds2_ctc: T=%d / Lmax=%d need %zu bytes of shared memory (> 200 KB)", T, Lmax, smem);
+  static bool attr_done = false;
+  if (!attr_done) {
+    DS2_CUDA(cudaFuncSetAttribute(ctc_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    DS2_CUDA(cudaFuncSetAttribute(ctc_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    attr_done = true;
+  }
+  ctc_chain_kernel<<<dim3(B, 2), threads, smem, st>>>(logits, T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws);
+  DS2_LAUNCH_CHECK("ctc_chain_kernel");
+  count_launch();
+  if (grad) {
+    const int warps = 8;
+    const int rows_per_warp = 1;
+    size_t gsmem = sizeof(float) * (size_t)warps * ws.Sp;
+    DS2_REQUIRE(gsmem <= 64 * 1024, DS2_ERR_BAD_SHAPE, "ds2_ctc: Lmax=%d too large for the gradient kernel", Lmax);
+    dim3 grid((T + warps * rows_per_warp - 1) / (warps * rows_per_warp), B);
+    ctc_grad_kernel<<<grid, warps * 32, gsmem, st>>>(logits, T, B, K, labels, Lmax, label_lens, seq_lens, dloss, grad, ws,
+                                                     rows_per_warp);
+    DS2_LAUNCH_CHECK("ctc_grad_kernel");
+    count_launch();
+  }
+  return DS2_OK;
+}
+}  // namespace ds2
+
+extern "C" int ds2_ctc_loss_fwd_bwd(const float* logits, int T, int B, int K, const int* labels, int Lmax,
+                                    const int* label_lens, const int* seq_lens, const float* dloss, float* loss, float* grad,
+                                    void* workspace, size_t workspace_bytes, void* stream) {
+  return ctc_launch(logits, T, B, K, labels, Lmax, label_lens, seq_lens, dloss, loss, grad, workspace, workspace_bytes,
+                    static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,281 @@
+// bf16 x bf16 -> fp32 GEMM on the 5th-gen tensor cores: TMA (128B swizzle) -> smem ring ->
+// tcgen05.mma (one elected thread) -> TMEM accumulators (double buffered) -> tcgen05.ld epilogue.
+// Persistent: one CTA per SM loops over 128x128 output tiles.
+//
+//   C[M,N] = alpha * A * B^T (+ bias[n]) (+ beta * C)
+//   A: K-major  [M,K] row-major (a_mn=0)  or MN-major [K,M] row-major (a_mn=1)
+//   B: K-major  [N,K] row-major (b_mn=0)  or MN-major [K,N] row-major (b_mn=1)
+//
+// Used for: the batched input projection W.x of every recurrent layer (src/custom_ops.py:60-61
+// executed for all timesteps at once), the FC layer (src/deepSpeech_NCHW.py:195-198), conv2 as an
+// (explicit-im2col) GEMM, and all batched backward GEMMs (dW, dU, dx).
+#include <stdarg.h>
+
+#include <mutex>
+
+#include "common.cuh"
+
+namespace ds2 {
+
+static constexpr int BM = 128, BN = 128, BK = 64;
+static constexpr int STAGES = 6, ACC_STAGES = 2;
+static constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
+static constexpr int GEMM_THREADS = 256;
+static constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+
+struct GemmParams {
+  void* C;
+  long ldc;
+  int M, N, K;
+  float alpha, beta;
+  const float* bias;
+  int c_bf16, a_mn, b_mn;
+  int num_m_blocks, num_n_blocks;
+};
+
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, GemmParams p) {
+  extern __shared__ uint8_t gemm_smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(gemm_smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* full_bar = bars;                         // [STAGES]
+  uint64_t* empty_bar = bars + STAGES;               // [STAGES]
+  uint64_t* tfull_bar = bars + 2 * STAGES;           // [ACC_STAGES]
+  uint64_t* tempty_bar = bars + 2 * STAGES + ACC_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 2 * ACC_STAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+  const int num_kb = (p.K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(full_bar + i, 1); mbar_init(empty_bar + i, 1); }
+    for (int i = 0; i < ACC_STAGES; ++i) { mbar_init(tfull_bar + i, 1); mbar_init(tempty_bar + i, 4); }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, ACC_STAGES * BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile % p.num_m_blocks) * BM, n0 = (tile / p.num_m_blocks) * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(empty_bar + stage, phase ^ 1, 100 + stage);
+          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          mbar_arrive_expect_tx(full_bar + stage, STAGE_BYTES);
+          const int k0 = kb * BK;
+          if (!p.a_mn) {
+            tma_load_2d(sa, &tmap_a, full_bar + stage, k0, m0);
+          } else {
+            tma_load_2d(sa, &tmap_a, full_bar + stage, m0, k0);
+            tma_load_2d(sa + A_BYTES / 2, &tmap_a, full_bar + stage, m0 + 64, k0);
+          }
+          if (!p.b_mn) {
+            tma_load_2d(sb, &tmap_b, full_bar + stage, k0, n0);
+          } else {
+            tma_load_2d(sb, &tmap_b, full_bar + stage, n0, k0);
+            tma_load_2d(sb + B_BYTES / 2, &tmap_b, full_bar + stage, n0 + 64, k0);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc = umma_idesc_bf16(BM, BN, p.a_mn, p.b_mn);
+    int stage = 0; uint32_t phase = 0;
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      mbar_wait(tempty_bar + acc, acc_phase ^ 1, 200 + acc);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * BN;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(full_bar + stage, phase, 300 + stage);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            // K-major: +32 B per K=16 inside the 128B swizzle atom, SBO = 8 rows * 128 B.
+            // MN-major: +16 k-rows * 128 B per K=16, LBO = 64-element MN group stride, SBO = 8 k-rows.
+            const uint64_t adesc = p.a_mn ? umma_smem_desc_sw128(sa + k * 2048, A_BYTES / 2, 1024)
+                                          : umma_smem_desc_sw128(sa + k * 32, 16, 1024);
+            const uint64_t bdesc = p.b_mn ? umma_smem_desc_sw128(sb + k * 2048, B_BYTES / 2, 1024)
+                                          : umma_smem_desc_sw128(sb + k * 32, 16, 1024);
+            umma_bf16(d_tmem, adesc, bdesc, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty_bar + stage);                 // frees the smem slot when the MMAs retire
+          if (kb == num_kb - 1) umma_commit(tfull_bar + acc);   // accumulator ready for the epilogue
+        }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1; }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue (TMEM -> registers -> global) =====================
+    const int wq = warp & 3;      // TMEM lane quarter this warp may access
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m0 = (tile % p.num_m_blocks) * BM, n0 = (tile / p.num_m_blocks) * BN;
+      mbar_wait(tfull_bar + acc, acc_phase, 400 + acc);
+      tc_fence_after();
+      const int row = m0 + wq * 32 + lane;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + acc * BN + c * 32 + (static_cast<uint32_t>(wq * 32) << 16), r);
+        tmem_ld_wait();
+        const int nbase = n0 + c * 32;
+        if (row < p.M && nbase < p.N) {
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = p.alpha * __uint_as_float(r[j]);
+          if (p.bias) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (nbase + j < p.N) v[j] += __ldg(p.bias + nbase + j);
+          }
+          const bool full = nbase + 32 <= p.N;
+          if (p.c_bf16) {
+            __nv_bfloat16* crow = static_cast<__nv_bfloat16*>(p.C) + (long)row * p.ldc + nbase;
+            if (p.beta != 0.f) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (nbase + j < p.N) v[j] += p.beta * __bfloat162float(crow[j]);
+            }
+            if (full && ((reinterpret_cast<uintptr_t>(crow) & 15) == 0)) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                uint4 pk;
+                __nv_bfloat162 b0 = __floats2bfloat162_rn(v[j], v[j + 1]), b1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
+                __nv_bfloat162 b2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]), b3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
+                pk.x = *reinterpret_cast<uint32_t*>(&b0); pk.y = *reinterpret_cast<uint32_t*>(&b1);
+                pk.z = *reinterpret_cast<uint32_t*>(&b2); pk.w = *reinterpret_cast<uint32_t*>(&b3);
+                *reinterpret_cast<uint4*>(crow + j) = pk;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (nbase + j < p.N) crow[j] = __float2bfloat16(v[j]);
+            }
+          } else {
+            float* crow = static_cast<float*>(p.C) + (long)row * p.ldc + nbase;
+            if (p.beta != 0.f) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (nbase + j < p.N) v[j] += p.beta * crow[j];
+            }
+            if (full && ((reinterpret_cast<uintptr_t>(crow) & 15) == 0)) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(crow + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (nbase + j < p.N) crow[j] = v[j];
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar + acc);
+      if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, ACC_STAGES * BN);
+  }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  });
+  return fn;
+}
+
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t stride_outer_elems,
+                      uint32_t box_inner, uint32_t box_outer) {
+  PFN_encodeTiled enc = get_encode_fn();
+  DS2_REQUIRE(enc != nullptr, DS2_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available from the driver");
+  DS2_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, DS2_ERR_BAD_ARG, "TMA operand base must be 16-byte aligned");
+  DS2_REQUIRE((stride_outer_elems * 2) % 16 == 0, DS2_ERR_BAD_SHAPE, "TMA operand row pitch (%llu elements) must be a multiple of 8",
+              (unsigned long long)stride_outer_elems);
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {stride_outer_elems * 2};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DS2_REQUIRE(r == CUDA_SUCCESS, DS2_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%llu outer=%llu pitch=%llu)",
+              (int)r, (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)stride_outer_elems);
+  return DS2_OK;
+}
+
+int gemm_bf16_launch(const void* A, long lda, int a_mn, const void* B, long ldb, int b_mn, void* C, int c_dtype, long ldc,
+                     int M, int N, int K, float alpha, float beta, const float* bias, cudaStream_t st) {
+  DS2_REQUIRE(A && B && C, DS2_ERR_BAD_ARG, "ds2_gemm_bf16: null pointer");
+  DS2_REQUIRE(M > 0 && N > 0 && K > 0, DS2_ERR_BAD_SHAPE, "ds2_gemm_bf16: bad shape M=%d N=%d K=%d", M, N, K);
+  DS2_REQUIRE(c_dtype == DS2_F32 || c_dtype == DS2_BF16, DS2_ERR_BAD_ARG, "ds2_gemm_bf16: bad c_dtype %d", c_dtype);
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn) rc = make_tmap_2d_bf16(&ta, A, K, M, lda, BK, BM);
+  else rc = make_tmap_2d_bf16(&ta, A, M, K, lda, 64, BK);
+  if (rc) return rc;
+  if (!b_mn) rc = make_tmap_2d_bf16(&tb, B, K, N, ldb, BK, BN);
+  else rc = make_tmap_2d_bf16(&tb, B, N, K, ldb, 64, BK);
+  if (rc) return rc;
+  static bool attr_done = false;
+  if (!attr_done) {
+    DS2_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
+    attr_done = true;
+  }
+  GemmParams p;
+  p.C = C; p.ldc = ldc; p.M = M; p.N = N; p.K = K; p.alpha = alpha; p.beta = beta; p.bias = bias;
+  p.c_bf16 = (c_dtype == DS2_BF16); p.a_mn = a_mn; p.b_mn = b_mn;
+  p.num_m_blocks = (M + BM - 1) / BM;
+  p.num_n_blocks = (N + BN - 1) / BN;
+  const int tiles = p.num_m_blocks * p.num_n_blocks;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  gemm_tcgen05_kernel<<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(ta, tb, p);
+  DS2_LAUNCH_CHECK("gemm_tcgen05_kernel");
+  count_launch();
+  return DS2_OK;
+}
+
+}  // namespace ds2
+
+extern "C" int ds2_gemm_bf16(const void* A, long lda, int a_mn_major, const void* B, long ldb, int b_mn_major, void* C,
+                             int c_dtype, long ldc, int M, int N, int K, float alpha, float beta, const float* bias,
+                             void* stream) {
+  return ds2::gemm_bf16_launch(A, lda, a_mn_major, B, ldb, b_mn_major, C, c_dtype, ldc, M, N, K, alpha, beta, bias,
+                               static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,100 @@
+"""Data-parallel plumbing: one process per GPU, batch sharded by utterance, gradients averaged with
+bucketed asynchronous all-reduce launched from inside backward so that it overlaps with the backward of
+earlier layers.  This is the NCCL form of the reference's (dead) in-graph tower averaging
+`average_gradients` (src/deepSpeech_train.py:193-228; call site commented out at :453).
+
+torch.distributed is the transport (NCCL over NVLink/NVSwitch on GPUs, gloo on CPU for tests)."""
+from __future__ import annotations
+
+from typing import Iterable, List
+
+import torch
+import torch.distributed as dist
+
+
+def shard_batch(n_items: int, rank: int, world: int) -> slice:
+    """Equal contiguous shards of the global batch (utterances are independent).  The global
+    batch must divide evenly so that the mean of per-rank mean losses equals the global mean
+    (src/deepSpeech_NCHW.py:226)."""
+    if n_items % world:
+        raise ValueError("global batch %d is not divisible by world size %d" % (n_items, world))
+    per = n_items // world
+    return slice(rank * per, (rank + 1) * per)
+
+
+class GradAllReducer(object):
+    """Registers post-accumulate hooks on `params`; each gradient is all-reduced (sum) asynchronously as
+    soon as autograd has produced it - backward visits layers last-to-first, so layer l's reduction runs
+    while layers < l are still back-propagating.  Small tensors are packed into buckets of
+    `bucket_bytes` to amortise launch latency.  `finish()` waits for all reductions and applies 1/world."""
+
+    def __init__(self, params: Iterable[torch.nn.Parameter], group=None, bucket_bytes: int = 32 << 20):
+        self.params: List[torch.nn.Parameter] = [p for p in params if p.requires_grad]
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.bucket_bytes = bucket_bytes
+        self._pending = []          # (work handle, flat buffer or None, [params])
+        self._bucket: List[torch.nn.Parameter] = []
+        self._bucket_size = 0
+        self._seen = 0
+        self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
+        self.launched = 0
+
+    def _flush(self):
+        if not self._bucket:
+            return
+        ps, self._bucket, self._bucket_size = self._bucket, [], 0
+        if len(ps) == 1:
+            w = dist.all_reduce(ps[0].grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            self._pending.append((w, None, ps))
+        else:
+            flat = torch.cat([p.grad.reshape(-1) for p in ps])
+            w = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            self._pending.append((w, flat, ps))
+        self.launched += 1
+
+    def _on_grad(self, p):
+        if self.world == 1:
+            return
+        self._seen += 1
+        nbytes = p.grad.numel() * p.grad.element_size()
+        if nbytes >= self.bucket_bytes:
+            self._flush()
+            self._bucket = [p]
+            self._flush()
+        else:
+            self._bucket.append(p)
+            self._bucket_size += nbytes
+            if self._bucket_size >= self.bucket_bytes:
+                self._flush()
+
+    def finish(self):
+        """Call after backward(): flush the tail bucket, wait, unpack, scale by 1/world."""
+        if self.world == 1:
+            return
+        self._flush()
+        inv = 1.0 / self.world
+        for w, flat, ps in self._pending:
+            w.wait()
+            if flat is not None:
+                off = 0
+                for p in ps:
+                    n = p.grad.numel()
+                    p.grad.copy_(flat[off:off + n].view_as(p.grad))
+                    off += n
+            for p in ps:
+                _scale_(p.grad, inv)
+        self._pending = []
+        self._seen = 0
+
+    def remove(self):
+        for h in self._hooks:
+            h.remove()
+
+
+def _scale_(t: torch.Tensor, s: float):
+    if t.is_cuda and t.dtype == torch.float32 and t.is_contiguous():
+        from . import ops
+        ops.check(ops.lib.ds2_scale(ops._p(t), float(s), ops._p(t), t.numel(), ops._stream()), "ds2_scale")
+    else:
+        t.mul_(s)

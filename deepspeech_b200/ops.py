@@ -1,0 +1,498 @@
+"""Thin torch-tensor wrappers over the C ABI plus the autograd glue of the hot path.
+
+torch is used for device memory, streams and autograd bookkeeping only; every FLOP goes through
+libds2_b200.so.  Tensors handed to the C ABI must be CUDA + contiguous."""
+from __future__ import annotations
+
+import math
+from ctypes import c_void_p
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import DS2_BF16, DS2_F32, check, lib
+
+RELU_CAP = 20.0                                   # src/custom_ops.py:71
+SBN_SCALE = 1.0 / math.sqrt(1.0 + 1e-5)           # src/custom_ops.py:184-199 as written
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else c_void_p(t.data_ptr())
+
+
+def _stream():
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return DS2_F32
+    if t.dtype == torch.bfloat16:
+        return DS2_BF16
+    raise ValueError("ds2: unsupported dtype %s (float32 / bfloat16 only)" % t.dtype)
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("deepspeech_b200 ops need CUDA tensors (no CPU fallback)")
+
+
+_ws_cache = {}
+
+
+def _workspace(nbytes: int, device, tag: str) -> torch.Tensor:
+    key = (tag, device)
+    ws = _ws_cache.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
+        _ws_cache[key] = ws
+    return ws
+
+
+# ------------------------------------------------------------------------------------ GEMM
+def gemm_nt(A: torch.Tensor, B: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False, M=None, N=None, K=None,
+            lda=None, ldb=None, out: Optional[torch.Tensor] = None, out_dtype=torch.float32, alpha: float = 1.0,
+            beta: float = 0.0, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """C[M,N] = alpha * A . B^T + bias + beta*C.  A is [M,K] (a_mn False) or [K,M] (a_mn True); B is
+    [N,K] or [K,N].  A/B may be 2-D row slices of larger buffers (lda/ldb = row pitch)."""
+    _need_cuda(A, B)
+    if M is None:
+        M = A.shape[1] if a_mn else A.shape[0]
+    if K is None:
+        K = A.shape[0] if a_mn else A.shape[1]
+    if N is None:
+        N = B.shape[1] if b_mn else B.shape[0]
+    lda = A.stride(0) if lda is None else lda
+    ldb = B.stride(0) if ldb is None else ldb
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=A.device)
+    ldc = out.stride(0)
+    use_tc = (A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16 and lda % 8 == 0 and ldb % 8 == 0
+              and A.data_ptr() % 16 == 0 and B.data_ptr() % 16 == 0 and K >= 8)
+    if use_tc:
+        check(lib.ds2_gemm_bf16(_p(A), lda, int(a_mn), _p(B), ldb, int(b_mn), _p(out), _dt(out), ldc, M, N, K,
+                                alpha, beta, _p(bias), _stream()), "ds2_gemm_bf16")
+    else:
+        sam, sak = (1, lda) if a_mn else (lda, 1)
+        sbn, sbk = (1, ldb) if b_mn else (ldb, 1)
+        check(lib.ds2_gemm_generic(_p(A), _dt(A), sam, sak, _p(B), _dt(B), sbn, sbk, _p(out), _dt(out), ldc, M, N, K,
+                                   alpha, beta, _p(bias), _stream()), "ds2_gemm_generic")
+    return out
+
+
+def cast(x: torch.Tensor, dtype) -> torch.Tensor:
+    if x.dtype == dtype:
+        return x
+    out = torch.empty(x.shape, dtype=dtype, device=x.device)
+    check(lib.ds2_cast(_p(x.contiguous()), _dt(x), _p(out), _dt(out), x.numel(), _stream()), "ds2_cast")
+    return out
+
+
+def add2(a: torch.Tensor, b: torch.Tensor, out_dtype) -> torch.Tensor:
+    out = torch.empty(a.shape, dtype=out_dtype, device=a.device)
+    check(lib.ds2_add2(_p(a), _p(b), _dt(a), _p(out), _dt(out), a.numel(), _stream()), "ds2_add2")
+    return out
+
+
+def colsum(x2d: torch.Tensor, R: int, N: int, ld: int) -> torch.Tensor:
+    out = torch.empty(N, dtype=torch.float32, device=x2d.device)
+    check(lib.ds2_colsum(_p(x2d), _dt(x2d), R, N, ld, _p(out), 0, _stream()), "ds2_colsum")
+    return out
+
+
+# ------------------------------------------------------------------------------------ relux
+class _ReluxFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, cap):
+        xc = x.contiguous()
+        y = torch.empty_like(xc)
+        has_cap = cap is not None
+        check(lib.ds2_relux_fwd(_p(xc), _p(y), xc.numel(), float(cap or 0.0), int(has_cap), _stream()), "ds2_relux_fwd")
+        ctx.save_for_backward(xc)
+        ctx.cap = cap
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        dyc = dy.contiguous()
+        dx = torch.empty_like(x)
+        check(lib.ds2_relux_bwd(_p(x), _p(dyc), _p(dx), x.numel(), float(ctx.cap or 0.0), int(ctx.cap is not None), _stream()),
+              "ds2_relux_bwd")
+        return dx, None
+
+
+def relux(x: torch.Tensor, capping=None) -> torch.Tensor:
+    _need_cuda(x)
+    if x.dtype != torch.float32:
+        raise ValueError("relux: float32 tensors only")
+    return _ReluxFn.apply(x, capping)
+
+
+# ------------------------------------------------------------------------------------ BN (+clip), channel-last
+def _bn_scratch(device):
+    return _workspace(2 * 256 * 8, device, "bn").view(torch.float64)
+
+
+def bn_stats(x: torch.Tensor, C: int, eps: float) -> Tuple[torch.Tensor, torch.Tensor]:
+    R = x.numel() // C
+    mean = torch.empty(C, dtype=torch.float32, device=x.device)
+    rstd = torch.empty(C, dtype=torch.float32, device=x.device)
+    check(lib.ds2_bn_stats(_p(x), R, C, eps, _p(_bn_scratch(x.device)), _p(mean), _p(rstd), _stream()), "ds2_bn_stats")
+    return mean, rstd
+
+
+class _BnClipFn(torch.autograd.Function):
+    """y = clip(gamma * (x - mean_batch) * rstd_batch + beta) over a channel-last [B,T,F,C] tensor;
+    the output is written with element strides `omap` = (sb, st, sf, sc) into a tensor of shape
+    `oshape` / dtype `odtype` (NHWC itself, or the RNN layout)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps, cap, oshape, omap, odtype):
+        B, T, Fq, C = x.shape
+        mean, rstd = bn_stats(x, C, eps)
+        out = torch.empty(oshape, dtype=odtype, device=x.device)
+        clip = cap is not None
+        check(lib.ds2_bn_clip_fwd(_p(x), B, T, Fq, C, _p(mean), _p(rstd), _p(gamma), _p(beta), float(cap or 0.0), int(clip),
+                                  _p(out), _dt(out), *omap, _stream()), "ds2_bn_clip_fwd")
+        ctx.save_for_backward(x, gamma, beta, mean, rstd)
+        ctx.cap, ctx.omap = cap, omap
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, gamma, beta, mean, rstd = ctx.saved_tensors
+        B, T, Fq, C = x.shape
+        dout = dout.contiguous()
+        dx = torch.empty_like(x)
+        dgamma = torch.empty_like(gamma)
+        dbeta = torch.empty_like(beta)
+        check(lib.ds2_bn_clip_bwd(_p(x), B, T, Fq, C, _p(mean), _p(rstd), _p(gamma), _p(beta), float(ctx.cap or 0.0),
+                                  int(ctx.cap is not None), _p(dout), _dt(dout), *ctx.omap, _p(_bn_scratch(x.device)),
+                                  _p(dx), _p(dgamma), _p(dbeta), _stream()), "ds2_bn_clip_bwd")
+        return dx, dgamma, dbeta, None, None, None, None, None
+
+
+def bn_clip_nhwc(x, gamma, beta, eps, cap=None):
+    """channel-last in, channel-last out (fp32)."""
+    B, T, Fq, C = x.shape
+    omap = (T * Fq * C, Fq * C, C, 1)
+    return _BnClipFn.apply(x.contiguous(), gamma, beta, eps, cap, tuple(x.shape), omap, torch.float32)
+
+
+def bn_clip_to_rnn_layout(x, gamma, beta, eps, cap, feature_order: str, odtype):
+    """channel-last [B,T,F,C] in, time-major [T,B,C*F] out; feature = c*F+f ('cf', NCHW model,
+    src/deepSpeech_NCHW.py:166-168) or f*C+c ('fc', NHWC model, src/deepSpeech.py:162-164)."""
+    B, T, Fq, C = x.shape
+    feat = C * Fq
+    omap = (feat, B * feat, 1, Fq) if feature_order == "cf" else (feat, B * feat, C, 1)
+    return _BnClipFn.apply(x.contiguous(), gamma, beta, eps, cap, (T, B, feat), omap, odtype)
+
+
+# ------------------------------------------------------------------------------------ conv2d (channel-last, HWIO)
+class _Conv2dFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, bias, st, sf):
+        B, Ti, Fi, Ci = x.shape
+        KT, KF, Ci2, Co = w.shape
+        if Ci2 != Ci:
+            raise ValueError("conv2d: filter in-channels %d != input channels %d" % (Ci2, Ci))
+        To, Fo = (Ti - KT) // st + 1, (Fi - KF) // sf + 1
+        if To <= 0 or Fo <= 0:
+            raise ValueError("conv2d: input %dx%d smaller than the %dx%d filter" % (Ti, Fi, KT, KF))
+        y = torch.empty((B, To, Fo, Co), dtype=torch.float32, device=x.device)
+        check(lib.ds2_conv2d_fwd(_p(x), _dt(x), _p(w), _p(bias), _p(y), B, Ti, Fi, Ci, Co, KT, KF, st, sf, _stream()),
+              "ds2_conv2d_fwd")
+        ctx.save_for_backward(x, w)
+        ctx.geom = (B, Ti, Fi, Ci, Co, KT, KF, st, sf)
+        ctx.has_bias = bias is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        g = ctx.geom
+        dy = dy.contiguous()
+        dw = torch.empty_like(w)
+        db = torch.empty(g[4], dtype=torch.float32, device=x.device) if ctx.has_bias else None
+        check(lib.ds2_conv2d_wgrad(_p(x), _dt(x), _p(dy), _p(dw), _p(db), *g, _stream()), "ds2_conv2d_wgrad")
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(x.shape, dtype=torch.float32, device=x.device)
+            check(lib.ds2_conv2d_dgrad(_p(dy), _p(w), _p(dx), *g, _stream()), "ds2_conv2d_dgrad")
+            if x.dtype != torch.float32:
+                dx = cast(dx, x.dtype)
+        return dx, dw, db, None, None
+
+
+def conv2d_nhwc(x, w, bias, st, sf):
+    _need_cuda(x, w)
+    return _Conv2dFn.apply(x.contiguous(), w.contiguous(), bias, st, sf)
+
+
+# ------------------------------------------------------------------------------------ recurrent stack
+def rnn_path_dtype(B: int, H: int, ND: int, want_bf16: bool):
+    """bf16 (persistent tcgen05 kernel) when requested and the shape is taken, else fp32."""
+    if want_bf16 and lib.ds2_rnn_relu_persistent_supported(B, H, ND):
+        return torch.bfloat16
+    return torch.float32
+
+
+class _BiRNNLayerFn(torch.autograd.Function):
+    """One (bi)directional clipped-ReLU layer over the whole sequence:
+         wx = x . Wcat^T            (one batched GEMM, all timesteps, both directions)
+         hs = recurrence(wx, U, b)  (persistent kernel or per-step kernels)
+         out = sum_d hs[d]          (src/custom_ops.py:95)
+       x [T,B,I]; Wcat [ND*H, I]; U [ND,H,H]; bias [ND,H]; lens int32 [B] (device).
+       Gradients flow in fp32 between layers (x.grad has x's dtype)."""
+
+    @staticmethod
+    def forward(ctx, x, Wcat, U, bias, lens, reverse_mask, want_bf16, out_dtype):
+        T, B, I = x.shape
+        ND, H = U.shape[0], U.shape[1]
+        dev = x.device
+        cdt = rnn_path_dtype(B, H, ND, want_bf16)
+        if cdt == torch.bfloat16:
+            xg, Wg, Ug = cast(x.contiguous(), torch.bfloat16), cast(Wcat, torch.bfloat16), cast(U, torch.bfloat16)
+        else:
+            xg, Wg, Ug = cast(x.contiguous(), torch.float32), Wcat, U
+        wx = gemm_nt(xg.view(T * B, I), Wg)                                       # [TB, ND*H] fp32
+        hs = torch.empty((ND, T, B, H), dtype=cdt, device=dev)
+        wsb = lib.ds2_rnn_workspace_bytes(T, B, H, ND, _dt(hs))
+        ws = _workspace(wsb, dev, "rnn") if wsb else None
+        check(lib.ds2_rnn_relu_fwd(_p(wx), SBN_SCALE, _p(Ug), _p(bias), _p(lens), _p(hs), _dt(hs), T, B, H, ND,
+                                   reverse_mask, RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_fwd")
+        if ND == 2:
+            out = add2(hs[0], hs[1], out_dtype)
+        else:
+            out = cast(hs[0], out_dtype)
+        ctx.save_for_backward(xg, Wg, Ug, hs, lens)
+        ctx.meta = (T, B, I, H, ND, reverse_mask, x.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        xg, Wg, Ug, hs, lens = ctx.saved_tensors
+        T, B, I, H, ND, reverse_mask, xdtype = ctx.meta
+        dev = xg.device
+        cdt = hs.dtype
+        dout = cast(dout.contiguous(), torch.float32)
+        dz = torch.empty((T * B, ND * H), dtype=cdt, device=dev)
+        wsb = lib.ds2_rnn_workspace_bytes(T, B, H, ND, _dt(hs))
+        ws = _workspace(wsb, dev, "rnn") if wsb else None
+        check(lib.ds2_rnn_relu_bwd(_p(dout), _p(Ug), _p(lens), _p(hs), _p(dz), _dt(hs), T, B, H, ND, reverse_mask,
+                                   RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_bwd")
+        db = colsum(dz, T * B, ND * H, ND * H).view(ND, H)
+        # dW = scale * dz^T x ; dx = scale * dz W   (both directions in one GEMM each)
+        dW = gemm_nt(dz, xg.view(T * B, I), a_mn=True, b_mn=True, alpha=SBN_SCALE)            # [ND*H, I]
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm_nt(dz, Wg, b_mn=True, alpha=SBN_SCALE).view(T, B, I)                   # [TB, I] fp32
+            if xdtype != torch.float32:
+                dx = cast(dx, xdtype)
+        # dU[d] = sum_t dz[d,t]^T h[d,t_prev]
+        dU = torch.empty((ND, H, H), dtype=torch.float32, device=dev)
+        for d in range(ND):
+            rev = (reverse_mask >> d) & 1
+            if T > 1:
+                a_off = (0 if rev else B * ND * H) + d * H           # dz rows t = 1.. (fw) / 0..T-2 (bw)
+                A = dz.view(-1)[a_off:]
+                Bm = hs[d].reshape(T * B, H)[(B if rev else 0):]
+                gemm_nt(A, Bm, a_mn=True, b_mn=True, M=H, N=H, K=(T - 1) * B, lda=ND * H, ldb=H, out=dU[d])
+            else:
+                dU[d].zero_()
+        return dx, dW, dU, db, None, None, None, None
+
+
+def birnn_layer(x, Wcat, U, bias, lens, reverse_mask: int, want_bf16: bool, out_dtype):
+    _need_cuda(x, Wcat, U, bias, lens)
+    return _BiRNNLayerFn.apply(x, Wcat.contiguous(), U.contiguous(), bias.contiguous(), lens, reverse_mask, want_bf16, out_dtype)
+
+
+class _BiGRULayerFn(torch.autograd.Function):
+    """GRU analogue of _BiRNNLayerFn (build-defined, see include/ds2_b200.h).  fp32 path."""
+
+    @staticmethod
+    def forward(ctx, x, Wcat, U, bw, bu, lens, reverse_mask, out_dtype):
+        T, B, I = x.shape
+        ND, H = U.shape[0], U.shape[2]
+        dev = x.device
+        xg = cast(x.contiguous(), torch.float32)
+        wx = gemm_nt(xg.view(T * B, I), Wcat)                                      # [TB, ND*3H]
+        hs = torch.empty((ND, T, B, H), dtype=torch.float32, device=dev)
+        gates = torch.empty((ND, T, B, 4 * H), dtype=torch.float32, device=dev)
+        check(lib.ds2_gru_fwd(_p(wx), SBN_SCALE, _p(U), _p(bw), _p(bu), _p(lens), _p(hs), _p(gates), DS2_F32, T, B, H, ND,
+                              reverse_mask, _stream()), "ds2_gru_fwd")
+        out = add2(hs[0], hs[1], out_dtype) if ND == 2 else cast(hs[0], out_dtype)
+        ctx.save_for_backward(xg, Wcat, U, hs, gates, lens)
+        ctx.meta = (T, B, I, H, ND, reverse_mask, x.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        xg, Wcat, U, hs, gates, lens = ctx.saved_tensors
+        T, B, I, H, ND, reverse_mask, xdtype = ctx.meta
+        dev = xg.device
+        dout = cast(dout.contiguous(), torch.float32)
+        dgi = torch.empty((T * B, ND * 3 * H), dtype=torch.float32, device=dev)
+        dgh = torch.empty((T * B, ND * 3 * H), dtype=torch.float32, device=dev)
+        dhz = torch.zeros((ND, B, H), dtype=torch.float32, device=dev)
+        check(lib.ds2_gru_bwd(_p(dout), _p(U), _p(lens), _p(hs), _p(gates), _p(dgi), _p(dgh), _p(dhz), DS2_F32, T, B, H, ND,
+                              reverse_mask, _stream()), "ds2_gru_bwd")
+        dbw = colsum(dgi, T * B, ND * 3 * H, ND * 3 * H).view(ND, 3 * H)
+        dbu = colsum(dgh, T * B, ND * 3 * H, ND * 3 * H).view(ND, 3 * H)
+        dW = gemm_nt(dgi, xg.view(T * B, I), a_mn=True, b_mn=True, alpha=SBN_SCALE)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm_nt(dgi, Wcat, b_mn=True, alpha=SBN_SCALE).view(T, B, I)
+            if xdtype != torch.float32:
+                dx = cast(dx, xdtype)
+        dU = torch.empty((ND, 3 * H, H), dtype=torch.float32, device=dev)
+        for d in range(ND):
+            rev = (reverse_mask >> d) & 1
+            if T > 1:
+                a_off = (0 if rev else B * ND * 3 * H) + d * 3 * H
+                A = dgh.view(-1)[a_off:]
+                Bm = hs[d].reshape(T * B, H)[(B if rev else 0):]
+                gemm_nt(A, Bm, a_mn=True, b_mn=True, M=3 * H, N=H, K=(T - 1) * B, lda=ND * 3 * H, ldb=H, out=dU[d])
+            else:
+                dU[d].zero_()
+        return dx, dW, dU, dbw, dbu, None, None, None
+
+
+def bigru_layer(x, Wcat, U, bw, bu, lens, reverse_mask: int, out_dtype):
+    _need_cuda(x, Wcat, U, bw, bu, lens)
+    return _BiGRULayerFn.apply(x, Wcat.contiguous(), U.contiguous(), bw.contiguous(), bu.contiguous(), lens, reverse_mask,
+                               out_dtype)
+
+
+# ------------------------------------------------------------------------------------ linear
+class _LinearFn(torch.autograd.Function):
+    """y[R,N] = x[R,K] . W[N,K]^T + b  (fp32 out).  src/deepSpeech_NCHW.py:195-198, custom_ops._linear."""
+
+    @staticmethod
+    def forward(ctx, x2d, W, b, want_bf16):
+        if want_bf16 and x2d.dtype == torch.bfloat16:
+            Wg = cast(W, torch.bfloat16)
+        else:
+            Wg = W
+            x2d = cast(x2d, torch.float32)
+        y = gemm_nt(x2d, Wg, bias=b)
+        ctx.save_for_backward(x2d, W)
+        ctx.has_bias = b is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2d, W = ctx.saved_tensors
+        dy = dy.contiguous()
+        R, K = x2d.shape
+        N = W.shape[0]
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm_nt(dy, W, b_mn=True)                      # [R,K] = dy[R,N] . W[N,K]
+            if x2d.dtype != torch.float32:
+                dx = cast(dx, x2d.dtype)
+        dW = gemm_nt(dy, x2d, a_mn=True, b_mn=True)             # [N,K] = dy^T x
+        db = colsum(dy, R, N, N) if ctx.has_bias else None
+        return dx, dW, db, None
+
+
+def linear(x2d, W, b, want_bf16=False):
+    _need_cuda(x2d, W)
+    return _LinearFn.apply(x2d.contiguous(), W.contiguous(), b, want_bf16)
+
+
+# ------------------------------------------------------------------------------------ CTC
+def ctc_prepare_labels(indices, values, dense_shape, num_classes: int, preprocess_collapse_repeated: bool):
+    """Host-side label pre-processing of tf.nn.ctc_loss on the SparseTensor built at
+    src/deepSpeech_train.py:437: per batch row, in index order, collapse adjacent repeats when asked,
+    stop at the first label >= num_classes-1 (a valid label after it is an error).  Returns
+    (labels [B,Lmax] int32, label_lens [B] int32, repeats [B] int32) as numpy arrays."""
+    idx = np.asarray(indices, dtype=np.int64).reshape(-1, 2)
+    vals = np.asarray(values, dtype=np.int64).reshape(-1)
+    Bn = int(dense_shape[0])
+    if idx.shape[0] != vals.shape[0]:
+        raise ValueError("ctc_loss: labels.indices and labels.values disagree in length")
+    if idx.shape[0] and (idx[:, 0].min() < 0 or idx[:, 0].max() >= Bn):
+        raise ValueError("ctc_loss: label batch index out of range")
+    seqs: List[List[int]] = [[] for _ in range(Bn)]
+    order = np.lexsort((idx[:, 1], idx[:, 0])) if idx.shape[0] else []
+    prev_b, prev_v, finished = -1, None, False
+    for i in order:
+        b, v = int(idx[i, 0]), int(vals[i])
+        if b != prev_b:
+            prev_b, prev_v, finished = b, None, False
+        if prev_v is None or not preprocess_collapse_repeated or v != prev_v:
+            if v >= num_classes - 1 or v < 0:
+                finished = True
+            else:
+                if finished:
+                    raise ValueError("ctc_loss: saw a non-null label (index >= num_classes - 1) following a null "
+                                     "label, batch: %d" % b)
+                seqs[b].append(v)
+        prev_v = v
+    Lmax = max([len(s) for s in seqs] + [1])
+    lab = np.zeros((Bn, Lmax), dtype=np.int32)
+    lens = np.zeros(Bn, dtype=np.int32)
+    reps = np.zeros(Bn, dtype=np.int32)
+    for b, s in enumerate(seqs):
+        lab[b, :len(s)] = s
+        lens[b] = len(s)
+        reps[b] = sum(1 for i in range(1, len(s)) if s[i] == s[i - 1])
+    return lab, lens, reps
+
+
+class _CTCFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, labels_dev, label_lens_dev, seq_lens_dev, Lmax):
+        T, B, K = logits.shape
+        loss = torch.empty(B, dtype=torch.float32, device=logits.device)
+        grad = torch.empty_like(logits)
+        wsb = lib.ds2_ctc_workspace_bytes(T, B, K, Lmax)
+        ws = _workspace(wsb, logits.device, "ctc")
+        check(lib.ds2_ctc_loss_fwd_bwd(_p(logits), T, B, K, _p(labels_dev), Lmax, _p(label_lens_dev), _p(seq_lens_dev), None,
+                                       _p(loss), _p(grad), _p(ws), wsb, _stream()), "ds2_ctc_loss_fwd_bwd")
+        ctx.save_for_backward(grad)
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        (grad,) = ctx.saved_tensors
+        T, B, K = grad.shape
+        out = torch.empty_like(grad)
+        check(lib.ds2_ctc_scale_grad(_p(grad), _p(dloss.contiguous().float()), _p(out), T, B, K, _stream()), "ds2_ctc_scale_grad")
+        return out, None, None, None, None
+
+
+def ctc_loss_dense(logits: torch.Tensor, labels_np, label_lens_np, repeats_np, seq_lens) -> torch.Tensor:
+    """Per-utterance CTC NLL [B] from packed labels; autograd-aware.  Raises ValueError where TF raises
+    InvalidArgumentError ("Not enough time for target transition sequence")."""
+    _need_cuda(logits)
+    if logits.dtype != torch.float32:
+        logits = cast(logits, torch.float32)             # CTC always runs in fp32 (src/deepSpeech_NCHW.py:225)
+    T, B, K = logits.shape
+    sl = np.asarray(seq_lens.detach().cpu().numpy() if isinstance(seq_lens, torch.Tensor) else seq_lens, dtype=np.int32)
+    if sl.shape[0] != B or labels_np.shape[0] != B:
+        raise ValueError("ctc_loss: batch size mismatch (logits %d, labels %d, sequence_length %d)" % (B, labels_np.shape[0], sl.shape[0]))
+    if (sl > T).any() or (sl < 0).any():
+        raise ValueError("ctc_loss: sequence_length must lie in [0, %d]" % T)
+    need = label_lens_np + repeats_np
+    bad = np.nonzero(sl < need)[0]
+    if bad.size:
+        b = int(bad[0])
+        raise ValueError("ctc_loss: Not enough time for target transition sequence (required: %d, available: %d) batch: %d"
+                         % (int(need[b]), int(sl[b]), b))
+    if labels_np.size and (labels_np.max() >= K - 1 or labels_np.min() < 0):
+        raise ValueError("ctc_loss: label out of range [0, %d)" % (K - 1))
+    dev = logits.device
+    host = np.concatenate([labels_np.reshape(-1), label_lens_np, sl]).astype(np.int32)
+    packed = torch.from_numpy(host).to(dev, non_blocking=True)
+    Lmax = labels_np.shape[1]
+    lab_d = packed[:B * Lmax]
+    ll_d = packed[B * Lmax:B * Lmax + B]
+    sl_d = packed[B * Lmax + B:]
+    return _CTCFn.apply(logits.contiguous(), lab_d, ll_d, sl_d, Lmax)

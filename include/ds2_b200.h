@@ -1,0 +1,138 @@
+/* ds2_b200 - C ABI of the B200-native DeepSpeech2 training hot path.
+ *
+ * The reference (yxlao/deepSpeech) has no FFI: its hot path is a set of Python call sites into
+ * TensorFlow's C++ CPU kernels.  Each entry point below replaces the TF op(s) reached from the
+ * cited reference line(s); a reference maintainer would bind them with ctypes.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - `stream` is a cudaStream_t passed as void*; work is stream-ordered, nothing synchronises;
+ *   - the library borrows the caller's buffers for the duration of the call and allocates nothing
+ *     itself: scratch is passed in explicitly (ds2_*_workspace_bytes tells how much);
+ *   - return value: DS2_OK or a DS2_ERR_* code; ds2_last_error() returns the message of the last
+ *     failure on the calling thread;
+ *   - dtypes: DS2_F32 = 0, DS2_BF16 = 1;
+ *   - activations are channel-last: conv tensors [B,T,F,C], recurrent tensors time-major [T,B,*].
+ */
+#ifndef DS2_B200_H_
+#define DS2_B200_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { DS2_F32 = 0, DS2_BF16 = 1 };
+enum {
+  DS2_OK = 0,
+  DS2_ERR_BAD_ARG = 1,      /* null pointer, misaligned pointer, bad enum                         */
+  DS2_ERR_BAD_SHAPE = 2,    /* negative / inconsistent / unsupported dimensions                   */
+  DS2_ERR_WORKSPACE = 3,    /* scratch buffer missing or too small                                */
+  DS2_ERR_UNSUPPORTED = 4,  /* shape/dtype combination this build has no kernel for               */
+  DS2_ERR_CUDA = 5          /* a CUDA runtime/driver call failed (message has the CUDA error)     */
+};
+
+const char* ds2_last_error(void);
+int ds2_version(void);
+/* number of kernels this library has launched in this process (bench.py's gpu_launches) */
+long long ds2_launch_count(void);
+
+/* ---- CTC ------------------------------------------------------------------------------------
+ * tf.nn.ctc_loss(labels, inputs=float32 logits [T,B,K], sequence_length, time_major=True) as
+ * called at src/deepSpeech_NCHW.py:225 and src/deepSpeech.py:227: blank = K-1, softmax inside,
+ * loss[b] = -log p(label_b | logits_b[:seq_lens[b]]), grad = d(sum_b dloss[b]*loss[b])/d logits
+ * (zero for t >= seq_lens[b]).  `labels` is [B,Lmax] int32, row b holds label_lens[b] class ids
+ * in [0,K-2] (already collapsed/terminated by the host shim, src/deepSpeech_dummy.py:89-98 +
+ * TF's preprocess_collapse_repeated).  dloss may be NULL (= all ones); grad may be NULL.
+ * The caller must have checked seq_lens[b] >= label_lens[b] + repeats (TF raises otherwise). */
+size_t ds2_ctc_workspace_bytes(int T, int B, int K, int Lmax);
+int ds2_ctc_loss_fwd_bwd(const float* logits, int T, int B, int K, const int* labels, int Lmax, const int* label_lens,
+                         const int* seq_lens, const float* dloss, float* loss, float* grad, void* workspace,
+                         size_t workspace_bytes, void* stream);
+/* out[t,b,k] = grad[t,b,k] * dloss[b]: applies the upstream d/dloss_b (e.g. 1/B of reduce_mean,
+ * src/deepSpeech_NCHW.py:226) to a gradient computed with dloss = NULL. */
+int ds2_ctc_scale_grad(const float* grad, const float* dloss, float* out, int T, int B, int K, void* stream);
+
+/* ---- GEMM -----------------------------------------------------------------------------------
+ * tf.matmul call sites: src/custom_ops.py:61 (W.x, batched over all timesteps), :67 (U.h, see
+ * ds2_rnn_*), :249-251 (_linear), src/deepSpeech_NCHW.py:196 (FC), and their gradients
+ * (src/deepSpeech_train.py:287).
+ * ds2_gemm_bf16: tcgen05/TMA kernel.  C[M,N] = alpha*A*B^T + bias[n] + beta*C.  A is [M,K]
+ *   row-major (a_mn_major=0, lda = row pitch) or [K,M] row-major (a_mn_major=1); same for B with N.
+ *   Pitches in elements, multiples of 8; bases 16-byte aligned.  c_dtype DS2_F32 or DS2_BF16.
+ * ds2_gemm_generic: any strides / dtypes, CUDA cores, fp32 accumulation (small or odd shapes).
+ *   C[m,n] = alpha * sum_k A[m*sam + k*sak] * B[n*sbn + k*sbk] + bias[n] + beta*C[m*ldc+n]. */
+int ds2_gemm_bf16(const void* A, long lda, int a_mn_major, const void* B, long ldb, int b_mn_major, void* C, int c_dtype,
+                  long ldc, int M, int N, int K, float alpha, float beta, const float* bias, void* stream);
+int ds2_gemm_generic(const void* A, int a_dtype, long sam, long sak, const void* B, int b_dtype, long sbn, long sbk, void* C,
+                     int c_dtype, long ldc, int M, int N, int K, float alpha, float beta, const float* bias, void* stream);
+
+/* ---- recurrent layers -----------------------------------------------------------------------
+ * CustomRNNCell2.__call__ (src/custom_ops.py:48-72) unrolled over time by
+ * tf.nn.bidirectional_dynamic_rnn (src/custom_ops.py:91-93, src/deepSpeech.py:174-183):
+ *   h[d,t] = t < lens[b] ? min(max(scale*wx[t,b,d*H:] + U[d] h[d,t-/+1] + bias[d], 0), cap) : 0
+ * wx   [T,B,ND*H] f32  - input projection W.x for all timesteps (scale = seq_batch_norm's
+ *                        1/sqrt(1+1e-5), src/custom_ops.py:184-199 as written);
+ * u    [ND,H,H], bias [ND,H] f32, lens [B] int32, hs [ND,T,B,H] out; direction d runs backward in
+ * time when bit d of reverse_mask is set.  dtype selects the path: DS2_F32 = per-step CUDA-core
+ * kernels, u/hs fp32; DS2_BF16 = persistent tcgen05 kernel, u/hs bf16 (see
+ * ds2_rnn_relu_persistent_supported).
+ * Backward: dout [T,B,H] f32 is the gradient w.r.t. sum_d hs[d]; dz [T,B,ND*H] (f32|bf16) receives
+ * the gradient w.r.t. the pre-activation, from which the caller forms dW, dU, db, dx by GEMM. */
+int ds2_rnn_relu_fwd(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, int dtype,
+                     int T, int B, int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes,
+                     void* stream);
+int ds2_rnn_relu_bwd(const float* dout, const void* u, const int* lens, const void* hs, void* dz, int dtype, int T, int B,
+                     int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes, void* stream);
+size_t ds2_rnn_workspace_bytes(int T, int B, int H, int ND, int dtype);
+int ds2_rnn_relu_persistent_supported(int B, int H, int ND);
+
+/* GRU (gate order r,z,n; cuDNN / torch.nn.GRU form).  NOT in the reference: BASELINE
+ * configs 3 and 5 ask for it, the build defines it.  wx [T,B,ND*3H], u [ND,3H,H], bw/bu [ND,3H],
+ * hs [ND,T,B,H], gates [ND,T,B,4H] (r,z,n,U_n h+bu_n saved for backward), dgi/dgh [T,B,ND*3H]. */
+int ds2_gru_fwd(const float* wx, float scale, const void* u, const float* bw, const float* bu, const int* lens, void* hs,
+                void* gates, int dtype, int T, int B, int H, int ND, int reverse_mask, void* stream);
+int ds2_gru_bwd(const float* dout, const void* u, const int* lens, const void* hs, const void* gates, void* dgi, void* dgh,
+                float* dhz_scratch, int dtype, int T, int B, int H, int ND, int reverse_mask, void* stream);
+
+/* ---- conv front-end -------------------------------------------------------------------------
+ * tf.nn.conv2d + bias_add at src/deepSpeech_NCHW.py:120-127,:142-151 (src/deepSpeech.py:120-126,
+ * :143-149): VALID cross-correlation, HWIO filters w[KT,KF,Ci,Co], strides (st,sf).
+ * x [B,Ti,Fi,Ci] (f32|bf16), y [B,To,Fo,Co] f32, To=(Ti-KT)/st+1, Fo=(Fi-KF)/sf+1. */
+int ds2_conv2d_fwd(const void* x, int x_dtype, const float* w, const float* bias, float* y, int B, int Ti, int Fi, int Ci,
+                   int Co, int KT, int KF, int st, int sf, void* stream);
+int ds2_conv2d_dgrad(const float* dy, const float* w, float* dx, int B, int Ti, int Fi, int Ci, int Co, int KT, int KF,
+                     int st, int sf, void* stream);
+int ds2_conv2d_wgrad(const void* x, int x_dtype, const float* dy, float* dw, float* dbias, int B, int Ti, int Fi, int Ci,
+                     int Co, int KT, int KF, int st, int sf, void* stream);
+
+/* batch_norm2 / batch_norm (src/custom_ops.py:107-160, :163-181; training mode, biased batch
+ * variance over all rows of the channel-last [R,C] tensor) fused with relux(.., capping)
+ * (src/custom_ops.py:99-104).  C must divide 256.  sums_scratch: 2*C doubles.
+ * The activation-side tensor (out / dout) is addressed as b*sb + t*st + f*sf + c*sc so it can be
+ * written straight into the RNN layout [T,B,C*F] (src/deepSpeech_NCHW.py:166-168) or [T,B,F*C]
+ * (src/deepSpeech.py:162-164). */
+int ds2_bn_stats(const float* x, long R, int C, float eps, double* sums_scratch, float* mean, float* rstd, void* stream);
+int ds2_bn_clip_fwd(const float* x, int B, int T, int F, int C, const float* mean, const float* rstd, const float* gamma,
+                    const float* beta, float cap, int clip, void* out, int out_dtype, long sb, long st, long sf, long sc,
+                    void* stream);
+int ds2_bn_clip_bwd(const float* x, int B, int T, int F, int C, const float* mean, const float* rstd, const float* gamma,
+                    const float* beta, float cap, int clip, const void* dout, int dout_dtype, long sb, long st, long sf,
+                    long sc, double* sums_scratch, float* dx, float* dgamma, float* dbeta, void* stream);
+
+/* ---- element-wise helpers -------------------------------------------------------------------
+ * relux: src/custom_ops.py:99-104.  add2: fw+bw sum, src/custom_ops.py:95, src/deepSpeech.py:185. */
+int ds2_relux_fwd(const float* x, float* y, long n, float cap, int has_cap, void* stream);
+int ds2_relux_bwd(const float* x, const float* dy, float* dx, long n, float cap, int has_cap, void* stream);
+/* y = s*x: seq_batch_norm as written, src/custom_ops.py:184-199 (x / sqrt(1+1e-5)). */
+int ds2_scale(const float* x, float s, float* y, long n, void* stream);
+int ds2_add2(const void* a, const void* b, int in_dtype, void* out, int out_dtype, long n, void* stream);
+int ds2_cast(const void* in, int in_dtype, void* out, int out_dtype, long n, void* stream);
+int ds2_colsum(const void* x, int dtype, long R, int N, long ld, float* out, int accumulate, void* stream);
+int ds2_transpose(const void* in, int in_dtype, long R, long C, long ldi, void* out, int out_dtype, long ldo, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DS2_B200_H_ */

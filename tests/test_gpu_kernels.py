@@ -1,0 +1,285 @@
+"""GPU parity tests, kernel level: every C-ABI entry point against the CPU oracle (oracle/ds2_oracle.py)
+or a float64 restatement of the same formula.  Tolerances: fp32 kernels 1e-4 rel. on losses, 1e-3 on
+gradients (BASELINE.json north_star); bf16 tensor-core GEMM checked on bf16-rounded inputs (fp32
+accumulate) to 1e-3 of the result's scale."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ds2_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _ops():
+    from deepspeech_b200 import ops
+    return ops
+
+
+def relerr(a, b):
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+
+
+# ----------------------------------------------------------------------------------------- CTC
+def _ctc_case(T, B, L, ragged, seed, K=29):
+    rng = np.random.default_rng(seed)
+    x = rng.standard_normal((T, B, K)).astype(np.float32)
+    if ragged:
+        lens = rng.integers(T // 2, T + 1, size=B)
+        labels = [list(rng.integers(0, K - 1, size=rng.integers(max(L // 2, 0), L + 1))) for _ in range(B)]
+    else:
+        lens = np.full(B, T)
+        labels = [list(rng.integers(0, K - 1, size=L)) for _ in range(B)]
+    # TF collapses repeats in the dense label (preprocess_collapse_repeated=True in the reference call)
+    labels = [[v for i, v in enumerate(l) if i == 0 or v != l[i - 1]] for l in labels]
+    return x, labels, lens.astype(np.int32)
+
+
+def _run_ctc(x, labels, lens):
+    ops = _ops()
+    B = x.shape[1]
+    Lmax = max([len(l) for l in labels] + [1])
+    lab = np.zeros((B, Lmax), np.int32)
+    ll = np.zeros(B, np.int32)
+    for b, l in enumerate(labels):
+        lab[b, :len(l)] = l
+        ll[b] = len(l)
+    reps = np.asarray([sum(1 for i in range(1, len(l)) if l[i] == l[i - 1]) for l in labels], np.int32)
+    xt = torch.tensor(x, device="cuda", requires_grad=True)
+    loss = ops.ctc_loss_dense(xt, lab, ll, reps, lens)
+    loss.sum().backward()
+    torch.cuda.synchronize()
+    return loss.detach().cpu().numpy(), xt.grad.cpu().numpy()
+
+
+@pytest.mark.parametrize("T,B,L,ragged", [(1, 1, 1, False), (5, 2, 2, False), (12, 3, 0, False), (30, 4, 9, True),
+                                           (64, 7, 20, True), (200, 16, 50, False), (366, 8, 209, False),
+                                           (400, 8, 100, True)])
+def test_ctc_vs_oracle(T, B, L, ragged):
+    x, labels, lens = _ctc_case(T, B, L, ragged, seed=T * 31 + B)
+    ref_loss, ref_grad = O.ctc_loss_and_grad_np(x, labels, lens)
+    loss, grad = _run_ctc(x, labels, lens)
+    assert np.allclose(loss, ref_loss, rtol=1e-4, atol=1e-4), (loss, ref_loss)
+    assert relerr(grad, ref_grad) < 1e-3
+    assert np.abs(grad.sum(2)).max() < 1e-4           # rows sum to zero inside, are zero outside
+    for b in range(B):
+        assert np.abs(grad[lens[b]:, b]).max(initial=0.0) == 0.0
+
+
+def test_ctc_repeated_labels_without_collapse_and_closed_form():
+    ops = _ops()
+    # uniform logits, no repeats: loss = T ln K - ln C(T+L, 2L)
+    import math
+    T, L = 12, 5
+    loss, grad = _run_ctc(np.zeros((T, 1, 29), np.float32), [list(range(1, L + 1))], np.asarray([T], np.int32))
+    assert abs(loss[0] - (T * math.log(29) - math.log(math.comb(T + L, 2 * L)))) < 1e-4
+    # a label with an adjacent repeat needs a blank between: handled, and needs T >= L + repeats
+    x = np.random.default_rng(0).standard_normal((6, 1, 29)).astype(np.float32)
+    ref_loss, ref_grad = O.ctc_loss_and_grad_np(x, [[3, 3, 4]], [6])
+    loss, grad = _run_ctc(x, [[3, 3, 4]], np.asarray([6], np.int32))
+    assert np.allclose(loss, ref_loss, rtol=1e-4) and relerr(grad, ref_grad) < 1e-3
+    with pytest.raises(ValueError, match="Not enough time"):
+        _run_ctc(x[:3], [[3, 3, 4]], np.asarray([3], np.int32))
+    del ops
+
+
+def test_ctc_sparse_front_door_matches_oracle_transform():
+    from deepspeech_b200.ctc import ctc_loss
+    rng = np.random.default_rng(4)
+    T, B = 40, 3
+    x = rng.standard_normal((T, B, 29)).astype(np.float32)
+    dense = np.asarray([[5, 5, 0, 7, 28, 0], [9, 0, 9, 9, 1, 28], [0, 0, 0, 0, 0, 28]])
+    idx = np.argwhere(dense != 0)
+    vals = dense[dense != 0]
+    seqs = O.sparse_to_label_seqs(idx, vals, dense.shape)
+    assert seqs == [[5, 7], [9, 1], []]
+    ref_loss, _ = O.ctc_loss_and_grad_np(x, seqs, [T, T - 5, T - 9])
+    got = ctc_loss((idx, vals, dense.shape), torch.tensor(x, device="cuda"), np.asarray([T, T - 5, T - 9], np.int32),
+                   preprocess_collapse_repeated=True)
+    assert np.allclose(got.cpu().numpy(), ref_loss, rtol=1e-4)
+    with pytest.raises(ValueError, match="non-null label"):
+        ctc_loss((np.asarray([[0, 0], [0, 1]]), np.asarray([28, 3]), (1, 2)), torch.tensor(x[:, :1], device="cuda"),
+                 np.asarray([T], np.int32), preprocess_collapse_repeated=True)
+
+
+# ----------------------------------------------------------------------------------------- GEMM
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (256, 384, 512), (100, 29, 72), (130, 200, 264), (1, 8, 8),
+                                    (517, 1760, 2400)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (True, False), (False, True), (True, True)])
+def test_gemm_tcgen05_vs_fp64(M, N, K, a_mn, b_mn):
+    ops = _ops()
+    rng = np.random.default_rng(M + N + K)
+    Mp, Np = (M + 7) // 8 * 8, (N + 7) // 8 * 8          # MN-major operands need a row pitch multiple of 8
+    A = torch.tensor(rng.standard_normal((K, Mp) if a_mn else (M, K)), dtype=torch.bfloat16, device="cuda")
+    B = torch.tensor(rng.standard_normal((K, Np) if b_mn else (N, K)), dtype=torch.bfloat16, device="cuda")
+    bias = torch.tensor(rng.standard_normal(N), dtype=torch.float32, device="cuda")
+    C0 = torch.tensor(rng.standard_normal((M, N)), dtype=torch.float32, device="cuda")
+    C = C0.clone()
+    out = ops.gemm_nt(A, B, a_mn=a_mn, b_mn=b_mn, M=M, N=N, K=K, out=C, alpha=0.5, beta=2.0, bias=bias)
+    torch.cuda.synchronize()
+    Ad = A.double().cpu().numpy()
+    Bd = B.double().cpu().numpy()
+    Am = Ad[:, :M].T if a_mn else Ad
+    Bm = Bd[:, :N].T if b_mn else Bd
+    ref = 0.5 * Am @ Bm.T + bias.double().cpu().numpy() + 2.0 * C0.double().cpu().numpy()
+    assert relerr(out.cpu().numpy(), ref) < 1e-3
+    # bf16 output, no epilogue extras
+    out2 = ops.gemm_nt(A, B, a_mn=a_mn, b_mn=b_mn, M=M, N=N, K=K, out_dtype=torch.bfloat16)
+    assert relerr(out2.float().cpu().numpy(), Am @ Bm.T) < 1e-2
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (True, True), (True, False)])
+def test_gemm_generic_vs_fp64(a_mn, b_mn):
+    ops = _ops()
+    rng = np.random.default_rng(9)
+    M, N, K = 37, 29, 53
+    A = torch.tensor(rng.standard_normal((K, M) if a_mn else (M, K)), dtype=torch.float32, device="cuda")
+    B = torch.tensor(rng.standard_normal((K, N) if b_mn else (N, K)), dtype=torch.float32, device="cuda")
+    bias = torch.tensor(rng.standard_normal(N), dtype=torch.float32, device="cuda")
+    out = ops.gemm_nt(A, B, a_mn=a_mn, b_mn=b_mn, alpha=1.5, bias=bias)
+    Am = A.double().cpu().numpy().T if a_mn else A.double().cpu().numpy()
+    Bm = B.double().cpu().numpy().T if b_mn else B.double().cpu().numpy()
+    assert relerr(out.cpu().numpy(), 1.5 * Am @ Bm.T + bias.double().cpu().numpy()) < 1e-5
+
+
+# ----------------------------------------------------------------------------------------- conv / BN
+def test_conv2d_fwd_bwd_vs_torch_fp64():
+    ops = _ops()
+    rng = np.random.default_rng(11)
+    for (B, Ti, Fi, Ci, Co, KT, KF, st, sf) in [(2, 45, 161, 1, 4, 20, 5, 2, 2), (2, 13, 79, 4, 4, 10, 5, 2, 1)]:
+        x = torch.tensor(rng.standard_normal((B, Ti, Fi, Ci)), dtype=torch.float32, device="cuda", requires_grad=True)
+        w = torch.tensor(rng.standard_normal((KT, KF, Ci, Co)) * 0.1, dtype=torch.float32, device="cuda", requires_grad=True)
+        b = torch.tensor(rng.standard_normal(Co), dtype=torch.float32, device="cuda", requires_grad=True)
+        y = ops.conv2d_nhwc(x, w, b, st, sf)
+        g = torch.tensor(rng.standard_normal(tuple(y.shape)), dtype=torch.float32, device="cuda")
+        (y * g).sum().backward()
+        xr = x.detach().double().cpu().permute(0, 3, 1, 2).requires_grad_(True)
+        wr = w.detach().double().cpu().requires_grad_(True)
+        br = b.detach().double().cpu().requires_grad_(True)
+        yr = torch.nn.functional.conv2d(xr, wr.permute(3, 2, 0, 1), br, stride=(st, sf))
+        (yr * g.double().cpu().permute(0, 3, 1, 2)).sum().backward()
+        assert relerr(y.detach().cpu().permute(0, 3, 1, 2).numpy(), yr.detach().numpy()) < 1e-5
+        assert relerr(w.grad.cpu().numpy(), wr.grad.numpy()) < 1e-4
+        assert relerr(b.grad.cpu().numpy(), br.grad.numpy()) < 1e-4
+        assert relerr(x.grad.cpu().permute(0, 3, 1, 2).numpy(), xr.grad.numpy()) < 1e-4
+
+
+@pytest.mark.parametrize("order", ["nhwc", "cf", "fc"])
+def test_bn_clip_fwd_bwd_vs_oracle(order):
+    ops = _ops()
+    rng = np.random.default_rng(12)
+    B, T, Fq, C = 3, 7, 5, 4
+    x = torch.tensor(rng.standard_normal((B, T, Fq, C)) * 8 + 3, dtype=torch.float32, device="cuda", requires_grad=True)
+    gm = torch.tensor(rng.uniform(0.5, 1.5, C), dtype=torch.float32, device="cuda", requires_grad=True)
+    bt = torch.tensor(rng.standard_normal(C), dtype=torch.float32, device="cuda", requires_grad=True)
+    if order == "nhwc":
+        y = ops.bn_clip_nhwc(x, gm, bt, 1e-3, 20.0)
+    else:
+        y = ops.bn_clip_to_rnn_layout(x, gm, bt, 1e-3, 20.0, order, torch.float32)
+    g = torch.tensor(rng.standard_normal(tuple(y.shape)), dtype=torch.float32, device="cuda")
+    (y * g).sum().backward()
+    xr = x.detach().double().cpu().requires_grad_(True)
+    gr = gm.detach().double().cpu().requires_grad_(True)
+    br = bt.detach().double().cpu().requires_grad_(True)
+    yr = O.relux(O.batch_norm_train(xr, gr, br, 1e-3, 3), 20.0)
+    if order == "cf":
+        yr = yr.permute(1, 0, 3, 2).reshape(T, B, C * Fq)
+    elif order == "fc":
+        yr = yr.permute(1, 0, 2, 3).reshape(T, B, Fq * C)
+    (yr * g.double().cpu()).sum().backward()
+    assert relerr(y.detach().cpu().numpy(), yr.detach().numpy()) < 1e-5
+    assert relerr(x.grad.cpu().numpy(), xr.grad.numpy()) < 1e-3
+    assert relerr(gm.grad.cpu().numpy(), gr.grad.numpy()) < 1e-3
+    assert relerr(bt.grad.cpu().numpy(), br.grad.numpy()) < 1e-3
+
+
+# ----------------------------------------------------------------------------------------- recurrent layers
+def _layer_params(rng, H, I, G=1):
+    mk = lambda *s: torch.tensor(rng.standard_normal(s) * (0.4 / np.sqrt(s[-1])), dtype=torch.float64)
+    lp = {}
+    for d in ("fw", "bw"):
+        lp[d] = {"W": mk(G * H, I) * 3, "U": mk(G * H, H) * 2}
+        if G == 1:
+            lp[d]["B"] = torch.tensor(rng.standard_normal(H) * 0.1)
+        else:
+            lp[d]["BW"] = torch.tensor(rng.standard_normal(G * H) * 0.1)
+            lp[d]["BU"] = torch.tensor(rng.standard_normal(G * H) * 0.1)
+    return lp
+
+
+@pytest.mark.parametrize("T,B,I,H,lens", [(5, 2, 6, 4, [5, 3]), (9, 3, 10, 16, [9, 9, 1]), (17, 4, 24, 40, [17, 2, 10, 16])])
+def test_birnn_layer_fp32_vs_oracle(T, B, I, H, lens):
+    ops = _ops()
+    rng = np.random.default_rng(T * 7 + H)
+    lp = _layer_params(rng, H, I)
+    x64 = torch.tensor(rng.standard_normal((T, B, I)) * 2, requires_grad=True)
+    for v in lp.values():
+        for t in v.values():
+            t.requires_grad_(True)
+    ref = O.rnn_direction(x64, lens, lp["fw"], False) + O.rnn_direction(x64, lens, lp["bw"], True)
+    g = torch.tensor(rng.standard_normal((T, B, H)))
+    (ref * g).sum().backward()
+    dev = "cuda"
+    x = x64.detach().float().to(dev).requires_grad_(True)
+    W = torch.cat([lp["fw"]["W"], lp["bw"]["W"]], 0).detach().float().to(dev).requires_grad_(True)
+    U = torch.stack([lp["fw"]["U"], lp["bw"]["U"]], 0).detach().float().to(dev).requires_grad_(True)
+    Bv = torch.stack([lp["fw"]["B"], lp["bw"]["B"]], 0).detach().float().to(dev).requires_grad_(True)
+    lens_d = torch.tensor(lens, dtype=torch.int32, device=dev)
+    out = ops.birnn_layer(x, W, U, Bv, lens_d, 0b10, False, torch.float32)
+    (out * g.float().to(dev)).sum().backward()
+    assert relerr(out.detach().cpu().numpy(), ref.detach().numpy()) < 1e-5
+    assert relerr(x.grad.cpu().numpy(), x64.grad.numpy()) < 1e-3
+    assert relerr(W.grad.cpu().numpy(), torch.cat([lp["fw"]["W"].grad, lp["bw"]["W"].grad], 0).numpy()) < 1e-3
+    assert relerr(U.grad.cpu().numpy(), torch.stack([lp["fw"]["U"].grad, lp["bw"]["U"].grad], 0).numpy()) < 1e-3
+    assert relerr(Bv.grad.cpu().numpy(), torch.stack([lp["fw"]["B"].grad, lp["bw"]["B"].grad], 0).numpy()) < 1e-3
+    # masking: outputs are exactly zero past each utterance's length
+    o = out.detach().cpu().numpy()
+    for b, n in enumerate(lens):
+        assert np.abs(o[n:, b]).max(initial=0.0) == 0.0
+
+
+@pytest.mark.parametrize("T,B,I,H,lens", [(6, 2, 5, 3, [6, 4]), (11, 3, 12, 16, [11, 5, 1])])
+def test_bigru_layer_fp32_vs_oracle(T, B, I, H, lens):
+    ops = _ops()
+    rng = np.random.default_rng(T * 5 + H)
+    lp = _layer_params(rng, H, I, G=3)
+    x64 = torch.tensor(rng.standard_normal((T, B, I)), requires_grad=True)
+    for v in lp.values():
+        for t in v.values():
+            t.requires_grad_(True)
+    ref = O.rnn_direction(x64, lens, lp["fw"], False, cell="gru") + O.rnn_direction(x64, lens, lp["bw"], True, cell="gru")
+    g = torch.tensor(rng.standard_normal((T, B, H)))
+    (ref * g).sum().backward()
+    dev = "cuda"
+    cat = lambda k: torch.cat([lp["fw"][k], lp["bw"][k]], 0).detach().float().to(dev).requires_grad_(True)
+    stk = lambda k: torch.stack([lp["fw"][k], lp["bw"][k]], 0).detach().float().to(dev).requires_grad_(True)
+    x = x64.detach().float().to(dev).requires_grad_(True)
+    W, U, BW, BU = cat("W"), stk("U"), stk("BW"), stk("BU")
+    out = ops.bigru_layer(x, W, U, BW, BU, torch.tensor(lens, dtype=torch.int32, device=dev), 0b10, torch.float32)
+    (out * g.float().to(dev)).sum().backward()
+    assert relerr(out.detach().cpu().numpy(), ref.detach().numpy()) < 1e-5
+    assert relerr(x.grad.cpu().numpy(), x64.grad.numpy()) < 1e-3
+    assert relerr(W.grad.cpu().numpy(), torch.cat([lp["fw"]["W"].grad, lp["bw"]["W"].grad], 0).numpy()) < 1e-3
+    assert relerr(U.grad.cpu().numpy(), torch.stack([lp["fw"]["U"].grad, lp["bw"]["U"].grad], 0).numpy()) < 1e-3
+    assert relerr(BW.grad.cpu().numpy(), torch.stack([lp["fw"]["BW"].grad, lp["bw"]["BW"].grad], 0).numpy()) < 1e-3
+    assert relerr(BU.grad.cpu().numpy(), torch.stack([lp["fw"]["BU"].grad, lp["bw"]["BU"].grad], 0).numpy()) < 1e-3
+
+
+def test_linear_and_errors():
+    ops = _ops()
+    rng = np.random.default_rng(2)
+    x = torch.tensor(rng.standard_normal((50, 40)), dtype=torch.float32, device="cuda", requires_grad=True)
+    W = torch.tensor(rng.standard_normal((29, 40)), dtype=torch.float32, device="cuda", requires_grad=True)
+    b = torch.tensor(rng.standard_normal(29), dtype=torch.float32, device="cuda", requires_grad=True)
+    y = ops.linear(x, W, b)
+    y.square().sum().backward()
+    xr, Wr, br = [t.detach().double().cpu().requires_grad_(True) for t in (x, W, b)]
+    yr = xr @ Wr.t() + br
+    yr.square().sum().backward()
+    assert relerr(y.detach().cpu().numpy(), yr.detach().numpy()) < 1e-5
+    for a, r in ((x, xr), (W, Wr), (b, br)):
+        assert relerr(a.grad.cpu().numpy(), r.grad.numpy()) < 1e-4
+    with pytest.raises(RuntimeError):
+        ops.relux(torch.zeros(3))            # CPU tensor: no fallback
