@@ -81,16 +81,25 @@ __device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K,
   double* coff = ws.coff + ((size_t)b * 2 + DIR) * ws.NB;
 
   for (int i = tid; i < L; i += nthr) lab[i] = labels[(size_t)b * Lmax + (DIR == 0 ? i : L - 1 - i)];
-  // row log-sum-exp, one warp per row
-  for (int t = warp; t < Tb; t += nwarps) {
+  // row log-sum-exp: one THREAD per row so that every thread has a whole row of independent loads in
+  // flight (a warp-per-row loop serialises one DRAM latency per row); this pass also pulls the
+  // utterance's logits into L2 for the recursion below.
+  for (int t = tid; t < Tb; t += nthr) {
     const float* row = logits + ((size_t)t * B + b) * K;
-    float m = -INFINITY;
-    for (int k = lane; k < K; k += 32) m = fmaxf(m, row[k]);
-    m = warp_max(m);
-    float s = 0.f;
-    for (int k = lane; k < K; k += 32) s += __expf(row[k] - m);
-    s = warp_sum(s);
-    if (lane == 0) lse[t] = m + __logf(s);
+    float m = -INFINITY, s = 0.f;
+    if (K <= 32) {
+      float v[32];
+#pragma unroll
+      for (int k = 0; k < 32; ++k) v[k] = (k < K) ? __ldg(row + k) : -INFINITY;
+#pragma unroll
+      for (int k = 0; k < 32; ++k) m = fmaxf(m, v[k]);
+#pragma unroll
+      for (int k = 0; k < 32; ++k) s += __expf(v[k] - m);
+    } else {
+      for (int k = 0; k < K; ++k) m = fmaxf(m, __ldg(row + k));
+      for (int k = 0; k < K; ++k) s += __expf(__ldg(row + k) - m);
+    }
+    lse[t] = m + __logf(s);
   }
   if (tid < 2) { buf0[tid] = NEGF; buf1[tid] = NEGF; }
   __syncthreads();

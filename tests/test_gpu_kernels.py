@@ -283,3 +283,44 @@ def test_linear_and_errors():
         assert relerr(a.grad.cpu().numpy(), r.grad.numpy()) < 1e-4
     with pytest.raises(RuntimeError):
         ops.relux(torch.zeros(3))            # CPU tensor: no fallback
+
+
+# ----------------------------------------------------------------------------------------- persistent tcgen05 recurrence
+@pytest.mark.parametrize("T,B,I,H,ragged", [(6, 32, 64, 64, False), (9, 32, 128, 256, True), (5, 64, 72, 200, True),
+                                             (4, 32, 256, 1760, False), (24, 32, 64, 800, True)])
+def test_birnn_layer_bf16_persistent_vs_oracle(T, B, I, H, ragged):
+    """bf16 operands / fp32 accumulation against the fp64 oracle run on the SAME bf16-rounded weights:
+    <= 1e-2 of the output scale (north_star: bf16 recurrence <= 1e-2), gradients <= 3e-2."""
+    ops = _ops()
+    from deepspeech_b200._lib import lib
+    assert lib.ds2_rnn_relu_persistent_supported(B, H, 2) == 1
+    rng = np.random.default_rng(T * 13 + H)
+    bf = lambda a: torch.tensor(a, dtype=torch.float32).to(torch.bfloat16).double()
+    lp = {}
+    for d in ("fw", "bw"):
+        lp[d] = {"W": bf(rng.standard_normal((H, I)) * (1.0 / np.sqrt(I))).requires_grad_(True),
+                 "U": bf(rng.standard_normal((H, H)) * (0.7 / np.sqrt(H))).requires_grad_(True),
+                 "B": torch.tensor(rng.standard_normal(H) * 0.1).float().double().requires_grad_(True)}
+    x64 = bf(rng.standard_normal((T, B, I))).requires_grad_(True)
+    lens = [T] * B
+    if ragged:
+        lens = [T] + [int(v) for v in rng.integers(1, T + 1, size=B - 1)]
+    ref = O.rnn_direction(x64, lens, lp["fw"], False) + O.rnn_direction(x64, lens, lp["bw"], True)
+    g = torch.tensor(rng.standard_normal((T, B, H)))
+    (ref * g).sum().backward()
+    dev = "cuda"
+    x = x64.detach().to(torch.bfloat16).to(dev).requires_grad_(True)
+    W = torch.cat([lp["fw"]["W"], lp["bw"]["W"]], 0).detach().float().to(dev).requires_grad_(True)
+    U = torch.stack([lp["fw"]["U"], lp["bw"]["U"]], 0).detach().float().to(dev).requires_grad_(True)
+    Bv = torch.stack([lp["fw"]["B"], lp["bw"]["B"]], 0).detach().float().to(dev).requires_grad_(True)
+    out = ops.birnn_layer(x, W, U, Bv, torch.tensor(lens, dtype=torch.int32, device=dev), 0b10, True, torch.float32)
+    (out * g.float().to(dev)).sum().backward()
+    torch.cuda.synchronize()
+    o = out.detach().cpu().numpy()
+    assert relerr(o, ref.detach().numpy()) < 1e-2
+    for b, n in enumerate(lens):
+        assert np.abs(o[n:, b]).max(initial=0.0) == 0.0
+    assert relerr(x.grad.float().cpu().numpy(), x64.grad.numpy()) < 3e-2
+    assert relerr(W.grad.cpu().numpy(), torch.cat([lp["fw"]["W"].grad, lp["bw"]["W"].grad], 0).numpy()) < 3e-2
+    assert relerr(U.grad.cpu().numpy(), torch.stack([lp["fw"]["U"].grad, lp["bw"]["U"].grad], 0).numpy()) < 3e-2
+    assert relerr(Bv.grad.cpu().numpy(), torch.stack([lp["fw"]["B"].grad, lp["bw"]["B"].grad], 0).numpy()) < 3e-2
