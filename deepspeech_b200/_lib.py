@@ -31,6 +31,9 @@ _SIGS = {
     "ds2_ctc_loss_fwd_bwd": (I, [P, I, I, I, P, I, P, P, P, P, P, P, SZ, P]),
     "ds2_ctc_scale_grad": (I, [P, P, P, I, I, I, P]),
     "ds2_gemm_bf16": (I, [P, L, I, P, L, I, P, I, L, I, I, I, F, F, P, P]),
+    "ds2_gemm_bf16_splitk": (I, [P, L, I, P, L, I, P, L, I, I, I, F, P, I, P]),
+    "ds2_im2col": (I, [P, P, P, P, P, F, I, P, L, I, I, I, I, I, I, I, I, P]),
+    "ds2_col2im": (I, [P, L, P, I, I, I, I, I, I, I, I, P]),
     "ds2_gemm_generic": (I, [P, I, L, L, P, I, L, L, P, I, L, I, I, I, F, F, P, P]),
     "ds2_rnn_relu_fwd": (I, [P, F, P, P, P, P, I, I, I, I, I, I, F, P, SZ, P]),
     "ds2_rnn_relu_bwd": (I, [P, P, P, P, P, I, I, I, I, I, I, F, P, SZ, P]),

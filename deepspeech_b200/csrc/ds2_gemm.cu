@@ -31,6 +31,7 @@ struct GemmParams {
   const float* bias;
   int c_bf16, a_mn, b_mn;
   int num_m_blocks, num_n_blocks;
+  int splits, kb_per_split;   // split-K: partial tiles are red.add'ed into a zero-initialised fp32 C
 };
 
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
@@ -45,7 +46,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 2 * ACC_STAGES);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+  const int mn_tiles = p.num_m_blocks * p.num_n_blocks;
+  const int num_tiles = mn_tiles * p.splits;
   const int num_kb = (p.K + BK - 1) / BK;
 
   if (warp == 0 && lane == 0) {
@@ -68,8 +70,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile % p.num_m_blocks) * BM, n0 = (tile / p.num_m_blocks) * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        const int mn = tile % mn_tiles, split = tile / mn_tiles;
+        const int m0 = (mn % p.num_m_blocks) * BM, n0 = (mn / p.num_m_blocks) * BN;
+        const int kb0 = split * p.kb_per_split, kb1 = min(num_kb, kb0 + p.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar + stage, phase ^ 1, 100 + stage);
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_BYTES;
@@ -100,7 +104,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       mbar_wait(tempty_bar + acc, acc_phase ^ 1, 200 + acc);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * BN;
-      for (int kb = 0; kb < num_kb; ++kb) {
+      const int split = tile / mn_tiles;
+      const int kb0 = split * p.kb_per_split, kb1 = min(num_kb, kb0 + p.kb_per_split);
+      for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(full_bar + stage, phase, 300 + stage);
         tc_fence_after();
         if (lane == 0) {
@@ -114,10 +120,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                                           : umma_smem_desc_sw128(sa + k * 32, 16, 1024);
             const uint64_t bdesc = p.b_mn ? umma_smem_desc_sw128(sb + k * 2048, B_BYTES / 2, 1024)
                                           : umma_smem_desc_sw128(sb + k * 32, 16, 1024);
-            umma_bf16(d_tmem, adesc, bdesc, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            umma_bf16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           umma_commit(empty_bar + stage);                 // frees the smem slot when the MMAs retire
-          if (kb == num_kb - 1) umma_commit(tfull_bar + acc);   // accumulator ready for the epilogue
+          if (kb == kb1 - 1) umma_commit(tfull_bar + acc);   // accumulator ready for the epilogue
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -129,7 +135,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     const int wq = warp & 3;      // TMEM lane quarter this warp may access
     int acc = 0; uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m0 = (tile % p.num_m_blocks) * BM, n0 = (tile / p.num_m_blocks) * BN;
+      const int mn = tile % mn_tiles, split = tile / mn_tiles;
+      const int m0 = (mn % p.num_m_blocks) * BM, n0 = (mn / p.num_m_blocks) * BN;
       mbar_wait(tfull_bar + acc, acc_phase, 400 + acc);
       tc_fence_after();
       const int row = m0 + wq * 32 + lane;
@@ -143,13 +150,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           float v[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = p.alpha * __uint_as_float(r[j]);
-          if (p.bias) {
+          if (p.bias && split == 0) {
 #pragma unroll
             for (int j = 0; j < 32; ++j)
               if (nbase + j < p.N) v[j] += __ldg(p.bias + nbase + j);
           }
           const bool full = nbase + 32 <= p.N;
-          if (p.c_bf16) {
+          if (p.splits > 1) {
+            float* crow = static_cast<float*>(p.C) + (long)row * p.ldc + nbase;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (nbase + j < p.N) atomicAdd(crow + j, v[j]);
+          } else if (p.c_bf16) {
             __nv_bfloat16* crow = static_cast<__nv_bfloat16*>(p.C) + (long)row * p.ldc + nbase;
             if (p.beta != 0.f) {
 #pragma unroll
@@ -241,7 +253,7 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64
 }
 
 int gemm_bf16_launch(const void* A, long lda, int a_mn, const void* B, long ldb, int b_mn, void* C, int c_dtype, long ldc,
-                     int M, int N, int K, float alpha, float beta, const float* bias, cudaStream_t st) {
+                     int M, int N, int K, float alpha, float beta, const float* bias, int splits, cudaStream_t st) {
   DS2_REQUIRE(A && B && C, DS2_ERR_BAD_ARG, "ds2_gemm_bf16: null pointer");
   DS2_REQUIRE(M > 0 && N > 0 && K > 0, DS2_ERR_BAD_SHAPE, "ds2_gemm_bf16: bad shape M=%d N=%d K=%d", M, N, K);
   DS2_REQUIRE(c_dtype == DS2_F32 || c_dtype == DS2_BF16, DS2_ERR_BAD_ARG, "ds2_gemm_bf16: bad c_dtype %d", c_dtype);
@@ -263,7 +275,16 @@ int gemm_bf16_launch(const void* A, long lda, int a_mn, const void* B, long ldb,
   p.c_bf16 = (c_dtype == DS2_BF16); p.a_mn = a_mn; p.b_mn = b_mn;
   p.num_m_blocks = (M + BM - 1) / BM;
   p.num_n_blocks = (N + BN - 1) / BN;
-  const int tiles = p.num_m_blocks * p.num_n_blocks;
+  const int num_kb = (K + BK - 1) / BK;
+  if (splits < 1) splits = 1;
+  if (splits > num_kb) splits = num_kb;
+  p.kb_per_split = (num_kb + splits - 1) / splits;
+  p.splits = (num_kb + p.kb_per_split - 1) / p.kb_per_split;     // no empty split
+  if (p.splits > 1) {
+    DS2_REQUIRE(c_dtype == DS2_F32 && beta == 0.f, DS2_ERR_BAD_ARG, "ds2_gemm_bf16: split-K needs an fp32 C and beta = 0");
+    DS2_CUDA(cudaMemset2DAsync(C, ldc * sizeof(float), 0, (size_t)N * sizeof(float), M, st));
+  }
+  const int tiles = p.num_m_blocks * p.num_n_blocks * p.splits;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   gemm_tcgen05_kernel<<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(ta, tb, p);
   DS2_LAUNCH_CHECK("gemm_tcgen05_kernel");
@@ -276,6 +297,16 @@ int gemm_bf16_launch(const void* A, long lda, int a_mn, const void* B, long ldb,
 extern "C" int ds2_gemm_bf16(const void* A, long lda, int a_mn_major, const void* B, long ldb, int b_mn_major, void* C,
                              int c_dtype, long ldc, int M, int N, int K, float alpha, float beta, const float* bias,
                              void* stream) {
-  return ds2::gemm_bf16_launch(A, lda, a_mn_major, B, ldb, b_mn_major, C, c_dtype, ldc, M, N, K, alpha, beta, bias,
+  return ds2::gemm_bf16_launch(A, lda, a_mn_major, B, ldb, b_mn_major, C, c_dtype, ldc, M, N, K, alpha, beta, bias, 1,
+                               static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ds2_gemm_bf16_splitk(const void* A, long lda, int a_mn_major, const void* B, long ldb, int b_mn_major, float* C,
+                                    long ldc, int M, int N, int K, float alpha, const float* bias, int splits, void* stream) {
+  if (splits <= 0) {   // auto: enough K-splits to put a tile on every SM
+    const int tiles = ((M + ds2::BM - 1) / ds2::BM) * ((N + ds2::BN - 1) / ds2::BN);
+    splits = (ds2::num_sms() + tiles - 1) / tiles;
+  }
+  return ds2::gemm_bf16_launch(A, lda, a_mn_major, B, ldb, b_mn_major, C, DS2_F32, ldc, M, N, K, alpha, 0.f, bias, splits,
                                static_cast<cudaStream_t>(stream));
 }

@@ -442,7 +442,7 @@ extern "C" int ds2_conv2d_wgrad(const void* x, int x_dtype, const float* dy, flo
 }
 
 static int act_map(ActMap* m, int T, int F, int C, long sb, long st, long sf, long sc) {
-  DS2_REQUIRE(C > 0 && C <= 256 && 256 % C == 0, DS2_ERR_BAD_SHAPE, "ds2_bn: channel count %d must divide 256", C);
+  DS2_REQUIRE(C > 0 && C <= 256, DS2_ERR_BAD_SHAPE, "ds2_bn: channel count %d must be in [1,256]", C);
   m->T = T; m->F = F; m->C = C; m->sb = sb; m->st = st; m->sf = sf; m->sc = sc;
   return DS2_OK;
 }
@@ -450,12 +450,12 @@ static int act_map(ActMap* m, int T, int F, int C, long sb, long st, long sf, lo
 extern "C" int ds2_bn_stats(const float* x, long R, int C, float eps, double* sums_scratch, float* mean, float* rstd, void* stream) {
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   DS2_REQUIRE(x && sums_scratch && mean && rstd && R > 0, DS2_ERR_BAD_ARG, "ds2_bn_stats: bad argument");
-  DS2_REQUIRE(C > 0 && C <= 256 && 256 % C == 0, DS2_ERR_BAD_SHAPE, "ds2_bn: channel count %d must divide 256", C);
+  DS2_REQUIRE(C > 0 && C <= 256, DS2_ERR_BAD_SHAPE, "ds2_bn: channel count %d must be in [1,256]", C);
   DS2_CUDA(cudaMemsetAsync(sums_scratch, 0, sizeof(double) * 2 * C, cs));
   long rows_per = 256 / C * 16;
   int grid = (int)((R + rows_per - 1) / rows_per);
   if (grid > num_sms() * 8) grid = num_sms() * 8;
-  bn_stats_kernel<<<grid, 256, 0, cs>>>(x, R, C, sums_scratch);
+  bn_stats_kernel<<<grid, (256 / C) * C, 0, cs>>>(x, R, C, sums_scratch);
   DS2_LAUNCH_CHECK("bn_stats_kernel");
   bn_finalize_kernel<<<1, 256, 0, cs>>>(sums_scratch, (double)R, eps, C, mean, rstd);
   DS2_LAUNCH_CHECK("bn_finalize_kernel");
@@ -495,12 +495,12 @@ extern "C" int ds2_bn_clip_bwd(const float* x, int B, int T, int F, int C, const
   if (grid > num_sms() * 8) grid = num_sms() * 8;
   if (dout_dtype == DS2_F32) {
     const float* d = static_cast<const float*>(dout);
-    bn_clip_bwd_reduce_kernel<float><<<grid, 256, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, d, m, sums_scratch);
+    bn_clip_bwd_reduce_kernel<float><<<grid, (256 / C) * C, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, d, m, sums_scratch);
     DS2_LAUNCH_CHECK("bn_clip_bwd_reduce_kernel");
     bn_clip_bwd_apply_kernel<float><<<ew_grid(R * C), 256, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, d, m, sums_scratch, dx, dgamma, dbeta);
   } else {
     const __nv_bfloat16* d = static_cast<const __nv_bfloat16*>(dout);
-    bn_clip_bwd_reduce_kernel<__nv_bfloat16><<<grid, 256, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, d, m, sums_scratch);
+    bn_clip_bwd_reduce_kernel<__nv_bfloat16><<<grid, (256 / C) * C, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, d, m, sums_scratch);
     DS2_LAUNCH_CHECK("bn_clip_bwd_reduce_kernel");
     bn_clip_bwd_apply_kernel<__nv_bfloat16><<<ew_grid(R * C), 256, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, d, m, sums_scratch, dx, dgamma, dbeta);
   }

@@ -97,10 +97,15 @@ class DeepSpeech2(torch.nn.Module):
         """feats [B,T,161] f32 -> rnn input [T2,B,75*nf] (bf16 when use_bf16)."""
         B, T, Fq = feats.shape
         x = feats.contiguous().view(B, T, Fq, 1)
-        y1 = ops.conv2d_nhwc(x, self.conv1_w, self.conv1_b, 2, 2)
-        a1 = ops.bn_clip_nhwc(y1, self.conv1_gamma, self.conv1_beta, self.eps, ops.RELU_CAP)
-        y2 = ops.conv2d_nhwc(a1, self.conv2_w, self.conv2_b, 2, 1)
         odt = torch.bfloat16 if self.use_bf16 else torch.float32
+        if self.use_bf16 and self.nf % 8 == 0:
+            # tensor-core route: patches gathered in bf16 (BN1 + clip fused into conv2's gather), tcgen05 GEMMs
+            y1 = ops.conv2d_gemm(x, self.conv1_w, self.conv1_b, 2, 2)
+            y2 = ops.conv2d_gemm(y1, self.conv2_w, self.conv2_b, 2, 1, self.conv1_gamma, self.conv1_beta, self.eps, ops.RELU_CAP)
+        else:
+            y1 = ops.conv2d_nhwc(x, self.conv1_w, self.conv1_b, 2, 2)
+            a1 = ops.bn_clip_nhwc(y1, self.conv1_gamma, self.conv1_beta, self.eps, ops.RELU_CAP)
+            y2 = ops.conv2d_nhwc(a1, self.conv2_w, self.conv2_b, 2, 1)
         return ops.bn_clip_to_rnn_layout(y2, self.conv2_gamma, self.conv2_beta, self.eps, ops.RELU_CAP,
                                          "cf" if self.layout == "NCHW" else "fc", odt)
 

@@ -233,6 +233,78 @@ def conv2d_nhwc(x, w, bias, st, sf):
     return _Conv2dFn.apply(x.contiguous(), w.contiguous(), bias, st, sf)
 
 
+class _ConvGemmFn(torch.autograd.Function):
+    """y = conv(f(x), w) + bias on the tensor cores, f = identity or clip(BN_batch(x)) of the previous
+    layer applied while the patch matrix is gathered (ds2_im2col -> ds2_gemm_bf16).  x fp32 channel-last
+    [B,Ti,Fi,Ci]; w HWIO fp32; y fp32 [B,To,Fo,Co].  Backward: dW = P^T dy (split-K GEMM), db = colsum,
+    dx through dP = dy W^T (GEMM) -> ds2_col2im -> BN/clip backward."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias, st, sf, gamma, beta, eps, cap):
+        B, Ti, Fi, Ci = x.shape
+        KT, KF, _, Co = w.shape
+        To, Fo = (Ti - KT) // st + 1, (Fi - KF) // sf + 1
+        if To <= 0 or Fo <= 0:
+            raise ValueError("conv2d: input %dx%d smaller than the %dx%d filter" % (Ti, Fi, KT, KF))
+        K = KT * KF * Ci
+        Kp = (K + 7) // 8 * 8
+        M = B * To * Fo
+        dev = x.device
+        has_bn = gamma is not None
+        mean = rstd = None
+        if has_bn:
+            mean, rstd = bn_stats(x, Ci, eps)
+        P = torch.empty((M, Kp), dtype=torch.bfloat16, device=dev)
+        check(lib.ds2_im2col(_p(x), _p(mean), _p(rstd), _p(gamma), _p(beta), float(cap or 0.0), int(cap is not None), _p(P), Kp,
+                             B, Ti, Fi, Ci, KT, KF, st, sf, _stream()), "ds2_im2col")
+        wb = torch.zeros((Kp, Co), dtype=torch.bfloat16, device=dev) if Kp != K else torch.empty((Kp, Co), dtype=torch.bfloat16, device=dev)
+        check(lib.ds2_cast(_p(w), DS2_F32, _p(wb), DS2_BF16, K * Co, _stream()), "ds2_cast")
+        y = gemm_nt(P, wb, b_mn=True, M=M, N=Co, K=Kp, bias=bias)                       # [M,Co] fp32
+        ctx.save_for_backward(x, gamma, beta, mean, rstd, P, wb)
+        ctx.geom = (B, Ti, Fi, Ci, KT, KF, st, sf)
+        ctx.misc = (Co, K, Kp, M, eps, cap, has_bn, bias is not None, tuple(w.shape))
+        return y.view(B, To, Fo, Co)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, gamma, beta, mean, rstd, P, wb = ctx.saved_tensors
+        B, Ti, Fi, Ci, KT, KF, st, sf = ctx.geom
+        Co, K, Kp, M, eps, cap, has_bn, has_bias, wshape = ctx.misc
+        dev = x.device
+        dy2 = dy.contiguous().view(M, Co)
+        dyb = cast(dy2, torch.bfloat16)
+        dwp = torch.empty((Kp, Co), dtype=torch.float32, device=dev)
+        check(lib.ds2_gemm_bf16_splitk(_p(P), Kp, 1, _p(dyb), Co, 1, _p(dwp), Co, Kp, Co, M, 1.0, None, 0, _stream()),
+              "ds2_gemm_bf16_splitk")
+        dw = dwp[:K].view(wshape)
+        db = colsum(dy2, M, Co, Co) if has_bias else None
+        dx = dgamma = dbeta = None
+        if ctx.needs_input_grad[0]:
+            dP = gemm_nt(dyb, wb, M=M, N=Kp, K=Co, out_dtype=torch.bfloat16)            # [M,Kp] = dy . W^T
+            da = torch.empty(x.shape, dtype=torch.float32, device=dev)
+            check(lib.ds2_col2im(_p(dP), Kp, _p(da), B, Ti, Fi, Ci, KT, KF, st, sf, _stream()), "ds2_col2im")
+            del dP
+            if has_bn:
+                dx = torch.empty_like(x)
+                dgamma = torch.empty_like(gamma)
+                dbeta = torch.empty_like(beta)
+                omap = (Ti * Fi * Ci, Fi * Ci, Ci, 1)
+                check(lib.ds2_bn_clip_bwd(_p(x), B, Ti, Fi, Ci, _p(mean), _p(rstd), _p(gamma), _p(beta), float(cap or 0.0),
+                                          int(cap is not None), _p(da), DS2_F32, *omap, _p(_bn_scratch(dev)), _p(dx), _p(dgamma),
+                                          _p(dbeta), _stream()), "ds2_bn_clip_bwd")
+            else:
+                dx = da
+        return dx, dw, db, None, None, dgamma, dbeta, None, None
+
+
+def conv2d_gemm(x, w, bias, st, sf, gamma=None, beta=None, eps=1e-3, cap=None):
+    """Tensor-core convolution of f(x): f = clip(BN(x)) when gamma/beta are given, identity otherwise."""
+    _need_cuda(x, w)
+    if x.dtype != torch.float32:
+        raise ValueError("conv2d_gemm: fp32 input expected")
+    return _ConvGemmFn.apply(x.contiguous(), w.contiguous(), bias, st, sf, gamma, beta, eps, cap)
+
+
 # ------------------------------------------------------------------------------------ recurrent stack
 def rnn_path_dtype(B: int, H: int, ND: int, want_bf16: bool):
     """bf16 (persistent tcgen05 kernel) when requested and the shape is taken, else fp32."""

@@ -65,6 +65,10 @@ int ds2_ctc_scale_grad(const float* grad, const float* dloss, float* out, int T,
  *   C[m,n] = alpha * sum_k A[m*sam + k*sak] * B[n*sbn + k*sbk] + bias[n] + beta*C[m*ldc+n]. */
 int ds2_gemm_bf16(const void* A, long lda, int a_mn_major, const void* B, long ldb, int b_mn_major, void* C, int c_dtype,
                   long ldc, int M, int N, int K, float alpha, float beta, const float* bias, void* stream);
+/* split-K variant for short-and-wide products (weight gradients: K = T*B or B*To*Fo rows): C is zeroed,
+ * then every K-split red.add's its partial tile.  fp32 C, beta = 0.  splits <= 0: chosen to fill the SMs. */
+int ds2_gemm_bf16_splitk(const void* A, long lda, int a_mn_major, const void* B, long ldb, int b_mn_major, float* C, long ldc,
+                         int M, int N, int K, float alpha, const float* bias, int splits, void* stream);
 int ds2_gemm_generic(const void* A, int a_dtype, long sam, long sak, const void* B, int b_dtype, long sbn, long sbk, void* C,
                      int c_dtype, long ldc, int M, int N, int K, float alpha, float beta, const float* bias, void* stream);
 
@@ -107,9 +111,19 @@ int ds2_conv2d_dgrad(const float* dy, const float* w, float* dx, int B, int Ti, 
 int ds2_conv2d_wgrad(const void* x, int x_dtype, const float* dy, float* dw, float* dbias, int B, int Ti, int Fi, int Ci,
                      int Co, int KT, int KF, int st, int sf, void* stream);
 
+/* Tensor-core route for the same convolutions: patch matrix P[M = B*To*Fo, ldp] (bf16, k = (kt*KF+kf)*Ci+ci,
+ * zero padded to ldp % 8 == 0) gathered from the fp32 channel-last input, optionally applying the previous
+ * layer's batch-norm + clipped ReLU on the fly (mean == NULL: plain gather).  Then y = P.W via ds2_gemm_bf16,
+ * dW = P^T.dy via ds2_gemm_bf16_splitk, dP = dy.W^T via ds2_gemm_bf16 and ds2_col2im sums dP back onto the
+ * input grid (dgrad).  ds2_col2im needs Ci % 8 == 0. */
+int ds2_im2col(const float* x, const float* mean, const float* rstd, const float* gamma, const float* beta, float cap,
+               int clip, void* P, long ldp, int B, int Ti, int Fi, int Ci, int KT, int KF, int st, int sf, void* stream);
+int ds2_col2im(const void* dP, long ldp, float* dx, int B, int Ti, int Fi, int Ci, int KT, int KF, int st, int sf,
+               void* stream);
+
 /* batch_norm2 / batch_norm (src/custom_ops.py:107-160, :163-181; training mode, biased batch
  * variance over all rows of the channel-last [R,C] tensor) fused with relux(.., capping)
- * (src/custom_ops.py:99-104).  C must divide 256.  sums_scratch: 2*C doubles.
+ * (src/custom_ops.py:99-104).  C <= 256.  sums_scratch: 2*C doubles.
  * The activation-side tensor (out / dout) is addressed as b*sb + t*st + f*sf + c*sc so it can be
  * written straight into the RNN layout [T,B,C*F] (src/deepSpeech_NCHW.py:166-168) or [T,B,F*C]
  * (src/deepSpeech.py:162-164). */
