@@ -13,6 +13,8 @@
 //     per-direction grid barrier (release/acquire counter in global memory).
 // The backward kernel is the same machine with A = U^T (pre-transposed by the caller-side wrapper),
 // B operand = dz_{t+1}, and the epilogue dz_t = [0 < h_t < cap] * (dout_t + U^T dz_{t+1}).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace ds2 {
@@ -27,6 +29,7 @@ struct RnnPersistParams {
   const __nv_bfloat16* hs_in;   // bwd: hs [ND,T,B,H] (activation mask)
   __nv_bfloat16* out;      // fwd: hs [ND,T,B,H] ; bwd: dz [T,B,ND*H]
   unsigned int* ctr;       // [ND] step counters, 32 uints apart
+  long long* prof;         // optional per-step clock64 stamps of CTA (0,0,0) (DS2_RNN_PROF=1), 8 per step
   int T, B, H, ND, reverse_mask;
   int tiles_m, ksl, nbox;  // M tiles per direction, K-slice length (multiple of 64), boxes per slice
   float scale, cap;
@@ -120,12 +123,14 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
           SpinGuard g;
           while (ld_acquire_u32(ctr) < need) g.check(20);
         }
+        if (p.prof && blockIdx.x + blockIdx.y + blockIdx.z == 0 && step < 1024) p.prof[step * 8 + 0] = dev_clock();
         asm volatile("fence.proxy.async;" ::: "memory");      // generic-proxy acquire -> async-proxy (TMA) reads
         tc_fence_after();
         mbar_arrive_expect_tx(h_bar, p.nbox * box_b_bytes);
         for (int i = 0; i < p.nbox; ++i)
           tma_load_2d(sB + i * box_b_bytes, tm_b, h_bar, rank * p.ksl + i * 64, tsrc * Bn);
         mbar_wait(h_bar, ph, 30);
+        if (p.prof && blockIdx.x + blockIdx.y + blockIdx.z == 0 && step < 1024) p.prof[step * 8 + 1] = dev_clock();
         tc_fence_after();
         const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
         for (int i = 0; i < p.nbox; ++i) {
@@ -137,6 +142,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
           }
         }
         umma_commit(mma_bar);
+        if (p.prof && blockIdx.x + blockIdx.y + blockIdx.z == 0 && step < 1024) p.prof[step * 8 + 2] = dev_clock();
       }
       __syncwarp();
       ph ^= 1;
@@ -182,6 +188,8 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
         for (int i = 0; i < 8; ++i) acc[g][i] = 0.f;
       if (step > 0) {
         mbar_wait(mma_bar, ph, 40);
+        const bool pr = p.prof && et == 0 && blockIdx.x + blockIdx.y + blockIdx.z == 0 && step < 1024;
+        if (pr) p.prof[step * 8 + 3] = dev_clock();
         ph ^= 1;
         tc_fence_after();
         // scatter this warp's 32 rows x B partial sums to the CTA that finishes those rows (rank q)
@@ -195,8 +203,10 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
             st_cluster_f32(dst + ((rank * Bn + g * 32 + bb) * 32 + lane) * 4, __uint_as_float(r[bb]));
         }
         tc_fence_before();
+        if (pr) p.prof[step * 8 + 4] = dev_clock();
         cluster_arrive();
         cluster_wait();
+        if (pr) p.prof[step * 8 + 5] = dev_clock();
         // reduce the KS partial slabs for this thread's (b, 8 rows)
         for (int g = 0; g < nb; ++g) {
           const int b = (et >> 2) + 32 * g;
@@ -239,9 +249,12 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
         }
       }
       // publish: all 128 epilogue threads' stores -> one release increment of the direction counter
-      __threadfence();
+      const bool pr2 = p.prof && et == 0 && blockIdx.x + blockIdx.y + blockIdx.z == 0 && step < 1024;
+      if (pr2) p.prof[step * 8 + 6] = dev_clock();
+      // CTA barrier orders the 128 threads' h_t stores before thread 0's gpu-scope release (cumulativity)
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (et == 0) red_release_add(ctr, 1u);
+      if (pr2) p.prof[step * 8 + 7] = dev_clock();
     }
   }
   // no CTA may exit while a peer can still write into its shared memory
@@ -277,7 +290,7 @@ int rnn_persist_supported(int B, int H, int ND) { return persist_geometry(B, H, 
 size_t rnn_persist_workspace_bytes(int T, int B, int H, int ND) {
   (void)T; (void)B;
   // 1 KB of step counters (one 128-byte line per direction) + room for U^T (bf16) used by the backward
-  return 1024 + (size_t)ND * H * H * 2;
+  return 1024 + 65536 + (size_t)ND * H * H * 2;
 }
 
 template <bool BWD>
@@ -302,7 +315,7 @@ static int persist_launch(const CUtensorMap& ta, const CUtensorMap& tb0, const C
   attrs[1].id = cudaLaunchAttributeCooperative;       // all CTAs co-resident (they spin on each other)
   attrs[1].val.cooperative = 1;
   cfg.attrs = attrs;
-  cfg.numAttrs = 2;
+  cfg.numAttrs = getenv("DS2_RNN_NO_COOP") ? 1 : 2;   // profilers cannot replay cooperative launches
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb0, tb1, p);
   if (e != cudaSuccess) {
     // some driver versions reject cooperative + cluster launches: the grid (<= 128 CTAs, 1 per SM)
@@ -321,7 +334,7 @@ int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const floa
   RnnPersistParams p = {};
   size_t smem;
   DS2_REQUIRE(persist_geometry(B, H, ND, &p.tiles_m, &p.ksl, &p.nbox, &smem), DS2_ERR_UNSUPPORTED, "rnn persist: unsupported shape");
-  DS2_REQUIRE(ws && ws_bytes >= 1024, DS2_ERR_WORKSPACE, "ds2_rnn_relu_fwd: workspace of %d bytes required", 1024);
+  DS2_REQUIRE(ws && ws_bytes >= 1024 + 65536, DS2_ERR_WORKSPACE, "ds2_rnn_relu_fwd: workspace of %d bytes required", 1024 + 65536);
   DS2_CUDA(cudaMemsetAsync(ws, 0, 1024, st));
   CUtensorMap ta, tb0, tb1;
   int rc = make_tmap_2d_bf16(&ta, u, H, (uint64_t)ND * H, H, 64, 128);
@@ -333,6 +346,7 @@ int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const floa
   if (rc) return rc;
   p.add_in = wx; p.bias = bias; p.lens = lens; p.hs_in = nullptr; p.out = static_cast<__nv_bfloat16*>(hs);
   p.ctr = static_cast<unsigned int*>(ws);
+  p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(static_cast<char*>(ws) + 1024) : nullptr;
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = scale; p.cap = cap;
   return persist_launch<false>(ta, tb0, tb1, p, smem, st);
 }
@@ -347,7 +361,7 @@ int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, cons
   const size_t need = rnn_persist_workspace_bytes(T, B, H, ND);
   DS2_REQUIRE(ws && ws_bytes >= need, DS2_ERR_WORKSPACE, "ds2_rnn_relu_bwd: workspace of %zu bytes required", need);
   DS2_CUDA(cudaMemsetAsync(ws, 0, 1024, st));
-  __nv_bfloat16* ut = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + 1024);
+  __nv_bfloat16* ut = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + 1024 + 65536);
   int rc;
   for (int d = 0; d < ND; ++d) {
     rc = ds2_transpose(static_cast<const __nv_bfloat16*>(u) + (size_t)d * H * H, DS2_BF16, H, H, H, ut + (size_t)d * H * H, DS2_BF16, H, st);
@@ -364,6 +378,7 @@ int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, cons
   p.add_in = dout; p.bias = nullptr; p.lens = lens; p.hs_in = static_cast<const __nv_bfloat16*>(hs);
   p.out = static_cast<__nv_bfloat16*>(dz);
   p.ctr = static_cast<unsigned int*>(ws);
+  p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(static_cast<char*>(ws) + 1024) : nullptr;
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = 1.f; p.cap = cap;
   return persist_launch<true>(ta, tb0, tb1, p, smem, st);
 }

@@ -80,7 +80,7 @@ def seq_batch_norm(x, scope=None, is_train=True):
     the variable list."""
     D = x.shape[-1]
     for name, val in (("beta", 0.0), ("gamma", 1.0), ("moving_mean", 0.0), ("moving_variance", 1.0)):
-        _get_variable("sbn", name, (D,), val, False, x.device)
+        _get_variable("sbn/%d" % D, name, (D,), val, False, x.device)
     return _ScaleFn.apply(x, ops.SBN_SCALE)
 
 
