@@ -29,6 +29,8 @@ _SIGS = {
     "ds2_launch_count": (c_longlong, []),
     "ds2_ctc_workspace_bytes": (SZ, [I, I, I, I]),
     "ds2_ctc_loss_fwd_bwd": (I, [P, I, I, I, P, I, P, P, P, P, P, P, SZ, P]),
+    "ds2_ctc_noalloc_max_bytes": (SZ, []),
+    "ds2_ctc_loss_fwd_bwd_noalloc": (I, [P, I, I, I, P, I, P, P, P, P, P, P]),
     "ds2_ctc_scale_grad": (I, [P, P, P, I, I, I, P]),
     "ds2_gemm_bf16": (I, [P, L, I, P, L, I, P, I, L, I, I, I, F, F, P, P]),
     "ds2_gemm_bf16_splitk": (I, [P, L, I, P, L, I, P, L, I, I, I, F, P, I, P]),

@@ -373,3 +373,61 @@ extern "C" int ds2_ctc_loss_fwd_bwd(const float* logits, int T, int B, int K, co
   return ctc_launch(logits, T, B, K, labels, Lmax, label_lens, seq_lens, dloss, loss, grad, workspace, workspace_bytes,
                     static_cast<cudaStream_t>(stream));
 }
+
+// ------------------------------------------------------------------ allocation-free variant
+// Some callers cannot give this library a scratch buffer because they cannot allocate one at the point of the
+// call: a host framework that has handed the whole of HBM to its own arena (cudaMalloc then has nothing left
+// to return), or a latency-critical step loop in which cudaMalloc/cudaFree would stall the device.  For them
+// the alpha/beta tables live in a fixed array that is part of the loaded module: every GPU that loads the
+// library carries these DS2_CTC_NOALLOC_MAX_BYTES until the process exits, used or not.
+#include <mutex>
+
+#define DS2_CTC_NOALLOC_MAX_BYTES (64ull << 20)
+static __device__ __align__(256) unsigned char g_ctc_noalloc_scratch[DS2_CTC_NOALLOC_MAX_BYTES];
+
+// The array's name is only a handle on the host side; the address kernels can use is fetched once per device,
+// with that device current, and remembered.
+static int ctc_noalloc_scratch(void** out) {
+  static std::mutex mu;
+  static void* dev_ptr[64] = {};
+  int dev = -1;
+  DS2_CUDA(cudaGetDevice(&dev));
+  DS2_REQUIRE(dev >= 0 && dev < 64, DS2_ERR_CUDA, "ds2_ctc_loss_fwd_bwd_noalloc: unexpected device ordinal %d", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!dev_ptr[dev]) {
+    void* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_ctc_noalloc_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_ctc_noalloc_scratch)");
+    DS2_REQUIRE(ptr != nullptr, DS2_ERR_CUDA, "ds2_ctc_loss_fwd_bwd_noalloc: no device address for the built-in scratch");
+    dev_ptr[dev] = ptr;
+  }
+  *out = dev_ptr[dev];
+  return DS2_OK;
+}
+
+extern "C" size_t ds2_ctc_noalloc_max_bytes(void) { return (size_t)DS2_CTC_NOALLOC_MAX_BYTES; }
+
+// Same computation and same kernels as ds2_ctc_loss_fwd_bwd; only the home of the scratch differs.
+//  * The first call on each device looks up the scratch address (no allocation, but a runtime query): make that
+//    first call before any stream capture is begun on that device.
+//  * Problems whose tables do not fit are refused (DS2_ERR_WORKSPACE, message names both sizes); nothing is
+//    launched in that case.  ds2_ctc_workspace_bytes(T,B,K,Lmax) <= ds2_ctc_noalloc_max_bytes() is the test.
+//  * All calls on a device share the one array and it keeps whatever the previous call left there.  Nothing in
+//    it has to start at zero - every cell a call reads it has written first - so no clearing is done; but two
+//    calls whose kernels overlap on the GPU (different streams, no dependency) overwrite each other's tables.
+extern "C" int ds2_ctc_loss_fwd_bwd_noalloc(const float* logits, int T, int B, int K, const int* labels, int Lmax,
+                                            const int* label_lens, const int* seq_lens, const float* dloss, float* loss,
+                                            float* grad, void* stream) {
+  DS2_REQUIRE(T > 0 && B > 0 && K > 1 && Lmax >= 0, DS2_ERR_BAD_SHAPE, "ds2_ctc_loss_fwd_bwd_noalloc: bad shape T=%d B=%d K=%d Lmax=%d",
+              T, B, K, Lmax);
+  const size_t need = ctc_ws_layout(T, B, K, Lmax, nullptr, nullptr);
+  DS2_REQUIRE(need <= (size_t)DS2_CTC_NOALLOC_MAX_BYTES, DS2_ERR_WORKSPACE,
+              "ds2_ctc_loss_fwd_bwd_noalloc: T=%d B=%d Lmax=%d needs %zu bytes of scratch, the built-in array holds %zu; "
+              "use ds2_ctc_loss_fwd_bwd with a caller-provided workspace",
+              T, B, Lmax, need, (size_t)DS2_CTC_NOALLOC_MAX_BYTES);
+  void* scratch = nullptr;
+  int rc = ctc_noalloc_scratch(&scratch);
+  if (rc) return rc;
+  return ctc_launch(logits, T, B, K, labels, Lmax, label_lens, seq_lens, dloss, loss, grad, scratch,
+                    (size_t)DS2_CTC_NOALLOC_MAX_BYTES, static_cast<cudaStream_t>(stream));
+}

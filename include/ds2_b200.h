@@ -50,6 +50,23 @@ size_t ds2_ctc_workspace_bytes(int T, int B, int K, int Lmax);
 int ds2_ctc_loss_fwd_bwd(const float* logits, int T, int B, int K, const int* labels, int Lmax, const int* label_lens,
                          const int* seq_lens, const float* dloss, float* loss, float* grad, void* workspace,
                          size_t workspace_bytes, void* stream);
+/* Allocation-free form of ds2_ctc_loss_fwd_bwd.  It has NO counterpart in the reference: it exists for
+ * callers of this library that cannot obtain scratch memory at the point of the call - a host framework that
+ * has handed all of HBM to its own arena so that cudaMalloc has nothing left to give, or a step loop that
+ * cannot afford the device stall of cudaMalloc/cudaFree.  Same arguments minus the workspace; the alpha/beta
+ * tables live in a fixed array inside the library (ds2_ctc_noalloc_max_bytes() = 64 MiB, resident on every GPU
+ * that loads the library until the process exits).  Limits and rules:
+ *   - refused with DS2_ERR_WORKSPACE when ds2_ctc_workspace_bytes(T,B,K,Lmax) exceeds that maximum
+ *     (the reference's largest dummy bucket at B=32 - T2=366, 209 labels - needs 39.4 MB and fits);
+ *   - the first call on each device resolves the array's device address; make it before starting any
+ *     stream capture on that device;
+ *   - the entry point itself calls no cudaMalloc/cudaFree or any allocating routine;
+ *   - all calls share the array and it keeps the previous call's contents; each call overwrites every cell
+ *     it later reads, so nothing is cleared, but calls that overlap on the GPU (two streams) race on it. */
+size_t ds2_ctc_noalloc_max_bytes(void);
+int ds2_ctc_loss_fwd_bwd_noalloc(const float* logits, int T, int B, int K, const int* labels, int Lmax,
+                                 const int* label_lens, const int* seq_lens, const float* dloss, float* loss, float* grad,
+                                 void* stream);
 /* out[t,b,k] = grad[t,b,k] * dloss[b]: applies the upstream d/dloss_b (e.g. 1/B of reduce_mean,
  * src/deepSpeech_NCHW.py:226) to a gradient computed with dloss = NULL. */
 int ds2_ctc_scale_grad(const float* grad, const float* dloss, float* out, int T, int B, int K, void* stream);
