@@ -1,0 +1,464 @@
+// Persistent, weights-resident recurrent kernel (clipped-ReLU RNN), forward and backward.
+//
+// Replaces the tf.while_loop of tf.nn.bidirectional_dynamic_rnn around CustomRNNCell2
+// (src/custom_ops.py:48-72, :91-93): per timestep  h_t = clip(relu(s*Wx_t + U h_{t-1} + b)).
+// The per-step product U.h is a [H x H] x [H x B] contraction on the tensor cores:
+//   * the H output units are tiled by 128 (tcgen05 M=128), the batch is the MMA N dimension;
+//   * the reduction dimension is split over a thread-block cluster of 4 CTAs; each CTA loads its
+//     [128 x H/4] bf16 slice of U ONCE (TMA -> shared memory -> tcgen05.cp -> TMEM) and keeps it resident in
+//     tensor memory as the MMA's A operand for all T steps (a shared-memory A operand caps the MMA at the
+//     ~64 B/clk operand read: 72 clk per K=16 step instead of 16);
+//   * the batch is cut into independent 16-utterance chains ("instances") that share the resident U: each
+//     instance has its own control warp, 4 epilogue warps, barriers, accumulator columns and step counter,
+//     so one chain's grid-barrier / TMA latency is covered by the other chains' work;
+//   * each step of an instance: acquire the step counter -> TMA its K-slice of h_{t-1} (per 64-column box,
+//     MMAs issue as boxes land) -> tcgen05.mma into TMEM -> tcgen05.ld -> partial sums sent through distributed
+//     shared memory to the CTA that finishes those 32 rows (remote mbarrier arrive, no cluster-wide barrier)
+//     -> epilogue (add s*Wx_t + b, clip, length mask) -> bf16 h_t to global -> release-increment of the counter;
+//   * both directions run concurrently as independent groups of CTAs of the same launch.
+// The backward kernel is the same machine with A = U^T, B operand = dz_{t+1}, and the epilogue
+// dz_t = [0 < h_t < cap] * (dout_t + U^T dz_{t+1}).
+#include <stdlib.h>
+
+#include "common.cuh"
+
+namespace ds2 {
+
+static constexpr int KS = 4;            // cluster size = K split
+static constexpr int BP = 16;           // utterances per instance (MMA N)
+static constexpr int INST_THREADS = 160;  // per instance: 1 control warp + 4 epilogue warps
+static constexpr int MAX_NI = 4;
+static constexpr int MAX_NBOX = 9;      // K-slice <= 576 columns
+
+struct RnnPersistParams {
+  const float* add_in;     // fwd: wx [T,B,ND*H] ; bwd: dout [T,B,H]
+  const float* bias;       // fwd: [ND,H]
+  const int* lens;         // [B]
+  const __nv_bfloat16* hs_in;   // bwd: hs [ND,T,B,H] (activation mask)
+  __nv_bfloat16* out;      // fwd: hs [ND,T,B,H] ; bwd: dz [T,B,ND*H]
+  unsigned int* ctr;       // [ND][NI] step counters, 32 uints apart
+  long long* prof;         // optional per-step clock64 stamps of CTA (0,0,0) instance 0 (DS2_RNN_PROF=1), 8 per step
+  int T, B, H, ND, reverse_mask;
+  int NI;                  // instances = B / BP
+  int tiles_m, ksl, nbox;  // M tiles per direction, K-slice length (multiple of 64), boxes per slice
+  int a_in_tmem;
+  float scale, cap;
+};
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+__device__ __forceinline__ uint32_t map_to_rank(uint32_t local_smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_v4(uint32_t addr, float a, float b, float c, float d) {
+  asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void mbar_remote_arrive_release(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_acq_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_add(unsigned int* p, unsigned int v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// smem (matrix descriptor, same format as the MMA operand descriptors) -> TMEM, 128 lanes x 256 bits
+__device__ __forceinline__ void tmem_cp_128x256b(uint32_t taddr, uint64_t sdesc) {
+  asm volatile("tcgen05.cp.cta_group::1.128x256b [%0], %1;" ::"r"(taddr), "l"(sdesc) : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem desc]
+__device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+// shared-memory carve-up (all offsets from a 1024-aligned base)
+struct RnnSmem {
+  uint32_t a_off, b_off, slab_off, bar_off, total;
+};
+__host__ __device__ inline RnnSmem rnn_smem_layout(int nbox, int NI) {
+  RnnSmem s;
+  s.a_off = 0;                                            // nbox x [128 x 64] bf16 (SW128 K-major)
+  s.b_off = s.a_off + nbox * 16384;                       // NI x nbox x [16 x 64] bf16
+  s.slab_off = s.b_off + NI * nbox * (BP * 128);          // NI x KS x [32 x 16] fp32
+  s.bar_off = s.slab_off + NI * KS * 32 * BP * 4;         // mbarriers
+  s.total = s.bar_off + 8 * (2 + NI * (MAX_NBOX + 2)) + 16;
+  return s;
+}
+
+template <bool BWD>
+__global__ void __launch_bounds__(INST_THREADS * MAX_NI, 1)
+rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b0,
+                   const __grid_constant__ CUtensorMap tm_b1, RnnPersistParams p) {
+  extern __shared__ uint8_t rnn_smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(rnn_smem_raw) + 1023) & ~uintptr_t(1023));
+  const int NI = p.NI, nbox = p.nbox;
+  const RnnSmem L = rnn_smem_layout(nbox, NI);
+  uint8_t* sA = smem + L.a_off;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
+  uint64_t* a_bar = bars;            // U slice landed in smem
+  uint64_t* acp_bar = bars + 1;      // U slice copied into TMEM
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 + NI * (MAX_NBOX + 2));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int inst = warp / 5, w_in = warp % 5;
+  uint64_t* h_bar = bars + 2 + inst * (MAX_NBOX + 2);       // [nbox] moving operand boxes landed (per step)
+  uint64_t* mma_bar = h_bar + MAX_NBOX;                     // accumulators ready (per step)
+  uint64_t* slab_bar = h_bar + MAX_NBOX + 1;                // KS partial slabs arrived (per step)
+  uint8_t* sB = smem + L.b_off + inst * nbox * (BP * 128);
+  float* slab = reinterpret_cast<float*>(smem + L.slab_off) + inst * KS * 32 * BP;
+
+  const uint32_t rank = cluster_ctarank();                  // K slice owned by this CTA, rows it finishes
+  const int mt = blockIdx.y, d = blockIdx.z;
+  const int m0 = mt * 128;
+  const int rev = (p.reverse_mask >> d) & 1;
+  const int T = p.T, H = p.H, ND = p.ND, Bn = p.B;
+  const CUtensorMap* tm_b = d ? &tm_b1 : &tm_b0;
+  unsigned int* ctr = p.ctr + (d * NI + inst) * 32;
+  const unsigned int ctas_per_dir = KS * p.tiles_m;
+  const bool prof_cta = p.prof && (blockIdx.x + blockIdx.y + blockIdx.z == 0) && inst == 0;
+  const int acols = p.a_in_tmem ? nbox * 32 : 0;            // TMEM columns holding U (8 per K=16 chunk)
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tm_a);
+    tma_prefetch_desc(tm_b);
+    mbar_init(a_bar, 1);
+    mbar_init(acp_bar, 1);
+    for (int i = 0; i < NI; ++i) {
+      uint64_t* hb = bars + 2 + i * (MAX_NBOX + 2);
+      for (int j = 0; j < nbox; ++j) mbar_init(hb + j, 1);
+      mbar_init(hb + MAX_NBOX, 1);
+      mbar_init(hb + MAX_NBOX + 1, KS);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t d_tmem = tmem_base + acols + inst * BP;
+  // every CTA of the cluster must have initialised its barriers before any remote arrive / DSMEM store
+  cluster_arrive();
+  cluster_wait();
+
+  if (w_in == 0) {
+    // =========================== control warp of this instance: TMA + MMA issue ===========================
+    if (inst == 0 && lane == 0) {
+      mbar_arrive_expect_tx(a_bar, nbox * 16384);
+      for (int i = 0; i < nbox; ++i) tma_load_2d(sA + i * 16384, &tm_a, a_bar, rank * p.ksl + i * 64, d * H + m0);
+      mbar_wait(a_bar, 0, 10);
+      if (p.a_in_tmem) {
+        tc_fence_after();
+        const uint32_t a0 = smem_u32(sA);
+        for (int c = 0; c < nbox * 4; ++c)
+          tmem_cp_128x256b(tmem_base + c * 8, umma_smem_desc_sw128(a0 + (c >> 2) * 16384 + (c & 3) * 32, 16, 1024));
+      }
+      umma_commit(acp_bar);          // arrives when the copies (if any) have completed
+    }
+    __syncwarp();
+    mbar_wait(acp_bar, 0, 11);       // every instance's control warp: U is in place
+    tc_fence_after();
+    const uint32_t idesc = umma_idesc_bf16(128, BP, 0, 0);
+    uint32_t ph = 0;
+    for (int step = 1; step < T; ++step) {
+      const int t = BWD ? (rev ? step : T - 1 - step) : (rev ? T - 1 - step : step);
+      const int tsrc = BWD ? (rev ? t - 1 : t + 1) : (rev ? t + 1 : t - 1);   // step whose result feeds this one
+      if (lane == 0) {
+        // wait until every CTA of this direction has published the previous step of this instance
+        const unsigned int need = ctas_per_dir * (unsigned int)step;
+        if (ld_acquire_u32(ctr) < need) {
+          SpinGuard g;
+          while (ld_acquire_u32(ctr) < need) g.check(20);
+        }
+        if (prof_cta && step < 1024) p.prof[step * 8 + 0] = dev_clock();
+        asm volatile("fence.proxy.async;" ::: "memory");      // generic-proxy acquire -> async-proxy (TMA) reads
+        for (int i = 0; i < nbox; ++i) {
+          mbar_arrive_expect_tx(h_bar + i, BP * 128);
+          tma_load_2d(sB + i * (BP * 128), tm_b, h_bar + i, rank * p.ksl + i * 64, tsrc * Bn + inst * BP);
+        }
+        const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
+        for (int i = 0; i < nbox; ++i) {
+          mbar_wait(h_bar + i, ph, 30);
+          tc_fence_after();
+          if (i == 0 && prof_cta && step < 1024) p.prof[step * 8 + 1] = dev_clock();
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t bdesc = umma_smem_desc_sw128(b0 + i * (BP * 128) + k * 32, 16, 1024);
+            if (p.a_in_tmem)
+              umma_bf16_ts(d_tmem, tmem_base + (i * 4 + k) * 8, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            else
+              umma_bf16(d_tmem, umma_smem_desc_sw128(a0 + i * 16384 + k * 32, 16, 1024), bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
+        }
+        umma_commit(mma_bar);
+        if (prof_cta && step < 1024) p.prof[step * 8 + 2] = dev_clock();
+      }
+      __syncwarp();
+      ph ^= 1;
+    }
+  } else {
+    // =========================== epilogue warps of this instance ===========================
+    const int q = warp & 3;                      // TMEM lane quarter = rows [32q, 32q+32) of the tile
+    const int et = (w_in - 1) * 32 + lane;       // 0..127
+    const int bl = et % BP;                      // utterance within the instance
+    const int jg = et / BP;                      // 0..7: 4-row group of this CTA's 32 rows
+    const int b = inst * BP + bl;
+    const int j = m0 + 32 * (int)rank + 4 * jg;  // first of 4 consecutive output units
+    const bool jvalid = j < H;                   // H % 8 == 0 -> all-or-nothing
+    float bias4[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) bias4[i] = (!BWD && jvalid) ? p.bias[d * H + j + i] : 0.f;
+    const int len_b = p.lens[b];
+    const uint32_t slab_local = smem_u32(slab);
+    const uint32_t slab_bar_local = smem_u32(slab_bar);
+    uint32_t ph = 0;
+    for (int step = 0; step < T; ++step) {
+      const int t = BWD ? (rev ? step : T - 1 - step) : (rev ? T - 1 - step : step);
+      // prefetch the additive term (s*Wx_t or dout_t) and, for the backward, h_t for the mask
+      float4 add = make_float4(0.f, 0.f, 0.f, 0.f);
+      uint2 hm = make_uint2(0u, 0u);
+      if (jvalid) {
+        const float* src = BWD ? p.add_in + ((size_t)t * Bn + b) * H + j
+                               : p.add_in + ((size_t)t * Bn + b) * ND * H + (size_t)d * H + j;
+        add = __ldg(reinterpret_cast<const float4*>(src));
+        if (BWD) hm = *reinterpret_cast<const uint2*>(p.hs_in + (((size_t)d * T + t) * Bn + b) * H + j);
+      }
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      const bool pr = prof_cta && et == 0 && step < 1024;
+      if (step > 0) {
+        mbar_wait(mma_bar, ph, 40);
+        tc_fence_after();
+        if (pr) p.prof[step * 8 + 3] = dev_clock();
+        // send this warp's 32 rows x 16 partial sums to the CTA that finishes those rows (cluster rank q)
+        uint32_t r[16];
+        tmem_ld_32x16(d_tmem + (static_cast<uint32_t>(q * 32) << 16), r);
+        tmem_ld_wait();
+        const uint32_t dst = map_to_rank(slab_local, (uint32_t)q) + ((rank * 32 + lane) * BP) * 4;
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          st_cluster_v4(dst + c * 16, __uint_as_float(r[4 * c]), __uint_as_float(r[4 * c + 1]), __uint_as_float(r[4 * c + 2]),
+                        __uint_as_float(r[4 * c + 3]));
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_remote_arrive_release(map_to_rank(slab_bar_local, (uint32_t)q));
+        if (pr) p.prof[step * 8 + 4] = dev_clock();
+        if (!mbar_try_wait_acq_cluster(slab_bar, ph)) {
+          SpinGuard g;
+          while (!mbar_try_wait_acq_cluster(slab_bar, ph)) g.check(50);
+        }
+        ph ^= 1;
+        if (pr) p.prof[step * 8 + 5] = dev_clock();
+        // reduce the KS partial slabs for this thread's (utterance, 4 rows)
+#pragma unroll
+        for (int s = 0; s < KS; ++s) {
+          const float* sp = slab + (s * 32 + 4 * jg) * BP + bl;
+          acc[0] += sp[0]; acc[1] += sp[BP]; acc[2] += sp[2 * BP]; acc[3] += sp[3 * BP];
+        }
+      }
+      if (jvalid) {
+        const bool live = t < len_b;
+        const float av[4] = {add.x, add.y, add.z, add.w};
+        float o[4];
+        if (!BWD) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float z = fmaf(p.scale, av[i], acc[i] + bias4[i]);
+            o[i] = live ? fminf(fmaxf(z, 0.f), p.cap) : 0.f;
+          }
+        } else {
+          const __nv_bfloat16* hb = reinterpret_cast<const __nv_bfloat16*>(&hm);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float h = __bfloat162float(hb[i]);
+            o[i] = (live && h > 0.f && h < p.cap) ? (av[i] + acc[i]) : 0.f;
+          }
+        }
+        uint2 pk;
+        __nv_bfloat162 b0 = __floats2bfloat162_rn(o[0], o[1]), b1 = __floats2bfloat162_rn(o[2], o[3]);
+        pk.x = *reinterpret_cast<uint32_t*>(&b0);
+        pk.y = *reinterpret_cast<uint32_t*>(&b1);
+        __nv_bfloat16* dstp = BWD ? p.out + ((size_t)t * Bn + b) * ND * H + (size_t)d * H + j
+                                  : p.out + (((size_t)d * T + t) * Bn + b) * H + j;
+        *reinterpret_cast<uint2*>(dstp) = pk;
+      }
+      if (pr) p.prof[step * 8 + 6] = dev_clock();
+      // publish: the instance's 128 epilogue threads' stores -> one release increment of its step counter
+      // (CTA-level barrier orders their stores before thread 0's gpu-scope release: cumulativity)
+      asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
+      if (et == 0) red_release_add(ctr, 1u);
+      if (pr) p.prof[step * 8 + 7] = dev_clock();
+    }
+  }
+  // no CTA may exit while a peer can still write into its shared memory
+  tc_fence_before();
+  cluster_arrive();
+  cluster_wait();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------ host side
+static int persist_geometry(int B, int H, int ND, int* tiles_m, int* ksl, int* nbox, int* ni, size_t* smem) {
+  if (B % BP != 0 || B < BP || B / BP > MAX_NI || H % 8 != 0 || H < 8 || (ND != 1 && ND != 2)) return 0;
+  const int tm = (H + 127) / 128;
+  const int slice = (H + KS - 1) / KS;
+  const int l = ((slice + 63) / 64) * 64;
+  const int nb = l / 64;
+  if (nb > MAX_NBOX) return 0;
+  const int n_inst = B / BP;
+  if (nb * 32 + n_inst * BP > 512) return 0;   // TMEM columns: resident U + accumulators
+  const size_t bytes = rnn_smem_layout(nb, n_inst).total + 1024;
+  if (bytes > 225 * 1024) return 0;
+  if (KS * tm * ND > 128) return 0;           // must be co-resident in clusters of 4 (148 SMs, 1 CTA / SM)
+  if (tiles_m) *tiles_m = tm;
+  if (ksl) *ksl = l;
+  if (nbox) *nbox = nb;
+  if (ni) *ni = n_inst;
+  if (smem) *smem = bytes;
+  return 1;
+}
+
+int rnn_persist_supported(int B, int H, int ND) { return persist_geometry(B, H, ND, nullptr, nullptr, nullptr, nullptr, nullptr); }
+
+static constexpr size_t WS_CTR_BYTES = 2048;     // ND x MAX_NI counters, one 128-byte line each
+static constexpr size_t WS_PROF_BYTES = 65536;
+
+size_t rnn_persist_workspace_bytes(int T, int B, int H, int ND) {
+  (void)T; (void)B;
+  // step counters + optional profile stamps + room for U^T (bf16) used by the backward
+  return WS_CTR_BYTES + WS_PROF_BYTES + (size_t)ND * H * H * 2;
+}
+
+template <bool BWD>
+static int persist_launch(const CUtensorMap& ta, const CUtensorMap& tb0, const CUtensorMap& tb1, RnnPersistParams& p, size_t smem,
+                          cudaStream_t st) {
+  auto kern = rnn_persist_kernel<BWD>;
+  static bool attr_done[2] = {false, false};
+  if (!attr_done[BWD]) {
+    DS2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+    attr_done[BWD] = true;
+  }
+  p.a_in_tmem = getenv("DS2_RNN_A_SMEM") ? 0 : 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(KS, p.tiles_m, p.ND);
+  cfg.blockDim = dim3(INST_THREADS * p.NI);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attrs[2];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = KS;
+  attrs[0].val.clusterDim.y = 1;
+  attrs[0].val.clusterDim.z = 1;
+  attrs[1].id = cudaLaunchAttributeCooperative;       // all CTAs co-resident (they spin on each other)
+  attrs[1].val.cooperative = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs = getenv("DS2_RNN_NO_COOP") ? 1 : 2;   // profilers cannot replay cooperative launches
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb0, tb1, p);
+  if (e != cudaSuccess && cfg.numAttrs == 2) {
+    // some driver versions reject cooperative + cluster launches: the grid (<= 128 CTAs, 1 per SM)
+    // fits the device anyway, so fall back to a plain cluster launch
+    (void)cudaGetLastError();
+    cfg.numAttrs = 1;
+    e = cudaLaunchKernelEx(&cfg, kern, ta, tb0, tb1, p);
+  }
+  if (e != cudaSuccess) return cuda_fail(e, BWD ? "rnn_persist_kernel<bwd>" : "rnn_persist_kernel<fwd>");
+  count_launch();
+  return DS2_OK;
+}
+
+static int persist_common(RnnPersistParams& p, size_t* smem, int T, int B, int H, int ND, void* ws, size_t ws_bytes, const char* who,
+                          cudaStream_t st) {
+  DS2_REQUIRE(persist_geometry(B, H, ND, &p.tiles_m, &p.ksl, &p.nbox, &p.NI, smem), DS2_ERR_UNSUPPORTED,
+              "%s: persistent kernel does not take B=%d H=%d ND=%d", who, B, H, ND);
+  const size_t need = rnn_persist_workspace_bytes(T, B, H, ND);
+  DS2_REQUIRE(ws && ws_bytes >= need, DS2_ERR_WORKSPACE, "%s: workspace of %zu bytes required", who, need);
+  DS2_CUDA(cudaMemsetAsync(ws, 0, WS_CTR_BYTES, st));
+  p.ctr = static_cast<unsigned int*>(ws);
+  p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(static_cast<char*>(ws) + WS_CTR_BYTES) : nullptr;
+  return DS2_OK;
+}
+
+int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, int T, int B,
+                         int H, int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
+  RnnPersistParams p = {};
+  size_t smem;
+  int rc = persist_common(p, &smem, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_fwd", st);
+  if (rc) return rc;
+  CUtensorMap ta, tb0, tb1;
+  rc = make_tmap_2d_bf16(&ta, u, H, (uint64_t)ND * H, H, 64, 128);
+  if (rc) return rc;
+  const __nv_bfloat16* hsb = static_cast<const __nv_bfloat16*>(hs);
+  rc = make_tmap_2d_bf16(&tb0, hsb, H, (uint64_t)T * B, H, 64, BP);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&tb1, hsb + (ND > 1 ? (size_t)T * B * H : 0), H, (uint64_t)T * B, H, 64, BP);
+  if (rc) return rc;
+  p.add_in = wx; p.bias = bias; p.lens = lens; p.hs_in = nullptr; p.out = static_cast<__nv_bfloat16*>(hs);
+  p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = scale; p.cap = cap;
+  return persist_launch<false>(ta, tb0, tb1, p, smem, st);
+}
+
+// The backward contraction is U^T dz: U is transposed per direction into the workspace first
+// (ut[d][k][j] = U[d][j][k], 2*ND*H*H bytes, one small kernel per direction), then used as the resident A operand.
+int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, const void* hs, void* dz, int T, int B, int H, int ND,
+                         int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
+  RnnPersistParams p = {};
+  size_t smem;
+  int rc = persist_common(p, &smem, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_bwd", st);
+  if (rc) return rc;
+  __nv_bfloat16* ut = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + WS_CTR_BYTES + WS_PROF_BYTES);
+  for (int d = 0; d < ND; ++d) {
+    rc = ds2_transpose(static_cast<const __nv_bfloat16*>(u) + (size_t)d * H * H, DS2_BF16, H, H, H, ut + (size_t)d * H * H, DS2_BF16, H, st);
+    if (rc) return rc;
+  }
+  CUtensorMap ta, tb0, tb1;
+  rc = make_tmap_2d_bf16(&ta, ut, H, (uint64_t)ND * H, H, 64, 128);
+  if (rc) return rc;
+  const __nv_bfloat16* dzb = static_cast<const __nv_bfloat16*>(dz);
+  rc = make_tmap_2d_bf16(&tb0, dzb, H, (uint64_t)T * B, (uint64_t)ND * H, 64, BP);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&tb1, dzb + (ND > 1 ? H : 0), H, (uint64_t)T * B, (uint64_t)ND * H, 64, BP);
+  if (rc) return rc;
+  p.add_in = dout; p.bias = nullptr; p.lens = lens; p.hs_in = static_cast<const __nv_bfloat16*>(hs);
+  p.out = static_cast<__nv_bfloat16*>(dz);
+  p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = 1.f; p.cap = cap;
+  return persist_launch<true>(ta, tb0, tb1, p, smem, st);
+}
+
+}  // namespace ds2

@@ -468,7 +468,15 @@ class _LinearFn(torch.autograd.Function):
             dx = gemm_nt(dy, W, b_mn=True)                      # [R,K] = dy[R,N] . W[N,K]
             if x2d.dtype != torch.float32:
                 dx = cast(dx, x2d.dtype)
-        dW = gemm_nt(dy, x2d, a_mn=True, b_mn=True)             # [N,K] = dy^T x
+        if x2d.dtype == torch.bfloat16 and R % 8 == 0 and K % 8 == 0:
+            # tensor cores: dy^T as a K-major bf16 operand (transpose+cast, N x R), x as the MN-major one, split-K over R
+            dyT = torch.empty((N, R), dtype=torch.bfloat16, device=dy.device)
+            check(lib.ds2_transpose(_p(dy), DS2_F32, R, N, N, _p(dyT), DS2_BF16, R, _stream()), "ds2_transpose")
+            dW = torch.empty((N, K), dtype=torch.float32, device=dy.device)
+            check(lib.ds2_gemm_bf16_splitk(_p(dyT), R, 0, _p(x2d), K, 1, _p(dW), K, N, K, R, 1.0, None, 0, _stream()),
+                  "ds2_gemm_bf16_splitk")
+        else:
+            dW = gemm_nt(dy, x2d, a_mn=True, b_mn=True)         # [N,K] = dy^T x
         db = colsum(dy, R, N, N) if ctx.has_bias else None
         return dx, dW, db, None
 
