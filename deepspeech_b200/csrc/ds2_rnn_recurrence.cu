@@ -42,6 +42,7 @@ struct RnnPersistParams {
   int NI;                  // instances = B / BP
   int tiles_m, ksl, nbox;  // M tiles per direction, K-slice length (multiple of 64), boxes per slice
   int a_in_tmem;
+  int nacc;                // independent accumulator tiles per instance (breaks the MMA->MMA dependency chain)
   float scale, cap;
 };
 
@@ -170,7 +171,8 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t d_tmem = tmem_base + acols + inst * BP;
+  const int nacc = p.nacc;
+  const uint32_t d_tmem = tmem_base + acols + inst * nacc * BP;
   // every CTA of the cluster must have initialised its barriers before any remote arrive / DSMEM store
   cluster_arrive();
   cluster_wait();
@@ -211,17 +213,20 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
           tma_load_2d(sB + i * (BP * 128), tm_b, h_bar + i, rank * p.ksl + i * 64, tsrc * Bn + inst * BP);
         }
         const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
+        int c = 0;                                            // K=16 chunk index -> accumulator c % nacc
         for (int i = 0; i < nbox; ++i) {
           mbar_wait(h_bar + i, ph, 30);
           tc_fence_after();
           if (i == 0 && prof_cta && step < 1024) p.prof[step * 8 + 1] = dev_clock();
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
+          for (int k = 0; k < 4; ++k, ++c) {
             const uint64_t bdesc = umma_smem_desc_sw128(b0 + i * (BP * 128) + k * 32, 16, 1024);
+            const uint32_t dt = d_tmem + (c % nacc) * BP;
+            const uint32_t accum = (c >= nacc) ? 1u : 0u;
             if (p.a_in_tmem)
-              umma_bf16_ts(d_tmem, tmem_base + (i * 4 + k) * 8, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+              umma_bf16_ts(dt, tmem_base + c * 8, bdesc, idesc, accum);
             else
-              umma_bf16(d_tmem, umma_smem_desc_sw128(a0 + i * 16384 + k * 32, 16, 1024), bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+              umma_bf16(dt, umma_smem_desc_sw128(a0 + i * 16384 + k * 32, 16, 1024), bdesc, idesc, accum);
           }
         }
         umma_commit(mma_bar);
@@ -267,6 +272,13 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
         uint32_t r[16];
         tmem_ld_32x16(d_tmem + (static_cast<uint32_t>(q * 32) << 16), r);
         tmem_ld_wait();
+        for (int a = 1; a < nacc; ++a) {                    // fold the independent accumulator tiles
+          uint32_t r2[16];
+          tmem_ld_32x16(d_tmem + a * BP + (static_cast<uint32_t>(q * 32) << 16), r2);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) + __uint_as_float(r2[i]));
+        }
         const uint32_t dst = map_to_rank(slab_local, (uint32_t)q) + ((rank * 32 + lane) * BP) * 4;
 #pragma unroll
         for (int c = 0; c < 4; ++c)
@@ -376,6 +388,14 @@ static int persist_launch(const CUtensorMap& ta, const CUtensorMap& tb0, const C
     attr_done[BWD] = true;
   }
   p.a_in_tmem = getenv("DS2_RNN_A_SMEM") ? 0 : 1;
+  {
+    const int acols = p.a_in_tmem ? p.nbox * 32 : 0;
+    int nacc = (512 - acols) / (p.NI * BP);
+    if (nacc > 8) nacc = 8;
+    if (nacc > p.nbox * 4) nacc = p.nbox * 4;
+    if (const char* e = getenv("DS2_RNN_NACC")) { int v = atoi(e); if (v >= 1 && v <= nacc) nacc = v; }
+    p.nacc = nacc < 1 ? 1 : nacc;
+  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(KS, p.tiles_m, p.ND);
   cfg.blockDim = dim3(INST_THREADS * p.NI);
