@@ -42,7 +42,6 @@ struct RnnPersistParams {
   int NI;                  // instances = B / BP
   int tiles_m, ksl, nbox;  // M tiles per direction, K-slice length (multiple of 64), boxes per slice
   int a_in_tmem;
-  int nacc;                // independent accumulator tiles per instance (breaks the MMA->MMA dependency chain)
   float scale, cap;
 };
 
@@ -120,7 +119,7 @@ __host__ __device__ inline RnnSmem rnn_smem_layout(int nbox, int NI) {
   return s;
 }
 
-template <bool BWD>
+template <bool BWD, bool ATMEM>
 __global__ void __launch_bounds__(INST_THREADS * MAX_NI, 1)
 rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b0,
                    const __grid_constant__ CUtensorMap tm_b1, RnnPersistParams p) {
@@ -134,7 +133,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
   uint64_t* acp_bar = bars + 1;      // U slice copied into TMEM
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 + NI * (MAX_NBOX + 2));
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const int inst = warp / 5, w_in = warp % 5;
   uint64_t* h_bar = bars + 2 + inst * (MAX_NBOX + 2);       // [nbox] moving operand boxes landed (per step)
   uint64_t* mma_bar = h_bar + MAX_NBOX;                     // accumulators ready (per step)
@@ -151,7 +150,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
   unsigned int* ctr = p.ctr + (d * NI + inst) * 32;
   const unsigned int ctas_per_dir = KS * p.tiles_m;
   const bool prof_cta = p.prof && (blockIdx.x + blockIdx.y + blockIdx.z == 0) && inst == 0;
-  const int acols = p.a_in_tmem ? nbox * 32 : 0;            // TMEM columns holding U (8 per K=16 chunk)
+  const int acols = ATMEM ? nbox * 32 : 0;            // TMEM columns holding U (8 per K=16 chunk)
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tm_a);
@@ -171,19 +170,18 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int nacc = p.nacc;
-  const uint32_t d_tmem = tmem_base + acols + inst * nacc * BP;
+  const uint32_t d_tmem = tmem_base + acols + inst * BP;
   // every CTA of the cluster must have initialised its barriers before any remote arrive / DSMEM store
   cluster_arrive();
   cluster_wait();
 
   if (w_in == 0) {
     // =========================== control warp of this instance: TMA + MMA issue ===========================
-    if (inst == 0 && lane == 0) {
+    if (inst == 0 && elect_one_sync()) {
       mbar_arrive_expect_tx(a_bar, nbox * 16384);
       for (int i = 0; i < nbox; ++i) tma_load_2d(sA + i * 16384, &tm_a, a_bar, rank * p.ksl + i * 64, d * H + m0);
       mbar_wait(a_bar, 0, 10);
-      if (p.a_in_tmem) {
+      if (ATMEM) {
         tc_fence_after();
         const uint32_t a0 = smem_u32(sA);
         for (int c = 0; c < nbox * 4; ++c)
@@ -199,7 +197,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
     for (int step = 1; step < T; ++step) {
       const int t = BWD ? (rev ? step : T - 1 - step) : (rev ? T - 1 - step : step);
       const int tsrc = BWD ? (rev ? t - 1 : t + 1) : (rev ? t + 1 : t - 1);   // step whose result feeds this one
-      if (lane == 0) {
+      if (elect_one_sync()) {
         // wait until every CTA of this direction has published the previous step of this instance
         const unsigned int need = ctas_per_dir * (unsigned int)step;
         if (ld_acquire_u32(ctr) < need) {
@@ -213,20 +211,17 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
           tma_load_2d(sB + i * (BP * 128), tm_b, h_bar + i, rank * p.ksl + i * 64, tsrc * Bn + inst * BP);
         }
         const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
-        int c = 0;                                            // K=16 chunk index -> accumulator c % nacc
         for (int i = 0; i < nbox; ++i) {
           mbar_wait(h_bar + i, ph, 30);
           tc_fence_after();
           if (i == 0 && prof_cta && step < 1024) p.prof[step * 8 + 1] = dev_clock();
 #pragma unroll
-          for (int k = 0; k < 4; ++k, ++c) {
+          for (int k = 0; k < 4; ++k) {
             const uint64_t bdesc = umma_smem_desc_sw128(b0 + i * (BP * 128) + k * 32, 16, 1024);
-            const uint32_t dt = d_tmem + (c % nacc) * BP;
-            const uint32_t accum = (c >= nacc) ? 1u : 0u;
-            if (p.a_in_tmem)
-              umma_bf16_ts(dt, tmem_base + c * 8, bdesc, idesc, accum);
+            if (ATMEM)
+              umma_bf16_ts(d_tmem, tmem_base + (i * 4 + k) * 8, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
             else
-              umma_bf16(dt, umma_smem_desc_sw128(a0 + i * 16384 + k * 32, 16, 1024), bdesc, idesc, accum);
+              umma_bf16(d_tmem, umma_smem_desc_sw128(a0 + i * 16384 + k * 32, 16, 1024), bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
         }
         umma_commit(mma_bar);
@@ -272,13 +267,6 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
         uint32_t r[16];
         tmem_ld_32x16(d_tmem + (static_cast<uint32_t>(q * 32) << 16), r);
         tmem_ld_wait();
-        for (int a = 1; a < nacc; ++a) {                    // fold the independent accumulator tiles
-          uint32_t r2[16];
-          tmem_ld_32x16(d_tmem + a * BP + (static_cast<uint32_t>(q * 32) << 16), r2);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) + __uint_as_float(r2[i]));
-        }
         const uint32_t dst = map_to_rank(slab_local, (uint32_t)q) + ((rank * 32 + lane) * BP) * 4;
 #pragma unroll
         for (int c = 0; c < 4; ++c)
@@ -381,20 +369,12 @@ size_t rnn_persist_workspace_bytes(int T, int B, int H, int ND) {
 template <bool BWD>
 static int persist_launch(const CUtensorMap& ta, const CUtensorMap& tb0, const CUtensorMap& tb1, RnnPersistParams& p, size_t smem,
                           cudaStream_t st) {
-  auto kern = rnn_persist_kernel<BWD>;
-  static bool attr_done[2] = {false, false};
-  if (!attr_done[BWD]) {
-    DS2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
-    attr_done[BWD] = true;
-  }
   p.a_in_tmem = getenv("DS2_RNN_A_SMEM") ? 0 : 1;
-  {
-    const int acols = p.a_in_tmem ? p.nbox * 32 : 0;
-    int nacc = (512 - acols) / (p.NI * BP);
-    if (nacc > 8) nacc = 8;
-    if (nacc > p.nbox * 4) nacc = p.nbox * 4;
-    if (const char* e = getenv("DS2_RNN_NACC")) { int v = atoi(e); if (v >= 1 && v <= nacc) nacc = v; }
-    p.nacc = nacc < 1 ? 1 : nacc;
+  auto kern = p.a_in_tmem ? rnn_persist_kernel<BWD, true> : rnn_persist_kernel<BWD, false>;
+  static bool attr_done[2][2] = {{false, false}, {false, false}};
+  if (!attr_done[BWD][p.a_in_tmem]) {
+    DS2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+    attr_done[BWD][p.a_in_tmem] = true;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(KS, p.tiles_m, p.ND);
