@@ -42,6 +42,7 @@ struct RnnPersistParams {
   int NI;                  // instances = B / BP
   int tiles_m, ksl, nbox;  // M tiles per direction, K-slice length (multiple of 64), boxes per slice
   int a_in_tmem;
+  int stagger;             // start offset (cycles) between the instances of a CTA so their per-step phases interleave
   float scale, cap;
 };
 
@@ -193,6 +194,10 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
     mbar_wait(acp_bar, 0, 11);       // every instance's control warp: U is in place
     tc_fence_after();
     const uint32_t idesc = umma_idesc_bf16(128, BP, 0, 0);
+    if (inst > 0 && p.stagger > 0) {   // de-phase the instances: their TMA / MMA / DSMEM bursts then do not collide
+      const long long t0 = dev_clock();
+      while (dev_clock() - t0 < (long long)inst * p.stagger) {}
+    }
     uint32_t ph = 0;
     for (int step = 1; step < T; ++step) {
       const int t = BWD ? (rev ? step : T - 1 - step) : (rev ? T - 1 - step : step);
@@ -370,6 +375,7 @@ template <bool BWD>
 static int persist_launch(const CUtensorMap& ta, const CUtensorMap& tb0, const CUtensorMap& tb1, RnnPersistParams& p, size_t smem,
                           cudaStream_t st) {
   p.a_in_tmem = getenv("DS2_RNN_A_SMEM") ? 0 : 1;
+  p.stagger = getenv("DS2_RNN_STAGGER") ? atoi(getenv("DS2_RNN_STAGGER")) : 0;
   auto kern = p.a_in_tmem ? rnn_persist_kernel<BWD, true> : rnn_persist_kernel<BWD, false>;
   static bool attr_done[2][2] = {{false, false}, {false, false}};
   if (!attr_done[BWD][p.a_in_tmem]) {
