@@ -42,6 +42,7 @@ struct RnnPersistParams {
   int NI;                  // instances = B / BP
   int tiles_m, ksl, nbox;  // M tiles per direction, K-slice length (multiple of 64), boxes per slice
   int a_in_tmem;
+  int nacc;                // 4 or 8 independent accumulator tiles per instance: consecutive tcgen05.mma into ONE tile serialise on its ~60-cycle latency
   int stagger;             // start offset (cycles) between the instances of a CTA so their per-step phases interleave
   float scale, cap;
 };
@@ -171,7 +172,9 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t d_tmem = tmem_base + acols + inst * BP;
+  const int nacc = p.nacc;
+  const uint32_t d_tmem = tmem_base + acols + inst * nacc * BP;
+  const uint32_t acc_hi = (nacc > 4) ? 4u * BP : 0u;         // odd boxes use accumulators 4..7 when there are 8
   // every CTA of the cluster must have initialised its barriers before any remote arrive / DSMEM store
   cluster_arrive();
   cluster_wait();
@@ -224,9 +227,9 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
           for (int k = 0; k < 4; ++k) {
             const uint64_t bdesc = umma_smem_desc_sw128(b0 + i * (BP * 128) + k * 32, 16, 1024);
             if (ATMEM)
-              umma_bf16_ts(d_tmem, tmem_base + (i * 4 + k) * 8, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+              umma_bf16_ts(d_tmem + k * BP + (i & 1) * acc_hi, tmem_base + (i * 4 + k) * 8, bdesc, idesc, (i > (acc_hi ? 1 : 0)) ? 1u : 0u);
             else
-              umma_bf16(d_tmem, umma_smem_desc_sw128(a0 + i * 16384 + k * 32, 16, 1024), bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+              umma_bf16(d_tmem + k * BP + (i & 1) * acc_hi, umma_smem_desc_sw128(a0 + i * 16384 + k * 32, 16, 1024), bdesc, idesc, (i > (acc_hi ? 1 : 0)) ? 1u : 0u);
           }
         }
         umma_commit(mma_bar);
@@ -271,6 +274,17 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
         // send this warp's 32 rows x 16 partial sums to the CTA that finishes those rows (cluster rank q)
         uint32_t r[16];
         tmem_ld_32x16(d_tmem + (static_cast<uint32_t>(q * 32) << 16), r);
+        {
+          const int nfold = (nacc > 4 && nbox < 2) ? 4 : nacc;   // tiles actually written this step
+          for (int a = 1; a < nfold; ++a) {                     // fold the independent accumulator tiles
+            uint32_t r2[16];
+            tmem_ld_wait();
+            tmem_ld_32x16(d_tmem + a * BP + (static_cast<uint32_t>(q * 32) << 16), r2);
+            tmem_ld_wait();
+#pragma unroll
+            for (int e = 0; e < 16; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) + __uint_as_float(r2[e]));
+          }
+        }
         tmem_ld_wait();
         const uint32_t dst = map_to_rank(slab_local, (uint32_t)q) + ((rank * 32 + lane) * BP) * 4;
 #pragma unroll
@@ -348,7 +362,7 @@ static int persist_geometry(int B, int H, int ND, int* tiles_m, int* ksl, int* n
   const int nb = l / 64;
   if (nb > MAX_NBOX) return 0;
   const int n_inst = B / BP;
-  if (nb * 32 + n_inst * BP > 512) return 0;   // TMEM columns: resident U + accumulators
+  if (nb * 32 + n_inst * 4 * BP > 512) return 0;   // TMEM columns: resident U + accumulators
   const size_t bytes = rnn_smem_layout(nb, n_inst).total + 1024;
   if (bytes > 225 * 1024) return 0;
   if (KS * tm * ND > 128) return 0;           // must be co-resident in clusters of 4 (148 SMs, 1 CTA / SM)
@@ -375,6 +389,7 @@ template <bool BWD>
 static int persist_launch(const CUtensorMap& ta, const CUtensorMap& tb0, const CUtensorMap& tb1, RnnPersistParams& p, size_t smem,
                           cudaStream_t st) {
   p.a_in_tmem = getenv("DS2_RNN_A_SMEM") ? 0 : 1;
+  p.nacc = ((p.a_in_tmem ? p.nbox * 32 : 0) + p.NI * 8 * BP <= 512 && !getenv("DS2_RNN_NACC4")) ? 8 : 4;
   p.stagger = getenv("DS2_RNN_STAGGER") ? atoi(getenv("DS2_RNN_STAGGER")) : 0;
   auto kern = p.a_in_tmem ? rnn_persist_kernel<BWD, true> : rnn_persist_kernel<BWD, false>;
   static bool attr_done[2][2] = {{false, false}, {false, false}};
