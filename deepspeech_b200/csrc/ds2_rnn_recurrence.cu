@@ -212,17 +212,20 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
           SpinGuard g;
           while (ld_acquire_u32(ctr) < need) g.check(20);
         }
-        if (prof_cta && step < 1024) p.prof[step * 8 + 0] = dev_clock();
+        if (prof_cta && step < 1024) p.prof[step * 16 + 0] = dev_clock();
         asm volatile("fence.proxy.async;" ::: "memory");      // generic-proxy acquire -> async-proxy (TMA) reads
+        if (prof_cta && step < 1024) p.prof[step * 16 + 8] = dev_clock();
         for (int i = 0; i < nbox; ++i) {
           mbar_arrive_expect_tx(h_bar + i, BP * 128);
           tma_load_2d(sB + i * (BP * 128), tm_b, h_bar + i, rank * p.ksl + i * 64, tsrc * Bn + inst * BP);
         }
+        if (prof_cta && step < 1024) p.prof[step * 16 + 9] = dev_clock();
         const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
         for (int i = 0; i < nbox; ++i) {
           mbar_wait(h_bar + i, ph, 30);
           tc_fence_after();
-          if (i == 0 && prof_cta && step < 1024) p.prof[step * 8 + 1] = dev_clock();
+          if (i == 0 && prof_cta && step < 1024) p.prof[step * 16 + 1] = dev_clock();
+          if (i == nbox - 1 && prof_cta && step < 1024) p.prof[step * 16 + 10] = dev_clock();
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             const uint64_t bdesc = umma_smem_desc_sw128(b0 + i * (BP * 128) + k * 32, 16, 1024);
@@ -233,7 +236,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
           }
         }
         umma_commit(mma_bar);
-        if (prof_cta && step < 1024) p.prof[step * 8 + 2] = dev_clock();
+        if (prof_cta && step < 1024) p.prof[step * 16 + 2] = dev_clock();
       }
       __syncwarp();
       ph ^= 1;
@@ -270,7 +273,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
       if (step > 0) {
         mbar_wait(mma_bar, ph, 40);
         tc_fence_after();
-        if (pr) p.prof[step * 8 + 3] = dev_clock();
+        if (pr) p.prof[step * 16 + 3] = dev_clock();
         // send this warp's 32 rows x 16 partial sums to the CTA that finishes those rows (cluster rank q)
         uint32_t r[16];
         tmem_ld_32x16(d_tmem + (static_cast<uint32_t>(q * 32) << 16), r);
@@ -286,21 +289,23 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
           }
         }
         tmem_ld_wait();
+        if (pr) p.prof[step * 16 + 11] = dev_clock();
         const uint32_t dst = map_to_rank(slab_local, (uint32_t)q) + ((rank * 32 + lane) * BP) * 4;
 #pragma unroll
         for (int c = 0; c < 4; ++c)
           st_cluster_v4(dst + c * 16, __uint_as_float(r[4 * c]), __uint_as_float(r[4 * c + 1]), __uint_as_float(r[4 * c + 2]),
                         __uint_as_float(r[4 * c + 3]));
+        if (pr) p.prof[step * 16 + 12] = dev_clock();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_remote_arrive_release(map_to_rank(slab_bar_local, (uint32_t)q));
-        if (pr) p.prof[step * 8 + 4] = dev_clock();
+        if (pr) p.prof[step * 16 + 4] = dev_clock();
         if (!mbar_try_wait_acq_cluster(slab_bar, ph)) {
           SpinGuard g;
           while (!mbar_try_wait_acq_cluster(slab_bar, ph)) g.check(50);
         }
         ph ^= 1;
-        if (pr) p.prof[step * 8 + 5] = dev_clock();
+        if (pr) p.prof[step * 16 + 5] = dev_clock();
         // reduce the KS partial slabs for this thread's (utterance, 4 rows)
 #pragma unroll
         for (int s = 0; s < KS; ++s) {
@@ -334,12 +339,12 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
                                   : p.out + (((size_t)d * T + t) * Bn + b) * H + j;
         *reinterpret_cast<uint2*>(dstp) = pk;
       }
-      if (pr) p.prof[step * 8 + 6] = dev_clock();
+      if (pr) p.prof[step * 16 + 6] = dev_clock();
       // publish: the instance's 128 epilogue threads' stores -> one release increment of its step counter
       // (CTA-level barrier orders their stores before thread 0's gpu-scope release: cumulativity)
       asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
       if (et == 0) red_release_add(ctr, 1u);
-      if (pr) p.prof[step * 8 + 7] = dev_clock();
+      if (pr) p.prof[step * 16 + 7] = dev_clock();
     }
   }
   // no CTA may exit while a peer can still write into its shared memory
@@ -377,7 +382,7 @@ static int persist_geometry(int B, int H, int ND, int* tiles_m, int* ksl, int* n
 int rnn_persist_supported(int B, int H, int ND) { return persist_geometry(B, H, ND, nullptr, nullptr, nullptr, nullptr, nullptr); }
 
 static constexpr size_t WS_CTR_BYTES = 2048;     // ND x MAX_NI counters, one 128-byte line each
-static constexpr size_t WS_PROF_BYTES = 65536;
+static constexpr size_t WS_PROF_BYTES = 131072;
 
 size_t rnn_persist_workspace_bytes(int T, int B, int H, int ND) {
   (void)T; (void)B;

@@ -1,6 +1,7 @@
 #!/usr/bin/env python
-"""Per-stage latency of the persistent recurrent kernel (needs a GPU).  Runs the forward (or backward)
-recurrence with DS2_RNN_PROF=1 and prints the mean clock-cycle gap between the in-kernel stamps of CTA (0,0,0)."""
+"""Per-stage latency of the persistent recurrent kernel (needs a GPU).  Runs the forward recurrence with
+DS2_RNN_PROF=1 and prints the mean clock-cycle gap between the in-kernel stamps of CTA (0,0,0), instance 0.
+usage: tools/rnn_prof.py [T] [H] [B]"""
 import os
 import sys
 
@@ -12,7 +13,9 @@ import torch
 from deepspeech_b200 import ops
 from deepspeech_b200._lib import DS2_BF16, check, lib
 
-T, B, H = int(sys.argv[1]) if len(sys.argv) > 1 else 366, 32, int(sys.argv[2]) if len(sys.argv) > 2 else 1760
+T = int(sys.argv[1]) if len(sys.argv) > 1 else 366
+H = int(sys.argv[2]) if len(sys.argv) > 2 else 1760
+B = int(sys.argv[3]) if len(sys.argv) > 3 else 32
 dev = "cuda"
 wx = torch.randn(T * B, 2 * H, device=dev) * 0.5
 U = (torch.randn(2, H, H, device=dev) * (0.5 / H ** 0.5)).to(torch.bfloat16)
@@ -28,16 +31,20 @@ for it in range(3):
     check(lib.ds2_rnn_relu_fwd(p(wx), 1.0, p(U), p(bias), p(lens), p(hs), DS2_BF16, T, B, H, 2, 2, 20.0, p(ws), wsb, st()), "fwd")
     e1.record()
     torch.cuda.synchronize()
-print("fwd kernel %.3f ms  (%.2f us/step)" % (e0.elapsed_time(e1), e0.elapsed_time(e1) * 1e3 / T))
-stamps = ws[1024:1024 + min(T, 1024) * 64].view(torch.int64).cpu().numpy().reshape(-1, 8)
-s = stamps[2:min(T, 1024) - 1]
-nxt = stamps[3:min(T, 1024)]
-names = ["poll->tma_landed", "tma_landed->mma_issued", "mma_issued->mma_done(epi)", "mma_done->scatter_done", "scatter->cluster_barrier",
-         "cluster_barrier->stores_issued", "stores->published", "published->next poll done"]
-gaps = [s[:, 1] - s[:, 0], s[:, 2] - s[:, 1], s[:, 3] - s[:, 2], s[:, 4] - s[:, 3], s[:, 5] - s[:, 4], s[:, 6] - s[:, 5], s[:, 7] - s[:, 6],
-        nxt[:, 0] - s[:, 7]]
-tot = 0
-for n, g in zip(names, gaps):
-    print("%-34s mean %8.1f cyc   median %8.1f   p90 %8.1f" % (n, g.mean(), np.median(g), np.percentile(g, 90)))
+print("T=%d H=%d B=%d: fwd kernel %.3f ms  (%.2f us/step)" % (T, H, B, e0.elapsed_time(e1), e0.elapsed_time(e1) * 1e3 / T))
+n = min(T, 1024)
+S = ws[2048:2048 + n * 128].view(torch.int64).cpu().numpy().reshape(-1, 16)
+s, nxt = S[2:n - 1], S[3:n]
+seq = [("poll done -> fence.proxy.async done", 0, 8), ("fence -> TMA issued", 8, 9), ("TMA issued -> box0 landed", 9, 1),
+       ("box0 landed -> last box landed", 1, 10), ("last box landed -> MMAs+commit issued", 10, 2),
+       ("commit issued -> epilogue sees accumulators", 2, 3), ("tcgen05.ld + fold", 3, 11), ("DSMEM stores issued", 11, 12),
+       ("remote arrive (release.cluster) issued", 12, 4), ("all 4 slabs arrived", 4, 5), ("reduce + epilogue + h_t stores", 5, 6),
+       ("bar.sync + red.release issued", 6, 7)]
+tot = 0.0
+for name, a, b in seq:
+    g = (s[:, b] - s[:, a]).astype(np.float64)
+    print("%-46s mean %8.1f cyc   median %8.1f   p90 %8.1f" % (name, g.mean(), np.median(g), np.percentile(g, 90)))
     tot += g.mean()
-print("sum %.1f cycles per step" % tot)
+g = (nxt[:, 0] - s[:, 7]).astype(np.float64)
+print("%-46s mean %8.1f cyc   median %8.1f   p90 %8.1f" % ("published -> next step's poll done", g.mean(), np.median(g), np.percentile(g, 90)))
+print("sum %.0f cycles per step" % (tot + g.mean()))
