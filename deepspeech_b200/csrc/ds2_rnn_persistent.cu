@@ -6,44 +6,48 @@
 //   * the H output units are tiled by 128 (tcgen05 M=128), the batch is the MMA N dimension;
 //   * the reduction dimension is split over a thread-block cluster of 4 CTAs; each CTA loads its
 //     [128 x H/4] bf16 slice of U ONCE (TMA -> shared memory -> tcgen05.cp -> TMEM) and keeps it resident in
-//     tensor memory as the MMA's A operand for all T steps (a shared-memory A operand caps the MMA at the
-//     ~64 B/clk operand read: 72 clk per K=16 step instead of 16);
+//     tensor memory as the MMA's A operand for all T steps;
 //   * the batch is cut into independent 16-utterance chains ("instances") that share the resident U: each
-//     instance has its own control warp, 4 epilogue warps, barriers, accumulator columns and step counter,
-//     so one chain's grid-barrier / TMA latency is covered by the other chains' work;
-//   * each step of an instance: acquire the step counter -> TMA its K-slice of h_{t-1} (per 64-column box,
-//     MMAs issue as boxes land) -> tcgen05.mma into TMEM -> tcgen05.ld -> partial sums sent through distributed
-//     shared memory to the CTA that finishes those 32 rows (remote mbarrier arrive, no cluster-wide barrier)
-//     -> epilogue (add s*Wx_t + b, clip, length mask) -> bf16 h_t to global -> release-increment of the counter;
+//     instance has its own control warp, 4 loader/epilogue warps, barriers and accumulator columns, so one
+//     chain's memory latency is covered by the other chains' work;
+//   * NO grid barrier and no memory fence sits on the per-step critical path.  The output tensor is
+//     pre-filled with a bf16 NaN pattern (0xFFFF) that the kernel never produces; a consumer simply re-loads
+//     (ld.relaxed.gpu, 16 bytes) the rows of h_{t-1} it needs until none of the 8 values is the sentinel, and
+//     writes them into shared memory in the 128B-swizzled K-major layout the MMA descriptor expects.  Every
+//     element is written exactly once per launch, so there is no buffer reuse to order;
+//   * each step of an instance: poll-load its K-slice of h_{t-1} -> tcgen05.mma into TMEM -> tcgen05.ld ->
+//     partial sums pushed with st.async (completes a transaction barrier in the receiving CTA, no fence) to
+//     the cluster CTA that finishes those 32 rows -> epilogue (add s*Wx_t + b, clip, length mask) -> bf16
+//     h_t to global;
 //   * both directions run concurrently as independent groups of CTAs of the same launch.
-// The backward kernel is the same machine with A = U^T, B operand = dz_{t+1}, and the epilogue
+// The backward kernel is the same machine with A = U^T, moving operand dz_{t+1}, and the epilogue
 // dz_t = [0 < h_t < cap] * (dout_t + U^T dz_{t+1}).
+// Every spin loop is bounded by the device watchdog (common.cuh), so a protocol bug traps instead of hanging.
 #include <stdlib.h>
 
 #include "common.cuh"
 
 namespace ds2 {
 
-static constexpr int KS = 4;            // cluster size = K split
-static constexpr int BP = 16;           // utterances per instance (MMA N)
-static constexpr int INST_THREADS = 160;  // per instance: 1 control warp + 4 epilogue warps
+static constexpr int KS = 4;              // cluster size = K split
+static constexpr int BP = 16;             // utterances per instance (MMA N)
+static constexpr int INST_THREADS = 160;  // per instance: 1 control warp + 4 loader/epilogue warps
 static constexpr int MAX_NI = 4;
-static constexpr int MAX_NBOX = 9;      // K-slice <= 576 columns
+static constexpr int MAX_NBOX = 9;        // K-slice <= 576 columns
+static constexpr int MAX_UNITS = (BP * MAX_NBOX * 8 + 127) / 128;   // 16-byte units per loader thread
 
 struct RnnPersistParams {
   const float* add_in;     // fwd: wx [T,B,ND*H] ; bwd: dout [T,B,H]
   const float* bias;       // fwd: [ND,H]
   const int* lens;         // [B]
   const __nv_bfloat16* hs_in;   // bwd: hs [ND,T,B,H] (activation mask)
-  __nv_bfloat16* out;      // fwd: hs [ND,T,B,H] ; bwd: dz [T,B,ND*H]
-  unsigned int* ctr;       // [ND][NI] step counters, 32 uints apart
-  long long* prof;         // optional per-step clock64 stamps of CTA (0,0,0) instance 0 (DS2_RNN_PROF=1), 8 per step
+  __nv_bfloat16* out;      // fwd: hs [ND,T,B,H] ; bwd: dz [T,B,ND*H]   (also the moving operand of the next step)
+  long long* prof;         // optional per-step clock64 stamps of CTA (0,0,0) instance 0 (DS2_RNN_PROF=1), 16 per step
+  long out_row_pitch;      // elements between consecutive (t,b) rows of `out`
+  long out_dir_stride;     // element offset of direction d inside `out`
   int T, B, H, ND, reverse_mask;
   int NI;                  // instances = B / BP
   int tiles_m, ksl, nbox;  // M tiles per direction, K-slice length (multiple of 64), boxes per slice
-  int a_in_tmem;
-  int nacc;                // 4 or 8 independent accumulator tiles per instance: consecutive tcgen05.mma into ONE tile serialise on its ~60-cycle latency
-  int stagger;             // start offset (cycles) between the instances of a CTA so their per-step phases interleave
   float scale, cap;
 };
 
@@ -59,30 +63,25 @@ __device__ __forceinline__ uint32_t map_to_rank(uint32_t local_smem_addr, uint32
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
   return r;
 }
-__device__ __forceinline__ void st_cluster_v4(uint32_t addr, float a, float b, float c, float d) {
-  asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+// asynchronous 16-byte store into a cluster CTA's shared memory; completes 16 bytes on that CTA's mbarrier
+__device__ __forceinline__ void st_async_v4(uint32_t remote_addr, uint32_t remote_bar, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%2, %3, %4, %5}, [%1];"
+               ::"r"(remote_addr), "r"(remote_bar), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
-__device__ __forceinline__ void mbar_remote_arrive_release(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait_acq_cluster(uint64_t* bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
-  unsigned int v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+__device__ __forceinline__ uint4 ld_relaxed_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void red_release_add(unsigned int* p, unsigned int v) {
-  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ bool has_sentinel(uint32_t w) { return ((w & 0xFFFFu) == 0xFFFFu) || ((w >> 16) == 0xFFFFu); }
+__device__ __forceinline__ bool unit_ready(const uint4& v) {
+  return !(has_sentinel(v.x) || has_sentinel(v.y) || has_sentinel(v.z) || has_sentinel(v.w));
+}
+// never emit the "not written yet" pattern: a negative NaN payload 0xFFFF becomes the positive one
+__device__ __forceinline__ uint32_t scrub_sentinel(uint32_t w) {
+  if ((w & 0xFFFFu) == 0xFFFFu) w &= 0xFFFF7FFFu;
+  if ((w >> 16) == 0xFFFFu) w &= 0x7FFFFFFFu;
+  return w;
 }
 // smem (matrix descriptor, same format as the MMA operand descriptors) -> TMEM, 128 lanes x 256 bits
 __device__ __forceinline__ void tmem_cp_128x256b(uint32_t taddr, uint64_t sdesc) {
@@ -111,20 +110,20 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16])
 struct RnnSmem {
   uint32_t a_off, b_off, slab_off, bar_off, total;
 };
+static constexpr int BARS_PER_INST = 4;   // b_ready, mma_done, slab_full[2]
 __host__ __device__ inline RnnSmem rnn_smem_layout(int nbox, int NI) {
   RnnSmem s;
-  s.a_off = 0;                                            // nbox x [128 x 64] bf16 (SW128 K-major)
+  s.a_off = 0;                                            // nbox x [128 x 64] bf16 (SW128 K-major), staging for TMEM
   s.b_off = s.a_off + nbox * 16384;                       // NI x nbox x [16 x 64] bf16
-  s.slab_off = s.b_off + NI * nbox * (BP * 128);          // NI x KS x [32 x 16] fp32
-  s.bar_off = s.slab_off + NI * KS * 32 * BP * 4;         // mbarriers
-  s.total = s.bar_off + 8 * (2 + NI * (MAX_NBOX + 2)) + 16;
+  s.slab_off = s.b_off + NI * nbox * (BP * 128);          // NI x 2 x KS x [32 x 16] fp32
+  s.bar_off = s.slab_off + NI * 2 * KS * 32 * BP * 4;     // mbarriers
+  s.total = s.bar_off + 8 * (2 + NI * BARS_PER_INST) + 16;
   return s;
 }
 
-template <bool BWD, bool ATMEM>
+template <bool BWD>
 __global__ void __launch_bounds__(INST_THREADS * MAX_NI, 1)
-rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b0,
-                   const __grid_constant__ CUtensorMap tm_b1, RnnPersistParams p) {
+rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p) {
   extern __shared__ uint8_t rnn_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(rnn_smem_raw) + 1023) & ~uintptr_t(1023));
   const int NI = p.NI, nbox = p.nbox;
@@ -133,37 +132,34 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
   uint64_t* a_bar = bars;            // U slice landed in smem
   uint64_t* acp_bar = bars + 1;      // U slice copied into TMEM
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 + NI * (MAX_NBOX + 2));
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 + NI * BARS_PER_INST);
 
   const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const int inst = warp / 5, w_in = warp % 5;
-  uint64_t* h_bar = bars + 2 + inst * (MAX_NBOX + 2);       // [nbox] moving operand boxes landed (per step)
-  uint64_t* mma_bar = h_bar + MAX_NBOX;                     // accumulators ready (per step)
-  uint64_t* slab_bar = h_bar + MAX_NBOX + 1;                // KS partial slabs arrived (per step)
+  uint64_t* b_ready = bars + 2 + inst * BARS_PER_INST;      // moving operand of this step is in shared memory
+  uint64_t* mma_bar = b_ready + 1;                          // accumulators ready
+  uint64_t* slab_bar = b_ready + 2;                         // [2] partial slabs of step parity arrived (tx bytes)
   uint8_t* sB = smem + L.b_off + inst * nbox * (BP * 128);
-  float* slab = reinterpret_cast<float*>(smem + L.slab_off) + inst * KS * 32 * BP;
+  float* slab = reinterpret_cast<float*>(smem + L.slab_off) + inst * 2 * KS * 32 * BP;
 
   const uint32_t rank = cluster_ctarank();                  // K slice owned by this CTA, rows it finishes
   const int mt = blockIdx.y, d = blockIdx.z;
   const int m0 = mt * 128;
   const int rev = (p.reverse_mask >> d) & 1;
   const int T = p.T, H = p.H, ND = p.ND, Bn = p.B;
-  const CUtensorMap* tm_b = d ? &tm_b1 : &tm_b0;
-  unsigned int* ctr = p.ctr + (d * NI + inst) * 32;
-  const unsigned int ctas_per_dir = KS * p.tiles_m;
   const bool prof_cta = p.prof && (blockIdx.x + blockIdx.y + blockIdx.z == 0) && inst == 0;
-  const int acols = ATMEM ? nbox * 32 : 0;            // TMEM columns holding U (8 per K=16 chunk)
+  const int acols = nbox * 32;                              // TMEM columns holding U (8 per K=16 chunk)
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tm_a);
-    tma_prefetch_desc(tm_b);
     mbar_init(a_bar, 1);
     mbar_init(acp_bar, 1);
     for (int i = 0; i < NI; ++i) {
-      uint64_t* hb = bars + 2 + i * (MAX_NBOX + 2);
-      for (int j = 0; j < nbox; ++j) mbar_init(hb + j, 1);
-      mbar_init(hb + MAX_NBOX, 1);
-      mbar_init(hb + MAX_NBOX + 1, KS);
+      uint64_t* bb = bars + 2 + i * BARS_PER_INST;
+      mbar_init(bb, 128);          // every loader thread arrives once per step
+      mbar_init(bb + 1, 1);        // tcgen05.commit
+      mbar_init(bb + 2, 1);        // one arrive.expect_tx per use + the st.async bytes
+      mbar_init(bb + 3, 1);
     }
     fence_barrier_init();
   }
@@ -172,77 +168,48 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int nacc = p.nacc;
-  const uint32_t d_tmem = tmem_base + acols + inst * nacc * BP;
-  const uint32_t acc_hi = (nacc > 4) ? 4u * BP : 0u;         // odd boxes use accumulators 4..7 when there are 8
-  // every CTA of the cluster must have initialised its barriers before any remote arrive / DSMEM store
+  const uint32_t d_tmem = tmem_base + acols + inst * BP;
+  // every CTA of the cluster must have initialised its barriers before any remote st.async
   cluster_arrive();
   cluster_wait();
 
   if (w_in == 0) {
-    // =========================== control warp of this instance: TMA + MMA issue ===========================
+    // =========================== control warp of this instance: MMA issue ===========================
     if (inst == 0 && elect_one_sync()) {
       mbar_arrive_expect_tx(a_bar, nbox * 16384);
       for (int i = 0; i < nbox; ++i) tma_load_2d(sA + i * 16384, &tm_a, a_bar, rank * p.ksl + i * 64, d * H + m0);
       mbar_wait(a_bar, 0, 10);
-      if (ATMEM) {
-        tc_fence_after();
-        const uint32_t a0 = smem_u32(sA);
-        for (int c = 0; c < nbox * 4; ++c)
-          tmem_cp_128x256b(tmem_base + c * 8, umma_smem_desc_sw128(a0 + (c >> 2) * 16384 + (c & 3) * 32, 16, 1024));
-      }
-      umma_commit(acp_bar);          // arrives when the copies (if any) have completed
+      tc_fence_after();
+      const uint32_t a0 = smem_u32(sA);
+      for (int c = 0; c < nbox * 4; ++c)
+        tmem_cp_128x256b(tmem_base + c * 8, umma_smem_desc_sw128(a0 + (c >> 2) * 16384 + (c & 3) * 32, 16, 1024));
+      umma_commit(acp_bar);          // arrives when the copies have completed
     }
     __syncwarp();
-    mbar_wait(acp_bar, 0, 11);       // every instance's control warp: U is in place
+    mbar_wait(acp_bar, 0, 11);       // every instance's control warp: U is resident in TMEM
     tc_fence_after();
     const uint32_t idesc = umma_idesc_bf16(128, BP, 0, 0);
-    if (inst > 0 && p.stagger > 0) {   // de-phase the instances: their TMA / MMA / DSMEM bursts then do not collide
-      const long long t0 = dev_clock();
-      while (dev_clock() - t0 < (long long)inst * p.stagger) {}
-    }
+    const uint32_t b0 = smem_u32(sB);
     uint32_t ph = 0;
     for (int step = 1; step < T; ++step) {
-      const int t = BWD ? (rev ? step : T - 1 - step) : (rev ? T - 1 - step : step);
-      const int tsrc = BWD ? (rev ? t - 1 : t + 1) : (rev ? t + 1 : t - 1);   // step whose result feeds this one
+      mbar_wait(b_ready, ph, 30);    // loaders have written h_{t-1} (generic proxy) and fenced it to the async proxy
+      tc_fence_after();
       if (elect_one_sync()) {
-        // wait until every CTA of this direction has published the previous step of this instance
-        const unsigned int need = ctas_per_dir * (unsigned int)step;
-        if (ld_acquire_u32(ctr) < need) {
-          SpinGuard g;
-          while (ld_acquire_u32(ctr) < need) g.check(20);
-        }
         if (prof_cta && step < 1024) p.prof[step * 16 + 0] = dev_clock();
-        asm volatile("fence.proxy.async;" ::: "memory");      // generic-proxy acquire -> async-proxy (TMA) reads
-        if (prof_cta && step < 1024) p.prof[step * 16 + 8] = dev_clock();
         for (int i = 0; i < nbox; ++i) {
-          mbar_arrive_expect_tx(h_bar + i, BP * 128);
-          tma_load_2d(sB + i * (BP * 128), tm_b, h_bar + i, rank * p.ksl + i * 64, tsrc * Bn + inst * BP);
-        }
-        if (prof_cta && step < 1024) p.prof[step * 16 + 9] = dev_clock();
-        const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
-        for (int i = 0; i < nbox; ++i) {
-          mbar_wait(h_bar + i, ph, 30);
-          tc_fence_after();
-          if (i == 0 && prof_cta && step < 1024) p.prof[step * 16 + 1] = dev_clock();
-          if (i == nbox - 1 && prof_cta && step < 1024) p.prof[step * 16 + 10] = dev_clock();
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const uint64_t bdesc = umma_smem_desc_sw128(b0 + i * (BP * 128) + k * 32, 16, 1024);
-            if (ATMEM)
-              umma_bf16_ts(d_tmem + k * BP + (i & 1) * acc_hi, tmem_base + (i * 4 + k) * 8, bdesc, idesc, (i > (acc_hi ? 1 : 0)) ? 1u : 0u);
-            else
-              umma_bf16(d_tmem + k * BP + (i & 1) * acc_hi, umma_smem_desc_sw128(a0 + i * 16384 + k * 32, 16, 1024), bdesc, idesc, (i > (acc_hi ? 1 : 0)) ? 1u : 0u);
-          }
+          for (int k = 0; k < 4; ++k)
+            umma_bf16_ts(d_tmem, tmem_base + (i * 4 + k) * 8, umma_smem_desc_sw128(b0 + i * (BP * 128) + k * 32, 16, 1024), idesc,
+                         (i > 0 || k > 0) ? 1u : 0u);
         }
         umma_commit(mma_bar);
-        if (prof_cta && step < 1024) p.prof[step * 16 + 2] = dev_clock();
+        if (prof_cta && step < 1024) p.prof[step * 16 + 1] = dev_clock();
       }
       __syncwarp();
       ph ^= 1;
     }
   } else {
-    // =========================== epilogue warps of this instance ===========================
+    // =========================== loader + epilogue warps of this instance ===========================
     const int q = warp & 3;                      // TMEM lane quarter = rows [32q, 32q+32) of the tile
     const int et = (w_in - 1) * 32 + lane;       // 0..127
     const int bl = et % BP;                      // utterance within the instance
@@ -256,9 +223,15 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
     const int len_b = p.lens[b];
     const uint32_t slab_local = smem_u32(slab);
     const uint32_t slab_bar_local = smem_u32(slab_bar);
+    // loader role: 16-byte units (8 consecutive k of one utterance) of this CTA's K slice
+    const int cpr = p.ksl / 8;                   // units per utterance row
+    const int nunits = BP * cpr;
+    const __nv_bfloat16* src_dir = p.out + (size_t)d * p.out_dir_stride;
     uint32_t ph = 0;
     for (int step = 0; step < T; ++step) {
       const int t = BWD ? (rev ? step : T - 1 - step) : (rev ? T - 1 - step : step);
+      const int tsrc = BWD ? (rev ? t - 1 : t + 1) : (rev ? t + 1 : t - 1);   // step whose result feeds this one
+      const bool pr = prof_cta && et == 0 && step < 1024;
       // prefetch the additive term (s*Wx_t or dout_t) and, for the backward, h_t for the mask
       float4 add = make_float4(0.f, 0.f, 0.f, 0.f);
       uint2 hm = make_uint2(0u, 0u);
@@ -269,49 +242,84 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
         if (BWD) hm = *reinterpret_cast<const uint2*>(p.hs_in + (((size_t)d * T + t) * Bn + b) * H + j);
       }
       float acc[4] = {0.f, 0.f, 0.f, 0.f};
-      const bool pr = prof_cta && et == 0 && step < 1024;
       if (step > 0) {
+        const int par = step & 1;
+        if (et == 0) mbar_arrive_expect_tx(slab_bar + par, KS * 32 * BP * 4);     // arm this step's slab barrier
+        // ---- loader: poll h_{t-1}[inst's utterances][this CTA's K slice] until written, stage into smem
+        if (pr) p.prof[step * 16 + 8] = dev_clock();
+        {
+          const __nv_bfloat16* rows = src_dir + ((size_t)tsrc * Bn + inst * BP) * p.out_row_pitch + (size_t)rank * p.ksl;
+          uint4 v[MAX_UNITS];
+          uint32_t pending = 0;
+#pragma unroll
+          for (int m = 0; m < MAX_UNITS; ++m) {
+            const int u = et + 128 * m;
+            v[m] = make_uint4(0u, 0u, 0u, 0u);
+            if (u < nunits) {
+              const int ub = u / cpr, uc = u - ub * cpr;
+              if ((int)rank * p.ksl + uc * 8 < H) {
+                v[m] = ld_relaxed_v4(rows + (size_t)ub * p.out_row_pitch + uc * 8);
+                if (!unit_ready(v[m])) pending |= 1u << m;
+              }
+            }
+          }
+          if (pending) {
+            SpinGuard g;
+            while (pending) {
+#pragma unroll
+              for (int m = 0; m < MAX_UNITS; ++m) {
+                if (pending & (1u << m)) {
+                  const int u = et + 128 * m;
+                  const int ub = u / cpr, uc = u - ub * cpr;
+                  v[m] = ld_relaxed_v4(rows + (size_t)ub * p.out_row_pitch + uc * 8);
+                  if (unit_ready(v[m])) pending &= ~(1u << m);
+                }
+              }
+              g.check(20);
+            }
+          }
+          if (pr) p.prof[step * 16 + 9] = dev_clock();
+#pragma unroll
+          for (int m = 0; m < MAX_UNITS; ++m) {
+            const int u = et + 128 * m;
+            if (u < nunits) {
+              const int ub = u / cpr, uc = u - ub * cpr;
+              // box (uc/8) of [16 rows x 128 B], 16-byte chunk (uc%8) XOR-swizzled with the row (SWIZZLE_128B)
+              uint8_t* dst = sB + (uc >> 3) * (BP * 128) + ub * 128 + (((uc & 7) ^ (ub & 7)) << 4);
+              *reinterpret_cast<uint4*>(dst) = v[m];
+            }
+          }
+          fence_proxy_async();       // generic-proxy smem writes -> visible to the tensor core (async proxy)
+          mbar_arrive(b_ready);
+        }
+        if (pr) p.prof[step * 16 + 10] = dev_clock();
+        // ---- epilogue part 1: partial sums of this CTA's K slice -> the CTA that finishes those rows
         mbar_wait(mma_bar, ph, 40);
         tc_fence_after();
         if (pr) p.prof[step * 16 + 3] = dev_clock();
-        // send this warp's 32 rows x 16 partial sums to the CTA that finishes those rows (cluster rank q)
         uint32_t r[16];
         tmem_ld_32x16(d_tmem + (static_cast<uint32_t>(q * 32) << 16), r);
-        {
-          const int nfold = (nacc > 4 && nbox < 2) ? 4 : nacc;   // tiles actually written this step
-          for (int a = 1; a < nfold; ++a) {                     // fold the independent accumulator tiles
-            uint32_t r2[16];
-            tmem_ld_wait();
-            tmem_ld_32x16(d_tmem + a * BP + (static_cast<uint32_t>(q * 32) << 16), r2);
-            tmem_ld_wait();
-#pragma unroll
-            for (int e = 0; e < 16; ++e) r[e] = __float_as_uint(__uint_as_float(r[e]) + __uint_as_float(r2[e]));
-          }
-        }
         tmem_ld_wait();
-        if (pr) p.prof[step * 16 + 11] = dev_clock();
-        const uint32_t dst = map_to_rank(slab_local, (uint32_t)q) + ((rank * 32 + lane) * BP) * 4;
-#pragma unroll
-        for (int c = 0; c < 4; ++c)
-          st_cluster_v4(dst + c * 16, __uint_as_float(r[4 * c]), __uint_as_float(r[4 * c + 1]), __uint_as_float(r[4 * c + 2]),
-                        __uint_as_float(r[4 * c + 3]));
-        if (pr) p.prof[step * 16 + 12] = dev_clock();
         tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_remote_arrive_release(map_to_rank(slab_bar_local, (uint32_t)q));
-        if (pr) p.prof[step * 16 + 4] = dev_clock();
-        if (!mbar_try_wait_acq_cluster(slab_bar, ph)) {
-          SpinGuard g;
-          while (!mbar_try_wait_acq_cluster(slab_bar, ph)) g.check(50);
+        if (pr) p.prof[step * 16 + 11] = dev_clock();
+        {
+          const uint32_t off = ((par * KS + rank) * 32 + lane) * BP * 4;
+          const uint32_t dst = map_to_rank(slab_local, (uint32_t)q) + off;
+          const uint32_t rbar = map_to_rank(slab_bar_local + par * 8, (uint32_t)q);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) st_async_v4(dst + c * 16, rbar, r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
         }
-        ph ^= 1;
+        if (pr) p.prof[step * 16 + 12] = dev_clock();
+        // ---- epilogue part 2: wait for the KS slabs of this step, reduce
+        mbar_wait(slab_bar + par, (uint32_t)(((step - 1) >> 1) & 1), 50);   // k-th use of this parity's barrier
         if (pr) p.prof[step * 16 + 5] = dev_clock();
-        // reduce the KS partial slabs for this thread's (utterance, 4 rows)
+        const float* sl = slab + par * KS * 32 * BP;
 #pragma unroll
         for (int s = 0; s < KS; ++s) {
-          const float* sp = slab + (s * 32 + 4 * jg) * BP + bl;
+          const float* sp = sl + (s * 32 + 4 * jg) * BP + bl;
           acc[0] += sp[0]; acc[1] += sp[BP]; acc[2] += sp[2 * BP]; acc[3] += sp[3 * BP];
         }
+        ph ^= 1;
       }
       if (jvalid) {
         const bool live = t < len_b;
@@ -332,19 +340,13 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_consta
           }
         }
         uint2 pk;
-        __nv_bfloat162 b0 = __floats2bfloat162_rn(o[0], o[1]), b1 = __floats2bfloat162_rn(o[2], o[3]);
-        pk.x = *reinterpret_cast<uint32_t*>(&b0);
-        pk.y = *reinterpret_cast<uint32_t*>(&b1);
-        __nv_bfloat16* dstp = BWD ? p.out + ((size_t)t * Bn + b) * ND * H + (size_t)d * H + j
-                                  : p.out + (((size_t)d * T + t) * Bn + b) * H + j;
-        *reinterpret_cast<uint2*>(dstp) = pk;
+        __nv_bfloat162 b0v = __floats2bfloat162_rn(o[0], o[1]), b1v = __floats2bfloat162_rn(o[2], o[3]);
+        pk.x = scrub_sentinel(*reinterpret_cast<uint32_t*>(&b0v));
+        pk.y = scrub_sentinel(*reinterpret_cast<uint32_t*>(&b1v));
+        __nv_bfloat16* dstp = p.out + (size_t)d * p.out_dir_stride + ((size_t)t * Bn + b) * p.out_row_pitch + j;
+        *reinterpret_cast<uint2*>(dstp) = pk;     // this store IS the publication: consumers poll these bytes
       }
       if (pr) p.prof[step * 16 + 6] = dev_clock();
-      // publish: the instance's 128 epilogue threads' stores -> one release increment of its step counter
-      // (CTA-level barrier orders their stores before thread 0's gpu-scope release: cumulativity)
-      asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
-      if (et == 0) red_release_add(ctr, 1u);
-      if (pr) p.prof[step * 16 + 7] = dev_clock();
     }
   }
   // no CTA may exit while a peer can still write into its shared memory
@@ -367,7 +369,7 @@ static int persist_geometry(int B, int H, int ND, int* tiles_m, int* ksl, int* n
   const int nb = l / 64;
   if (nb > MAX_NBOX) return 0;
   const int n_inst = B / BP;
-  if (nb * 32 + n_inst * 4 * BP > 512) return 0;   // TMEM columns: resident U + accumulators
+  if (nb * 32 + n_inst * BP > 512) return 0;   // TMEM columns: resident U + accumulators
   const size_t bytes = rnn_smem_layout(nb, n_inst).total + 1024;
   if (bytes > 225 * 1024) return 0;
   if (KS * tm * ND > 128) return 0;           // must be co-resident in clusters of 4 (148 SMs, 1 CTA / SM)
@@ -381,26 +383,21 @@ static int persist_geometry(int B, int H, int ND, int* tiles_m, int* ksl, int* n
 
 int rnn_persist_supported(int B, int H, int ND) { return persist_geometry(B, H, ND, nullptr, nullptr, nullptr, nullptr, nullptr); }
 
-static constexpr size_t WS_CTR_BYTES = 2048;     // ND x MAX_NI counters, one 128-byte line each
 static constexpr size_t WS_PROF_BYTES = 131072;
 
 size_t rnn_persist_workspace_bytes(int T, int B, int H, int ND) {
   (void)T; (void)B;
-  // step counters + optional profile stamps + room for U^T (bf16) used by the backward
-  return WS_CTR_BYTES + WS_PROF_BYTES + (size_t)ND * H * H * 2;
+  // optional profile stamps + room for U^T (bf16) used by the backward
+  return WS_PROF_BYTES + (size_t)ND * H * H * 2;
 }
 
 template <bool BWD>
-static int persist_launch(const CUtensorMap& ta, const CUtensorMap& tb0, const CUtensorMap& tb1, RnnPersistParams& p, size_t smem,
-                          cudaStream_t st) {
-  p.a_in_tmem = getenv("DS2_RNN_A_SMEM") ? 0 : 1;
-  p.nacc = ((p.a_in_tmem ? p.nbox * 32 : 0) + p.NI * 8 * BP <= 512 && !getenv("DS2_RNN_NACC4")) ? 8 : 4;
-  p.stagger = getenv("DS2_RNN_STAGGER") ? atoi(getenv("DS2_RNN_STAGGER")) : 0;
-  auto kern = p.a_in_tmem ? rnn_persist_kernel<BWD, true> : rnn_persist_kernel<BWD, false>;
-  static bool attr_done[2][2] = {{false, false}, {false, false}};
-  if (!attr_done[BWD][p.a_in_tmem]) {
+static int persist_launch(const CUtensorMap& ta, RnnPersistParams& p, size_t smem, cudaStream_t st) {
+  auto kern = rnn_persist_kernel<BWD>;
+  static bool attr_done[2] = {false, false};
+  if (!attr_done[BWD]) {
     DS2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
-    attr_done[BWD][p.a_in_tmem] = true;
+    attr_done[BWD] = true;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(KS, p.tiles_m, p.ND);
@@ -412,32 +409,29 @@ static int persist_launch(const CUtensorMap& ta, const CUtensorMap& tb0, const C
   attrs[0].val.clusterDim.x = KS;
   attrs[0].val.clusterDim.y = 1;
   attrs[0].val.clusterDim.z = 1;
-  attrs[1].id = cudaLaunchAttributeCooperative;       // all CTAs co-resident (they spin on each other)
+  attrs[1].id = cudaLaunchAttributeCooperative;       // all CTAs co-resident (they wait on each other's data)
   attrs[1].val.cooperative = 1;
   cfg.attrs = attrs;
   cfg.numAttrs = getenv("DS2_RNN_NO_COOP") ? 1 : 2;   // profilers cannot replay cooperative launches
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb0, tb1, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, p);
   if (e != cudaSuccess && cfg.numAttrs == 2) {
     // some driver versions reject cooperative + cluster launches: the grid (<= 128 CTAs, 1 per SM)
     // fits the device anyway, so fall back to a plain cluster launch
     (void)cudaGetLastError();
     cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, kern, ta, tb0, tb1, p);
+    e = cudaLaunchKernelEx(&cfg, kern, ta, p);
   }
   if (e != cudaSuccess) return cuda_fail(e, BWD ? "rnn_persist_kernel<bwd>" : "rnn_persist_kernel<fwd>");
   count_launch();
   return DS2_OK;
 }
 
-static int persist_common(RnnPersistParams& p, size_t* smem, int T, int B, int H, int ND, void* ws, size_t ws_bytes, const char* who,
-                          cudaStream_t st) {
+static int persist_common(RnnPersistParams& p, size_t* smem, int T, int B, int H, int ND, void* ws, size_t ws_bytes, const char* who) {
   DS2_REQUIRE(persist_geometry(B, H, ND, &p.tiles_m, &p.ksl, &p.nbox, &p.NI, smem), DS2_ERR_UNSUPPORTED,
               "%s: persistent kernel does not take B=%d H=%d ND=%d", who, B, H, ND);
   const size_t need = rnn_persist_workspace_bytes(T, B, H, ND);
   DS2_REQUIRE(ws && ws_bytes >= need, DS2_ERR_WORKSPACE, "%s: workspace of %zu bytes required", who, need);
-  DS2_CUDA(cudaMemsetAsync(ws, 0, WS_CTR_BYTES, st));
-  p.ctr = static_cast<unsigned int*>(ws);
-  p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(static_cast<char*>(ws) + WS_CTR_BYTES) : nullptr;
+  p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(ws) : nullptr;
   return DS2_OK;
 }
 
@@ -445,19 +439,17 @@ int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const floa
                          int H, int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
   RnnPersistParams p = {};
   size_t smem;
-  int rc = persist_common(p, &smem, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_fwd", st);
+  int rc = persist_common(p, &smem, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_fwd");
   if (rc) return rc;
-  CUtensorMap ta, tb0, tb1;
+  CUtensorMap ta;
   rc = make_tmap_2d_bf16(&ta, u, H, (uint64_t)ND * H, H, 64, 128);
   if (rc) return rc;
-  const __nv_bfloat16* hsb = static_cast<const __nv_bfloat16*>(hs);
-  rc = make_tmap_2d_bf16(&tb0, hsb, H, (uint64_t)T * B, H, 64, BP);
-  if (rc) return rc;
-  rc = make_tmap_2d_bf16(&tb1, hsb + (ND > 1 ? (size_t)T * B * H : 0), H, (uint64_t)T * B, H, 64, BP);
-  if (rc) return rc;
+  // "not written yet" pattern for the consumers' polling loads (see the header comment)
+  DS2_CUDA(cudaMemsetAsync(hs, 0xFF, (size_t)ND * T * B * H * 2, st));
   p.add_in = wx; p.bias = bias; p.lens = lens; p.hs_in = nullptr; p.out = static_cast<__nv_bfloat16*>(hs);
+  p.out_row_pitch = H; p.out_dir_stride = (long)T * B * H;
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = scale; p.cap = cap;
-  return persist_launch<false>(ta, tb0, tb1, p, smem, st);
+  return persist_launch<false>(ta, p, smem, st);
 }
 
 // The backward contraction is U^T dz: U is transposed per direction into the workspace first
@@ -466,25 +458,22 @@ int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, cons
                          int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
   RnnPersistParams p = {};
   size_t smem;
-  int rc = persist_common(p, &smem, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_bwd", st);
+  int rc = persist_common(p, &smem, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_bwd");
   if (rc) return rc;
-  __nv_bfloat16* ut = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + WS_CTR_BYTES + WS_PROF_BYTES);
+  __nv_bfloat16* ut = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + WS_PROF_BYTES);
   for (int d = 0; d < ND; ++d) {
     rc = ds2_transpose(static_cast<const __nv_bfloat16*>(u) + (size_t)d * H * H, DS2_BF16, H, H, H, ut + (size_t)d * H * H, DS2_BF16, H, st);
     if (rc) return rc;
   }
-  CUtensorMap ta, tb0, tb1;
+  CUtensorMap ta;
   rc = make_tmap_2d_bf16(&ta, ut, H, (uint64_t)ND * H, H, 64, 128);
   if (rc) return rc;
-  const __nv_bfloat16* dzb = static_cast<const __nv_bfloat16*>(dz);
-  rc = make_tmap_2d_bf16(&tb0, dzb, H, (uint64_t)T * B, (uint64_t)ND * H, 64, BP);
-  if (rc) return rc;
-  rc = make_tmap_2d_bf16(&tb1, dzb + (ND > 1 ? H : 0), H, (uint64_t)T * B, (uint64_t)ND * H, 64, BP);
-  if (rc) return rc;
+  DS2_CUDA(cudaMemsetAsync(dz, 0xFF, (size_t)T * B * ND * H * 2, st));
   p.add_in = dout; p.bias = nullptr; p.lens = lens; p.hs_in = static_cast<const __nv_bfloat16*>(hs);
   p.out = static_cast<__nv_bfloat16*>(dz);
+  p.out_row_pitch = (long)ND * H; p.out_dir_stride = H;
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = 1.f; p.cap = cap;
-  return persist_launch<true>(ta, tb0, tb1, p, smem, st);
+  return persist_launch<true>(ta, p, smem, st);
 }
 
 }  // namespace ds2
