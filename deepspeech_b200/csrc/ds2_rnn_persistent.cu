@@ -266,15 +266,18 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
           if (pending) {
             SpinGuard g;
             while (pending) {
+              // re-issue every pending unit first (loads in flight together), then test them
 #pragma unroll
               for (int m = 0; m < MAX_UNITS; ++m) {
                 if (pending & (1u << m)) {
                   const int u = et + 128 * m;
                   const int ub = u / cpr, uc = u - ub * cpr;
                   v[m] = ld_relaxed_v4(rows + (size_t)ub * p.out_row_pitch + uc * 8);
-                  if (unit_ready(v[m])) pending &= ~(1u << m);
                 }
               }
+#pragma unroll
+              for (int m = 0; m < MAX_UNITS; ++m)
+                if ((pending & (1u << m)) && unit_ready(v[m])) pending &= ~(1u << m);
               g.check(20);
             }
           }
@@ -289,7 +292,9 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
               *reinterpret_cast<uint4*>(dst) = v[m];
             }
           }
+          if (pr) p.prof[step * 16 + 13] = dev_clock();
           fence_proxy_async();       // generic-proxy smem writes -> visible to the tensor core (async proxy)
+          if (pr) p.prof[step * 16 + 14] = dev_clock();
           mbar_arrive(b_ready);
         }
         if (pr) p.prof[step * 16 + 10] = dev_clock();

@@ -35,7 +35,7 @@ print("T=%d H=%d B=%d: fwd kernel %.3f ms  (%.2f us/step)" % (T, H, B, e0.elapse
 n = min(T, 1024)
 S = ws[0:n * 128].view(torch.int64).cpu().numpy().reshape(-1, 16)
 s, nxt = S[2:n - 1], S[3:n]
-seq = [("poll-load h_{t-1} slice (all units ready)", 8, 9), ("st.shared + fence.proxy + arrive", 9, 10),
+seq = [("poll-load h_{t-1} slice (all units ready)", 8, 9), ("swizzled st.shared", 9, 13), ("fence.proxy.async.shared::cta", 13, 14), ("mbarrier.arrive", 14, 10),
        ("loaders arrived -> control sees b_ready", 10, 0), ("MMAs + commit issued", 0, 1), ("commit -> epilogue sees accumulators", 1, 3),
        ("tcgen05.ld", 3, 11), ("st.async partial slabs issued", 11, 12), ("all 4 slabs arrived", 12, 5),
        ("reduce + epilogue + h_t store issued", 5, 6)]
