@@ -349,7 +349,8 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
         pk.x = scrub_sentinel(*reinterpret_cast<uint32_t*>(&b0v));
         pk.y = scrub_sentinel(*reinterpret_cast<uint32_t*>(&b1v));
         __nv_bfloat16* dstp = p.out + (size_t)d * p.out_dir_stride + ((size_t)t * Bn + b) * p.out_row_pitch + j;
-        *reinterpret_cast<uint2*>(dstp) = pk;     // this store IS the publication: consumers poll these bytes
+        // this store IS the publication (consumers poll these bytes): gpu-scope store, not a lazily drained weak one
+        asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(dstp), "r"(pk.x), "r"(pk.y) : "memory");
       }
       if (pr) p.prof[step * 16 + 6] = dev_clock();
     }
