@@ -48,6 +48,7 @@ struct RnnPersistParams {
   int T, B, H, ND, reverse_mask;
   int NI;                  // instances = B / BP
   int tiles_m, ksl, nbox;  // M tiles per direction, K-slice length (multiple of 64), boxes per slice
+  int poll_ns;             // back-off between polling rounds
   float scale, cap;
 };
 
@@ -251,6 +252,24 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
           const __nv_bfloat16* rows = src_dir + ((size_t)tsrc * Bn + inst * BP) * p.out_row_pitch + (size_t)rank * p.ksl;
           uint4 v[MAX_UNITS];
           uint32_t pending = 0;
+          // Probe ONE unit with a throttled loop first: a tight 128-thread x 7-load spin floods the SM's
+          // load/store path (and L2) and slows the other instance's stores, DSMEM pushes and the producers.
+          {
+            const int ub = et / cpr, uc = et - ub * cpr;          // unit m = 0 of this thread (always < nunits)
+            const bool valid0 = (int)rank * p.ksl + uc * 8 < H;
+            if (valid0) {
+              const void* a0p = rows + (size_t)ub * p.out_row_pitch + uc * 8;
+              uint4 pv = ld_relaxed_v4(a0p);
+              if (!unit_ready(pv)) {
+                SpinGuard g;
+                do {
+                  __nanosleep(p.poll_ns);
+                  pv = ld_relaxed_v4(a0p);
+                  g.check(21);
+                } while (!unit_ready(pv));
+              }
+            }
+          }
 #pragma unroll
           for (int m = 0; m < MAX_UNITS; ++m) {
             const int u = et + 128 * m;
@@ -259,13 +278,17 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
               const int ub = u / cpr, uc = u - ub * cpr;
               if ((int)rank * p.ksl + uc * 8 < H) {
                 v[m] = ld_relaxed_v4(rows + (size_t)ub * p.out_row_pitch + uc * 8);
-                if (!unit_ready(v[m])) pending |= 1u << m;
+                pending |= 1u << m;
               }
             }
           }
+#pragma unroll
+          for (int m = 0; m < MAX_UNITS; ++m)
+            if ((pending & (1u << m)) && unit_ready(v[m])) pending &= ~(1u << m);
           if (pending) {
             SpinGuard g;
             while (pending) {
+              __nanosleep(p.poll_ns);
               // re-issue every pending unit first (loads in flight together), then test them
 #pragma unroll
               for (int m = 0; m < MAX_UNITS; ++m) {
@@ -437,6 +460,7 @@ static int persist_common(RnnPersistParams& p, size_t* smem, int T, int B, int H
               "%s: persistent kernel does not take B=%d H=%d ND=%d", who, B, H, ND);
   const size_t need = rnn_persist_workspace_bytes(T, B, H, ND);
   DS2_REQUIRE(ws && ws_bytes >= need, DS2_ERR_WORKSPACE, "%s: workspace of %zu bytes required", who, need);
+  p.poll_ns = getenv("DS2_RNN_POLL_NS") ? atoi(getenv("DS2_RNN_POLL_NS")) : 100;
   p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(ws) : nullptr;
   return DS2_OK;
 }
