@@ -10,15 +10,15 @@
 //   * the batch is cut into independent 16-utterance chains ("instances") that share the resident U: each
 //     instance has its own control warp, 4 loader/epilogue warps, barriers and accumulator columns, so one
 //     chain's memory latency is covered by the other chains' work;
-//   * NO grid barrier and no memory fence sits on the per-step critical path.  The output tensor is
-//     pre-filled with a bf16 NaN pattern (0xFFFF) that the kernel never produces; a consumer simply re-loads
-//     (ld.relaxed.gpu, 16 bytes) the rows of h_{t-1} it needs until none of the 8 values is the sentinel, and
-//     writes them into shared memory in the 128B-swizzled K-major layout the MMA descriptor expects.  Every
-//     element is written exactly once per launch, so there is no buffer reuse to order;
-//   * each step of an instance: poll-load its K-slice of h_{t-1} -> tcgen05.mma into TMEM -> tcgen05.ld ->
+//   * timesteps are ordered per (direction, instance) by a release/acquire step counter in global memory:
+//     one thread per instance acquires it, then the instance's 128 loader threads fetch their K-slice of
+//     h_{t-1} with ordinary 16-byte loads and write it into shared memory in the 128B-swizzled K-major layout
+//     the MMA descriptor expects (a TMA of the 7 thin [16 x 64] boxes measured ~2500 clk + a 700 clk
+//     cross-proxy fence; the loads + a shared-memory-only proxy fence take a fraction of that);
+//   * each step of an instance: acquire -> load h_{t-1} slice -> tcgen05.mma into TMEM -> tcgen05.ld ->
 //     partial sums pushed with st.async (completes a transaction barrier in the receiving CTA, no fence) to
 //     the cluster CTA that finishes those 32 rows -> epilogue (add s*Wx_t + b, clip, length mask) -> bf16
-//     h_t to global;
+//     h_t to global -> release-increment of the counter;
 //   * both directions run concurrently as independent groups of CTAs of the same launch.
 // The backward kernel is the same machine with A = U^T, moving operand dz_{t+1}, and the epilogue
 // dz_t = [0 < h_t < cap] * (dout_t + U^T dz_{t+1}).
@@ -42,13 +42,13 @@ struct RnnPersistParams {
   const int* lens;         // [B]
   const __nv_bfloat16* hs_in;   // bwd: hs [ND,T,B,H] (activation mask)
   __nv_bfloat16* out;      // fwd: hs [ND,T,B,H] ; bwd: dz [T,B,ND*H]   (also the moving operand of the next step)
+  unsigned int* ctr;       // [ND][NI] step counters, 32 uints apart
   long long* prof;         // optional per-step clock64 stamps of CTA (0,0,0) instance 0 (DS2_RNN_PROF=1), 16 per step
   long out_row_pitch;      // elements between consecutive (t,b) rows of `out`
   long out_dir_stride;     // element offset of direction d inside `out`
   int T, B, H, ND, reverse_mask;
   int NI;                  // instances = B / BP
   int tiles_m, ksl, nbox;  // M tiles per direction, K-slice length (multiple of 64), boxes per slice
-  int poll_ns;             // back-off between polling rounds
   float scale, cap;
 };
 
@@ -73,6 +73,14 @@ __device__ __forceinline__ uint4 ld_relaxed_v4(const void* p) {
   uint4 v;
   asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
+}
+__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_add(unsigned int* p, unsigned int v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ bool has_sentinel(uint32_t w) { return ((w & 0xFFFFu) == 0xFFFFu) || ((w >> 16) == 0xFFFFu); }
 __device__ __forceinline__ bool unit_ready(const uint4& v) {
@@ -148,6 +156,8 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
   const int m0 = mt * 128;
   const int rev = (p.reverse_mask >> d) & 1;
   const int T = p.T, H = p.H, ND = p.ND, Bn = p.B;
+  unsigned int* ctr = p.ctr + (d * NI + inst) * 32;
+  const unsigned int ctas_per_dir = KS * p.tiles_m;
   const bool prof_cta = p.prof && (blockIdx.x + blockIdx.y + blockIdx.z == 0) && inst == 0;
   const int acols = nbox * 32;                              // TMEM columns holding U (8 per K=16 chunk)
 
@@ -250,58 +260,25 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
         if (pr) p.prof[step * 16 + 8] = dev_clock();
         {
           const __nv_bfloat16* rows = src_dir + ((size_t)tsrc * Bn + inst * BP) * p.out_row_pitch + (size_t)rank * p.ksl;
-          uint4 v[MAX_UNITS];
-          uint32_t pending = 0;
-          // Probe ONE unit with a throttled loop first: a tight 128-thread x 7-load spin floods the SM's
-          // load/store path (and L2) and slows the other instance's stores, DSMEM pushes and the producers.
-          {
-            const int ub = et / cpr, uc = et - ub * cpr;          // unit m = 0 of this thread (always < nunits)
-            const bool valid0 = (int)rank * p.ksl + uc * 8 < H;
-            if (valid0) {
-              const void* a0p = rows + (size_t)ub * p.out_row_pitch + uc * 8;
-              uint4 pv = ld_relaxed_v4(a0p);
-              if (!unit_ready(pv)) {
-                SpinGuard g;
-                do {
-                  __nanosleep(p.poll_ns);
-                  pv = ld_relaxed_v4(a0p);
-                  g.check(21);
-                } while (!unit_ready(pv));
-              }
+          // one thread acquires "every CTA of this direction has published step-1 of this instance";
+          // the named barrier hands that visibility to the other 127 loader threads
+          if (et == 0) {
+            const unsigned int need = ctas_per_dir * (unsigned int)step;
+            if (ld_acquire_u32(ctr) < need) {
+              SpinGuard g;
+              while (ld_acquire_u32(ctr) < need) g.check(20);
             }
           }
+          asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
+          if (pr) p.prof[step * 16 + 15] = dev_clock();
+          uint4 v[MAX_UNITS];
 #pragma unroll
           for (int m = 0; m < MAX_UNITS; ++m) {
             const int u = et + 128 * m;
             v[m] = make_uint4(0u, 0u, 0u, 0u);
             if (u < nunits) {
               const int ub = u / cpr, uc = u - ub * cpr;
-              if ((int)rank * p.ksl + uc * 8 < H) {
-                v[m] = ld_relaxed_v4(rows + (size_t)ub * p.out_row_pitch + uc * 8);
-                pending |= 1u << m;
-              }
-            }
-          }
-#pragma unroll
-          for (int m = 0; m < MAX_UNITS; ++m)
-            if ((pending & (1u << m)) && unit_ready(v[m])) pending &= ~(1u << m);
-          if (pending) {
-            SpinGuard g;
-            while (pending) {
-              __nanosleep(p.poll_ns);
-              // re-issue every pending unit first (loads in flight together), then test them
-#pragma unroll
-              for (int m = 0; m < MAX_UNITS; ++m) {
-                if (pending & (1u << m)) {
-                  const int u = et + 128 * m;
-                  const int ub = u / cpr, uc = u - ub * cpr;
-                  v[m] = ld_relaxed_v4(rows + (size_t)ub * p.out_row_pitch + uc * 8);
-                }
-              }
-#pragma unroll
-              for (int m = 0; m < MAX_UNITS; ++m)
-                if ((pending & (1u << m)) && unit_ready(v[m])) pending &= ~(1u << m);
-              g.check(20);
+              if ((int)rank * p.ksl + uc * 8 < H) v[m] = ld_relaxed_v4(rows + (size_t)ub * p.out_row_pitch + uc * 8);
             }
           }
           if (pr) p.prof[step * 16 + 9] = dev_clock();
@@ -369,13 +346,17 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
         }
         uint2 pk;
         __nv_bfloat162 b0v = __floats2bfloat162_rn(o[0], o[1]), b1v = __floats2bfloat162_rn(o[2], o[3]);
-        pk.x = scrub_sentinel(*reinterpret_cast<uint32_t*>(&b0v));
-        pk.y = scrub_sentinel(*reinterpret_cast<uint32_t*>(&b1v));
+        pk.x = *reinterpret_cast<uint32_t*>(&b0v);
+        pk.y = *reinterpret_cast<uint32_t*>(&b1v);
         __nv_bfloat16* dstp = p.out + (size_t)d * p.out_dir_stride + ((size_t)t * Bn + b) * p.out_row_pitch + j;
-        // this store IS the publication (consumers poll these bytes): gpu-scope store, not a lazily drained weak one
-        asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(dstp), "r"(pk.x), "r"(pk.y) : "memory");
+        *reinterpret_cast<uint2*>(dstp) = pk;
       }
       if (pr) p.prof[step * 16 + 6] = dev_clock();
+      // publish: the instance's 128 threads' stores -> one release increment of its step counter
+      // (the CTA-level barrier orders their stores before thread 0's gpu-scope release: cumulativity)
+      asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
+      if (et == 0) red_release_add(ctr, 1u);
+      if (pr) p.prof[step * 16 + 7] = dev_clock();
     }
   }
   // no CTA may exit while a peer can still write into its shared memory
@@ -412,12 +393,13 @@ static int persist_geometry(int B, int H, int ND, int* tiles_m, int* ksl, int* n
 
 int rnn_persist_supported(int B, int H, int ND) { return persist_geometry(B, H, ND, nullptr, nullptr, nullptr, nullptr, nullptr); }
 
+static constexpr size_t WS_CTR_BYTES = 2048;     // ND x MAX_NI counters, one 128-byte line each
 static constexpr size_t WS_PROF_BYTES = 131072;
 
 size_t rnn_persist_workspace_bytes(int T, int B, int H, int ND) {
   (void)T; (void)B;
   // optional profile stamps + room for U^T (bf16) used by the backward
-  return WS_PROF_BYTES + (size_t)ND * H * H * 2;
+  return WS_CTR_BYTES + WS_PROF_BYTES + (size_t)ND * H * H * 2;
 }
 
 template <bool BWD>
@@ -455,13 +437,15 @@ static int persist_launch(const CUtensorMap& ta, RnnPersistParams& p, size_t sme
   return DS2_OK;
 }
 
-static int persist_common(RnnPersistParams& p, size_t* smem, int T, int B, int H, int ND, void* ws, size_t ws_bytes, const char* who) {
+static int persist_common(RnnPersistParams& p, size_t* smem, int T, int B, int H, int ND, void* ws, size_t ws_bytes, const char* who,
+                          cudaStream_t st) {
   DS2_REQUIRE(persist_geometry(B, H, ND, &p.tiles_m, &p.ksl, &p.nbox, &p.NI, smem), DS2_ERR_UNSUPPORTED,
               "%s: persistent kernel does not take B=%d H=%d ND=%d", who, B, H, ND);
   const size_t need = rnn_persist_workspace_bytes(T, B, H, ND);
   DS2_REQUIRE(ws && ws_bytes >= need, DS2_ERR_WORKSPACE, "%s: workspace of %zu bytes required", who, need);
-  p.poll_ns = getenv("DS2_RNN_POLL_NS") ? atoi(getenv("DS2_RNN_POLL_NS")) : 100;
-  p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(ws) : nullptr;
+  DS2_CUDA(cudaMemsetAsync(ws, 0, WS_CTR_BYTES, st));
+  p.ctr = static_cast<unsigned int*>(ws);
+  p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(static_cast<char*>(ws) + WS_CTR_BYTES) : nullptr;
   return DS2_OK;
 }
 
@@ -469,13 +453,11 @@ int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const floa
                          int H, int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
   RnnPersistParams p = {};
   size_t smem;
-  int rc = persist_common(p, &smem, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_fwd");
+  int rc = persist_common(p, &smem, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_fwd", st);
   if (rc) return rc;
   CUtensorMap ta;
   rc = make_tmap_2d_bf16(&ta, u, H, (uint64_t)ND * H, H, 64, 128);
   if (rc) return rc;
-  // "not written yet" pattern for the consumers' polling loads (see the header comment)
-  DS2_CUDA(cudaMemsetAsync(hs, 0xFF, (size_t)ND * T * B * H * 2, st));
   p.add_in = wx; p.bias = bias; p.lens = lens; p.hs_in = nullptr; p.out = static_cast<__nv_bfloat16*>(hs);
   p.out_row_pitch = H; p.out_dir_stride = (long)T * B * H;
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = scale; p.cap = cap;
@@ -488,9 +470,9 @@ int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, cons
                          int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
   RnnPersistParams p = {};
   size_t smem;
-  int rc = persist_common(p, &smem, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_bwd");
+  int rc = persist_common(p, &smem, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_bwd", st);
   if (rc) return rc;
-  __nv_bfloat16* ut = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + WS_PROF_BYTES);
+  __nv_bfloat16* ut = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + WS_CTR_BYTES + WS_PROF_BYTES);
   for (int d = 0; d < ND; ++d) {
     rc = ds2_transpose(static_cast<const __nv_bfloat16*>(u) + (size_t)d * H * H, DS2_BF16, H, H, H, ut + (size_t)d * H * H, DS2_BF16, H, st);
     if (rc) return rc;
@@ -498,7 +480,6 @@ int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, cons
   CUtensorMap ta;
   rc = make_tmap_2d_bf16(&ta, ut, H, (uint64_t)ND * H, H, 64, 128);
   if (rc) return rc;
-  DS2_CUDA(cudaMemsetAsync(dz, 0xFF, (size_t)T * B * ND * H * 2, st));
   p.add_in = dout; p.bias = nullptr; p.lens = lens; p.hs_in = static_cast<const __nv_bfloat16*>(hs);
   p.out = static_cast<__nv_bfloat16*>(dz);
   p.out_row_pitch = (long)ND * H; p.out_dir_stride = H;

@@ -33,17 +33,17 @@ for it in range(3):
     torch.cuda.synchronize()
 print("T=%d H=%d B=%d: fwd kernel %.3f ms  (%.2f us/step)" % (T, H, B, e0.elapsed_time(e1), e0.elapsed_time(e1) * 1e3 / T))
 n = min(T, 1024)
-S = ws[0:n * 128].view(torch.int64).cpu().numpy().reshape(-1, 16)
+S = ws[2048:2048 + n * 128].view(torch.int64).cpu().numpy().reshape(-1, 16)
 s, nxt = S[2:n - 1], S[3:n]
-seq = [("poll-load h_{t-1} slice (all units ready)", 8, 9), ("swizzled st.shared", 9, 13), ("fence.proxy.async.shared::cta", 13, 14), ("mbarrier.arrive", 14, 10),
+seq = [("acquire counter + bar.sync", 8, 15), ("load h_{t-1} slice (7 x 16 B / thread)", 15, 9), ("swizzled st.shared", 9, 13), ("fence.proxy.async.shared::cta", 13, 14), ("mbarrier.arrive", 14, 10),
        ("loaders arrived -> control sees b_ready", 10, 0), ("MMAs + commit issued", 0, 1), ("commit -> epilogue sees accumulators", 1, 3),
        ("tcgen05.ld", 3, 11), ("st.async partial slabs issued", 11, 12), ("all 4 slabs arrived", 12, 5),
-       ("reduce + epilogue + h_t store issued", 5, 6)]
+       ("reduce + epilogue + h_t store issued", 5, 6), ("bar.sync + red.release issued", 6, 7)]
 tot = 0.0
 for name, a, b in seq:
     g = (s[:, b] - s[:, a]).astype(np.float64)
     print("%-46s mean %8.1f cyc   median %8.1f   p90 %8.1f" % (name, g.mean(), np.median(g), np.percentile(g, 90)))
     tot += g.mean()
-g = (nxt[:, 8] - s[:, 6]).astype(np.float64)
-print("%-46s mean %8.1f cyc" % ("store issued -> next step's poll start", g.mean()))
+g = (nxt[:, 8] - s[:, 7]).astype(np.float64)
+print("%-46s mean %8.1f cyc" % ("published -> next step's poll start", g.mean()))
 print("sum %.0f cycles per step" % (tot + g.mean()))
