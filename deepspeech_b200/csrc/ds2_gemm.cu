@@ -17,11 +17,20 @@
 
 namespace ds2 {
 
-static constexpr int BM = 128, BN = 128, BK = 64;
-static constexpr int STAGES = 6, ACC_STAGES = 2;
-static constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
+static constexpr int BM = 128, BK = 64;
+static constexpr int ACC_STAGES = 2;
+static constexpr int A_BYTES = BM * BK * 2;
+static constexpr int MN_GROUP_BYTES = BK * 128;       // one 64-wide MN group of an MN-major tile: [BK rows][128 B]
+// Tile width BN is a template parameter: 256 for wide outputs (a 128x128 tile reads A+B at exactly the
+// 128 B/clk shared-memory limit per MMA; 128x256 needs 96 B/clk), 128 / 32 for narrow ones (N = 29, 32).
+template <int BN> struct GemmCfg {
+  static constexpr int B_BYTES = (BN * BK * 2 < MN_GROUP_BYTES) ? MN_GROUP_BYTES : BN * BK * 2;   // room for one MN-major group
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int TMEM_COLS = (ACC_STAGES * BN < 32) ? 32 : ACC_STAGES * BN;
+};
 static constexpr int GEMM_THREADS = 256;
-static constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 
 struct GemmParams {
   void* C;
@@ -34,8 +43,11 @@ struct GemmParams {
   int splits, kb_per_split;   // split-K: partial tiles are red.add'ed into a zero-initialised fp32 C
 };
 
+template <int BN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, GemmParams p) {
+  constexpr int NGROUPS = (BN / 64 > 0) ? BN / 64 : 1;   // 64-wide groups of an MN-major B tile
+  constexpr int B_BYTES = GemmCfg<BN>::B_BYTES, STAGE_BYTES = GemmCfg<BN>::STAGE_BYTES, STAGES = GemmCfg<BN>::STAGES;
   extern __shared__ uint8_t gemm_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(gemm_smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
@@ -59,7 +71,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     for (int i = 0; i < ACC_STAGES; ++i) { mbar_init(tfull_bar + i, 1); mbar_init(tempty_bar + i, 4); }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc(tmem_slot, ACC_STAGES * BN);
+  if (warp == 2) tmem_alloc(tmem_slot, GemmCfg<BN>::TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -77,19 +89,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           mbar_wait(empty_bar + stage, phase ^ 1, 100 + stage);
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_BYTES;
-          mbar_arrive_expect_tx(full_bar + stage, STAGE_BYTES);
+          mbar_arrive_expect_tx(full_bar + stage, A_BYTES + (p.b_mn ? NGROUPS * MN_GROUP_BYTES : BN * BK * 2));
           const int k0 = kb * BK;
           if (!p.a_mn) {
             tma_load_2d(sa, &tmap_a, full_bar + stage, k0, m0);
           } else {
             tma_load_2d(sa, &tmap_a, full_bar + stage, m0, k0);
-            tma_load_2d(sa + A_BYTES / 2, &tmap_a, full_bar + stage, m0 + 64, k0);
+            tma_load_2d(sa + MN_GROUP_BYTES, &tmap_a, full_bar + stage, m0 + 64, k0);
           }
           if (!p.b_mn) {
             tma_load_2d(sb, &tmap_b, full_bar + stage, k0, n0);
           } else {
-            tma_load_2d(sb, &tmap_b, full_bar + stage, n0, k0);
-            tma_load_2d(sb + B_BYTES / 2, &tmap_b, full_bar + stage, n0 + 64, k0);
+#pragma unroll
+            for (int g = 0; g < NGROUPS; ++g) tma_load_2d(sb + g * MN_GROUP_BYTES, &tmap_b, full_bar + stage, n0 + 64 * g, k0);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -116,9 +128,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           for (int k = 0; k < BK / 16; ++k) {
             // K-major: +32 B per K=16 inside the 128B swizzle atom, SBO = 8 rows * 128 B.
             // MN-major: +16 k-rows * 128 B per K=16, LBO = 64-element MN group stride, SBO = 8 k-rows.
-            const uint64_t adesc = p.a_mn ? umma_smem_desc_sw128(sa + k * 2048, A_BYTES / 2, 1024)
+            const uint64_t adesc = p.a_mn ? umma_smem_desc_sw128(sa + k * 2048, MN_GROUP_BYTES, 1024)
                                           : umma_smem_desc_sw128(sa + k * 32, 16, 1024);
-            const uint64_t bdesc = p.b_mn ? umma_smem_desc_sw128(sb + k * 2048, B_BYTES / 2, 1024)
+            const uint64_t bdesc = p.b_mn ? umma_smem_desc_sw128(sb + k * 2048, MN_GROUP_BYTES, 1024)
                                           : umma_smem_desc_sw128(sb + k * 32, 16, 1024);
             umma_bf16(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
@@ -211,7 +223,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, ACC_STAGES * BN);
+    tmem_dealloc(tmem_base, GemmCfg<BN>::TMEM_COLS);
   }
 }
 
@@ -262,19 +274,22 @@ int gemm_bf16_launch(const void* A, long lda, int a_mn, const void* B, long ldb,
   if (!a_mn) rc = make_tmap_2d_bf16(&ta, A, K, M, lda, BK, BM);
   else rc = make_tmap_2d_bf16(&ta, A, M, K, lda, 64, BK);
   if (rc) return rc;
-  if (!b_mn) rc = make_tmap_2d_bf16(&tb, B, K, N, ldb, BK, BN);
+  const int bn = (N <= 32) ? 32 : (N <= 128 ? 128 : 256);
+  if (!b_mn) rc = make_tmap_2d_bf16(&tb, B, K, N, ldb, BK, bn);
   else rc = make_tmap_2d_bf16(&tb, B, N, K, ldb, 64, BK);
   if (rc) return rc;
   static bool attr_done = false;
   if (!attr_done) {
-    DS2_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
+    DS2_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<32>::SMEM));
+    DS2_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<128>::SMEM));
+    DS2_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<256>::SMEM));
     attr_done = true;
   }
   GemmParams p;
   p.C = C; p.ldc = ldc; p.M = M; p.N = N; p.K = K; p.alpha = alpha; p.beta = beta; p.bias = bias;
   p.c_bf16 = (c_dtype == DS2_BF16); p.a_mn = a_mn; p.b_mn = b_mn;
   p.num_m_blocks = (M + BM - 1) / BM;
-  p.num_n_blocks = (N + BN - 1) / BN;
+  p.num_n_blocks = (N + bn - 1) / bn;
   const int num_kb = (K + BK - 1) / BK;
   if (splits < 1) splits = 1;
   if (splits > num_kb) splits = num_kb;
@@ -286,7 +301,9 @@ int gemm_bf16_launch(const void* A, long lda, int a_mn, const void* B, long ldb,
   }
   const int tiles = p.num_m_blocks * p.num_n_blocks * p.splits;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_tcgen05_kernel<<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(ta, tb, p);
+  if (bn == 32) gemm_tcgen05_kernel<32><<<grid, GEMM_THREADS, GemmCfg<32>::SMEM, st>>>(ta, tb, p);
+  else if (bn == 128) gemm_tcgen05_kernel<128><<<grid, GEMM_THREADS, GemmCfg<128>::SMEM, st>>>(ta, tb, p);
+  else gemm_tcgen05_kernel<256><<<grid, GEMM_THREADS, GemmCfg<256>::SMEM, st>>>(ta, tb, p);
   DS2_LAUNCH_CHECK("gemm_tcgen05_kernel");
   count_launch();
   return DS2_OK;
@@ -304,7 +321,8 @@ extern "C" int ds2_gemm_bf16(const void* A, long lda, int a_mn_major, const void
 extern "C" int ds2_gemm_bf16_splitk(const void* A, long lda, int a_mn_major, const void* B, long ldb, int b_mn_major, float* C,
                                     long ldc, int M, int N, int K, float alpha, const float* bias, int splits, void* stream) {
   if (splits <= 0) {   // auto: enough K-splits to put a tile on every SM
-    const int tiles = ((M + ds2::BM - 1) / ds2::BM) * ((N + ds2::BN - 1) / ds2::BN);
+    const int bn = (N <= 32) ? 32 : (N <= 128 ? 128 : 256);
+    const int tiles = ((M + ds2::BM - 1) / ds2::BM) * ((N + bn - 1) / bn);
     splits = (ds2::num_sms() + tiles - 1) / tiles;
   }
   return ds2::gemm_bf16_launch(A, lda, a_mn_major, B, ldb, b_mn_major, C, DS2_F32, ldc, M, N, K, alpha, 0.f, bias, splits,
