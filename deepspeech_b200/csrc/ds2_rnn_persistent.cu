@@ -124,8 +124,8 @@ __host__ __device__ inline RnnSmem rnn_smem_layout(int nbox, int NI) {
   RnnSmem s;
   s.a_off = 0;                                            // nbox x [128 x 64] bf16 (SW128 K-major), staging for TMEM
   s.b_off = s.a_off + nbox * 16384;                       // NI x nbox x [16 x 64] bf16
-  s.slab_off = s.b_off + NI * nbox * (BP * 128);          // NI x 2 x KS x [32 x 16] fp32
-  s.bar_off = s.slab_off + NI * 2 * KS * 32 * BP * 4;     // mbarriers
+  s.slab_off = s.b_off + NI * nbox * (BP * 128);          // NI x KS x [32 x 16] fp32
+  s.bar_off = s.slab_off + NI * KS * 32 * BP * 4;         // mbarriers
   s.total = s.bar_off + 8 * (2 + NI * BARS_PER_INST) + 16;
   return s;
 }
@@ -147,9 +147,10 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
   const int inst = warp / 5, w_in = warp % 5;
   uint64_t* b_ready = bars + 2 + inst * BARS_PER_INST;      // moving operand of this step is in shared memory
   uint64_t* mma_bar = b_ready + 1;                          // accumulators ready
-  uint64_t* slab_bar = b_ready + 2;                         // [2] partial slabs of step parity arrived (tx bytes)
+  uint64_t* slab_bar = b_ready + 2;                         // partial slabs of this step arrived (tx bytes); a sender
+                                                            // cannot be a step ahead: it first acquires the step counter
   uint8_t* sB = smem + L.b_off + inst * nbox * (BP * 128);
-  float* slab = reinterpret_cast<float*>(smem + L.slab_off) + inst * 2 * KS * 32 * BP;
+  float* slab = reinterpret_cast<float*>(smem + L.slab_off) + inst * KS * 32 * BP;
 
   const uint32_t rank = cluster_ctarank();                  // K slice owned by this CTA, rows it finishes
   const int mt = blockIdx.y, d = blockIdx.z;
@@ -238,6 +239,22 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
     const int cpr = p.ksl / 8;                   // units per utterance row
     const int nunits = BP * cpr;
     const __nv_bfloat16* src_dir = p.out + (size_t)d * p.out_dir_stride;
+    // per-thread unit table, computed once: global element offset inside the step's row block (-1: no load,
+    // the unit lies beyond H and is zero-filled) and swizzled byte offset inside this instance's B tile
+    long goff[MAX_UNITS];
+    int soff[MAX_UNITS];
+#pragma unroll
+    for (int m = 0; m < MAX_UNITS; ++m) {
+      const int u = et + 128 * m;
+      goff[m] = -1;
+      soff[m] = -1;
+      if (u < nunits) {
+        const int ub = u / cpr, uc = u - ub * cpr;
+        // box (uc/8) of [16 rows x 128 B], 16-byte chunk (uc%8) XOR-swizzled with the row (SWIZZLE_128B)
+        soff[m] = (uc >> 3) * (BP * 128) + ub * 128 + (((uc & 7) ^ (ub & 7)) << 4);
+        if ((int)rank * p.ksl + uc * 8 < H) goff[m] = (long)ub * p.out_row_pitch + uc * 8;
+      }
+    }
     uint32_t ph = 0;
     for (int step = 0; step < T; ++step) {
       const int t = BWD ? (rev ? step : T - 1 - step) : (rev ? T - 1 - step : step);
@@ -254,8 +271,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
       }
       float acc[4] = {0.f, 0.f, 0.f, 0.f};
       if (step > 0) {
-        const int par = step & 1;
-        if (et == 0) mbar_arrive_expect_tx(slab_bar + par, KS * 32 * BP * 4);     // arm this step's slab barrier
+        if (et == 0) mbar_arrive_expect_tx(slab_bar, KS * 32 * BP * 4);           // arm this step's slab barrier
         // ---- loader: poll h_{t-1}[inst's utterances][this CTA's K slice] until written, stage into smem
         if (pr) p.prof[step * 16 + 8] = dev_clock();
         {
@@ -274,24 +290,13 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
           uint4 v[MAX_UNITS];
 #pragma unroll
           for (int m = 0; m < MAX_UNITS; ++m) {
-            const int u = et + 128 * m;
             v[m] = make_uint4(0u, 0u, 0u, 0u);
-            if (u < nunits) {
-              const int ub = u / cpr, uc = u - ub * cpr;
-              if ((int)rank * p.ksl + uc * 8 < H) v[m] = ld_relaxed_v4(rows + (size_t)ub * p.out_row_pitch + uc * 8);
-            }
+            if (goff[m] >= 0) v[m] = ld_relaxed_v4(rows + goff[m]);
           }
           if (pr) p.prof[step * 16 + 9] = dev_clock();
 #pragma unroll
-          for (int m = 0; m < MAX_UNITS; ++m) {
-            const int u = et + 128 * m;
-            if (u < nunits) {
-              const int ub = u / cpr, uc = u - ub * cpr;
-              // box (uc/8) of [16 rows x 128 B], 16-byte chunk (uc%8) XOR-swizzled with the row (SWIZZLE_128B)
-              uint8_t* dst = sB + (uc >> 3) * (BP * 128) + ub * 128 + (((uc & 7) ^ (ub & 7)) << 4);
-              *reinterpret_cast<uint4*>(dst) = v[m];
-            }
-          }
+          for (int m = 0; m < MAX_UNITS; ++m)
+            if (soff[m] >= 0) *reinterpret_cast<uint4*>(sB + soff[m]) = v[m];
           if (pr) p.prof[step * 16 + 13] = dev_clock();
           fence_proxy_async();       // generic-proxy smem writes -> visible to the tensor core (async proxy)
           if (pr) p.prof[step * 16 + 14] = dev_clock();
@@ -308,17 +313,17 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
         tc_fence_before();
         if (pr) p.prof[step * 16 + 11] = dev_clock();
         {
-          const uint32_t off = ((par * KS + rank) * 32 + lane) * BP * 4;
+          const uint32_t off = ((rank * 32 + lane) * BP) * 4;
           const uint32_t dst = map_to_rank(slab_local, (uint32_t)q) + off;
-          const uint32_t rbar = map_to_rank(slab_bar_local + par * 8, (uint32_t)q);
+          const uint32_t rbar = map_to_rank(slab_bar_local, (uint32_t)q);
 #pragma unroll
           for (int c = 0; c < 4; ++c) st_async_v4(dst + c * 16, rbar, r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
         }
         if (pr) p.prof[step * 16 + 12] = dev_clock();
         // ---- epilogue part 2: wait for the KS slabs of this step, reduce
-        mbar_wait(slab_bar + par, (uint32_t)(((step - 1) >> 1) & 1), 50);   // k-th use of this parity's barrier
+        mbar_wait(slab_bar, ph, 50);
         if (pr) p.prof[step * 16 + 5] = dev_clock();
-        const float* sl = slab + par * KS * 32 * BP;
+        const float* sl = slab;
 #pragma unroll
         for (int s = 0; s < KS; ++s) {
           const float* sp = sl + (s * 32 + 4 * jg) * BP + bl;
