@@ -35,7 +35,7 @@ UNIT = "audio-s/s"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=32, help="utterances per GPU (train.sh: 32)")
@@ -50,39 +50,45 @@ def parse():
 
 # ----------------------------------------------------------------------------- clocks sampler
 class ClockSampler(object):
+    """nvidia-smi in loop mode (-lms 100) for the duration of the `with` block; summary() gives the median SM clock
+    and any throttle reason that was ever active."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
-        self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
-
-    def _run(self):
-        while not self._stop.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([s.strip() for s in out.split(",")])
-            except Exception:
-                return
-            self._stop.wait(0.2)
+        self.index, self.samples, self.proc = index, [], None
 
     def __enter__(self):
-        self._t = threading.Thread(target=self._run, daemon=True)
-        self._t.start()
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            time.sleep(0.35)                       # let the first samples arrive before the timed region starts
+        except Exception:
+            self.proc = None
         return self
 
     def __exit__(self, *a):
-        self._stop.set()
-        self._t.join(timeout=10)
+        if self.proc is None:
+            return
+        try:
+            time.sleep(0.15)
+            self.proc.terminate()
+            out, _ = self.proc.communicate(timeout=10)
+            for line in out.strip().splitlines():
+                f = [x.strip() for x in line.split(",")]
+                if len(f) >= 6:
+                    self.samples.append(f)
+        except Exception:
+            pass
 
     def summary(self):
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        mhz = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
+        isnum = lambda x: x.replace(".", "", 1).isdigit()
+        mhz = sorted(float(s[0]) for s in self.samples if isnum(s[0]))
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(len(s) > 2 + i and s[2 + i].lower().startswith("active") for s in self.samples)]
-        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": float(self.samples[0][1]) if self.samples[0][1].replace(".", "").isdigit() else None,
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": float(self.samples[0][1]) if isnum(self.samples[0][1]) else None,
                 "reasons": reasons, "samples": len(self.samples)}
 
 
@@ -194,12 +200,12 @@ def main():
     # ---------------- resident-input timing (value)
     sparse, lens = host_batch(0)
     feats_dev.copy_(pinned[0], non_blocking=True)
-    for _ in range(max(args.warmup, 3)):
-        loss = train_step(sparse, lens)
-    barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    launches0 = _lib.lib.ds2_launch_count()
     with ClockSampler(local_rank) as clk:
+        for _ in range(max(args.warmup, 3)):
+            loss = train_step(sparse, lens)
+        barrier()
+        launches0 = _lib.lib.ds2_launch_count()
         barrier()
         ev0.record()
         for _ in range(args.steps):
