@@ -60,7 +60,7 @@ __device__ __forceinline__ float lse3(float a, float b, float c) {
 static constexpr int CTC_NSMAX = 4;   // lattice states per thread (S <= 4096)
 static constexpr int CTC_PF = 4;      // emission prefetch distance (time steps)
 
-template <int DIR>
+template <int DIR, int NS>
 __device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K, const int* __restrict__ labels, int Lmax,
                           const int* __restrict__ label_lens, const int* __restrict__ seq_lens, float* __restrict__ loss,
                           CtcWs ws, float* smem) {
@@ -133,23 +133,23 @@ __device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K,
   }
 
   // Per-thread lattice states s = tid + j*nthr: class and skip-transition flag are loop-invariant.
-  int cls_j[CTC_NSMAX];
-  bool skip_j[CTC_NSMAX], on_j[CTC_NSMAX];
+  int cls_j[NS];
+  bool skip_j[NS], on_j[NS];
 #pragma unroll
-  for (int j = 0; j < CTC_NSMAX; ++j) {
+  for (int j = 0; j < NS; ++j) {
     const int s = tid + j * nthr;
     on_j[j] = s < S;
     cls_j[j] = (on_j[j] && (s & 1)) ? lab[s >> 1] : blank;
     skip_j[j] = on_j[j] && (s & 1) && s >= 2 && lab[s >> 1] != lab[(s >> 1) - 1];
   }
   // emission prefetch ring (raw logits; the row lse is subtracted at use)
-  float xq[CTC_PF][CTC_NSMAX];
+  float xq[CTC_PF][NS];
 #pragma unroll
   for (int u = 0; u < CTC_PF; ++u) {
     const int step = u;
     const int t = (DIR == 0) ? step : (Tb - 1 - step);
 #pragma unroll
-    for (int j = 0; j < CTC_NSMAX; ++j)
+    for (int j = 0; j < NS; ++j)
       xq[u][j] = (step < Tb && on_j[j]) ? __ldg(logits + ((size_t)t * B + b) * K + cls_j[j]) : 0.f;
   }
   double cum = 0.0;                          // cumulative renorm offset (uniform across threads)
@@ -163,7 +163,7 @@ __device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K,
       const int t = (DIR == 0) ? step : (Tb - 1 - step);
       const float l = lse[t];
 #pragma unroll
-      for (int j = 0; j < CTC_NSMAX; ++j) {
+      for (int j = 0; j < NS; ++j) {
         if (on_j[j]) {
           const int s = tid + j * nthr;
           const float ly = xq[u][j] - l;
@@ -187,7 +187,7 @@ __device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K,
         const int nstep = step + CTC_PF;
         const int nt = (DIR == 0) ? nstep : (Tb - 1 - nstep);
 #pragma unroll
-        for (int j = 0; j < CTC_NSMAX; ++j)
+        for (int j = 0; j < NS; ++j)
           if (nstep < Tb && on_j[j]) xq[u][j] = __ldg(logits + ((size_t)nt * B + b) * K + cls_j[j]);
       }
       __syncthreads();
@@ -195,7 +195,7 @@ __device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K,
         // block max of the carried values -> subtract, accumulate offset in fp64
         float m = NEGF;
 #pragma unroll
-        for (int j = 0; j < CTC_NSMAX; ++j)
+        for (int j = 0; j < NS; ++j)
           if (on_j[j]) m = fmaxf(m, cur[tid + j * nthr + 2]);
         m = warp_max(m);
         if (lane == 0) red[warp] = m;
@@ -214,7 +214,7 @@ __device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K,
           }
         } else {
 #pragma unroll
-          for (int j = 0; j < CTC_NSMAX; ++j)
+          for (int j = 0; j < NS; ++j)
             if (on_j[j]) cur[tid + j * nthr + 2] = fmaxf(cur[tid + j * nthr + 2] - mm, NEGF);
           cum += (double)mm;
           __syncthreads();
@@ -228,14 +228,18 @@ __device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K,
   if (tid == 0) coff[0] = 0.0;
 }
 
+// NS = lattice states per thread (1 whenever 2*Lmax+1 <= 1024): the recursion is instruction-latency bound
+// (ncu: ~70 % of issue slots lost to fixed-latency / MUFU dependencies), so the common case must not carry
+// the predicated code of the multi-state case.
+template <int NS>
 __global__ void __launch_bounds__(1024, 1)
 ctc_chain_kernel(const float* __restrict__ logits, int T, int B, int K, const int* __restrict__ labels, int Lmax,
                  const int* __restrict__ label_lens, const int* __restrict__ seq_lens, float* __restrict__ loss, CtcWs ws) {
   extern __shared__ __align__(16) float ctc_smem[];
   if (blockIdx.y == 0)
-    ctc_chain<0>(logits, T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws, ctc_smem);
+    ctc_chain<0, NS>(logits, T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws, ctc_smem);
   else
-    ctc_chain<1>(logits, T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws, ctc_smem);
+    ctc_chain<1, NS>(logits, T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws, ctc_smem);
 }
 
 // One warp per (t,b) row.  dynamic smem per warp: float e[Sp]
@@ -345,11 +349,16 @@ int ctc_launch(const float* logits, int T, int B, int K, const int* labels, int 
   DS2_REQUIRE(smem <= 200 * 1024, DS2_ERR_BAD_SHAPE, "ds2_ctc: T=%d / Lmax=%d need %zu bytes of shared memory (> 200 KB)", T, Lmax, smem);
   static bool attr_done = false;
   if (!attr_done) {
-    DS2_CUDA(cudaFuncSetAttribute(ctc_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    DS2_CUDA(cudaFuncSetAttribute(ctc_chain_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    DS2_CUDA(cudaFuncSetAttribute(ctc_chain_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    DS2_CUDA(cudaFuncSetAttribute(ctc_chain_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     DS2_CUDA(cudaFuncSetAttribute(ctc_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
     attr_done = true;
   }
-  ctc_chain_kernel<<<dim3(B, 2), threads, smem, st>>>(logits, T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws);
+  const int ns = (Smax + threads - 1) / threads;
+  if (ns <= 1) ctc_chain_kernel<1><<<dim3(B, 2), threads, smem, st>>>(logits, T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws);
+  else if (ns == 2) ctc_chain_kernel<2><<<dim3(B, 2), threads, smem, st>>>(logits, T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws);
+  else ctc_chain_kernel<4><<<dim3(B, 2), threads, smem, st>>>(logits, T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws);
   DS2_LAUNCH_CHECK("ctc_chain_kernel");
   count_launch();
   if (grad) {
