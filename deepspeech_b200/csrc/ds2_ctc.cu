@@ -8,6 +8,8 @@
 // magnitudes stay small (offsets kept in fp64).  Tables go to a caller-provided scratch.
 // Kernel 2 (ctc_grad_kernel): fully parallel over (t, b): one warp per logits row computes the
 // softmax and subtracts the per-class occupancy sum_s exp(alpha+beta-logp).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace ds2 {
@@ -51,10 +53,14 @@ static size_t ctc_ws_layout(int T, int B, int K, int Lmax, char* base, CtcWs* ws
   return off;
 }
 
+// log2(2^a + 2^b + 2^c): the recursion runs in base-2 log units (one MUFU.EX2 / MUFU.LG2 per term, no
+// conversion multiplies on the dependency chain)
 __device__ __forceinline__ float lse3(float a, float b, float c) {
-  float m = fmaxf(a, fmaxf(b, c));
-  return m + __logf(__expf(a - m) + __expf(b - m) + __expf(c - m));
+  const float m = fmaxf(a, fmaxf(b, c));
+  return m + __log2f(exp2f(a - m) + exp2f(b - m) + exp2f(c - m));
 }
+static constexpr float LOG2E = 1.4426950408889634f;
+static constexpr double LN2 = 0.6931471805599453;
 
 // dynamic smem: float buf[2][Smax+2] | float lse[T] | int lab[Lmax] | float red[32]
 static constexpr int CTC_NSMAX = 4;   // lattice states per thread (S <= 4096)
@@ -99,7 +105,7 @@ __device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K,
       for (int k = 0; k < K; ++k) m = fmaxf(m, __ldg(row + k));
       for (int k = 0; k < K; ++k) s += __expf(__ldg(row + k) - m);
     }
-    lse[t] = m + __logf(s);
+    lse[t] = (m + __logf(s)) * LOG2E;     // row log-sum-exp in log2 units
   }
   if (tid < 2) { buf0[tid] = NEGF; buf1[tid] = NEGF; }
   __syncthreads();
@@ -142,31 +148,45 @@ __device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K,
     cls_j[j] = (on_j[j] && (s & 1)) ? lab[s >> 1] : blank;
     skip_j[j] = on_j[j] && (s & 1) && s >= 2 && lab[s >> 1] != lab[(s >> 1) - 1];
   }
-  // emission prefetch ring (raw logits; the row lse is subtracted at use)
+  // per-thread streaming pointers (no 64-bit index arithmetic on the per-step path)
+  const long xstride = (DIR == 0) ? (long)B * K : -(long)B * K;
+  const long tstride = (DIR == 0) ? (long)ws.Sp : -(long)ws.Sp;
+  const int t_first = (DIR == 0) ? 0 : (Tb - 1);
+  const float* xp[NS];       // emission of the step being prefetched (CTC_PF ahead)
+  float* tp[NS];             // table cell of the current step
+#pragma unroll
+  for (int j = 0; j < NS; ++j) {
+    const int s = tid + j * nthr;
+    xp[j] = logits + ((size_t)t_first * B + b) * K + cls_j[j];
+    tp[j] = tab + (size_t)t_first * ws.Sp + ((DIR == 0) ? s : (S - 1 - s));
+  }
+  // emission prefetch ring (raw logits; scaled to log2 units and the row lse subtracted at use)
   float xq[CTC_PF][NS];
 #pragma unroll
   for (int u = 0; u < CTC_PF; ++u) {
-    const int step = u;
-    const int t = (DIR == 0) ? step : (Tb - 1 - step);
 #pragma unroll
-    for (int j = 0; j < NS; ++j)
-      xq[u][j] = (step < Tb && on_j[j]) ? __ldg(logits + ((size_t)t * B + b) * K + cls_j[j]) : 0.f;
+    for (int j = 0; j < NS; ++j) {
+      xq[u][j] = (u < Tb && on_j[j]) ? __ldg(xp[j]) : 0.f;
+      xp[j] += xstride;
+    }
   }
-  double cum = 0.0;                          // cumulative renorm offset (uniform across threads)
+  double cum = 0.0;                          // cumulative renorm offset (uniform across threads), log2 units
   float* prev = buf0;
   float* cur = buf1;
+  const float* lsep = lse + t_first;
+  const int lstride = (DIR == 0) ? 1 : -1;
   for (int base = 0; base < Tb; base += CTC_PF) {
 #pragma unroll
     for (int u = 0; u < CTC_PF; ++u) {
       const int step = base + u;
       if (step >= Tb) break;
-      const int t = (DIR == 0) ? step : (Tb - 1 - step);
-      const float l = lse[t];
+      const float l = *lsep;
+      lsep += lstride;
 #pragma unroll
       for (int j = 0; j < NS; ++j) {
         if (on_j[j]) {
           const int s = tid + j * nthr;
-          const float ly = xq[u][j] - l;
+          const float ly = fmaf(xq[u][j], LOG2E, -l);
           float v;
           if (step == 0) {
             v = (s < 2) ? 0.f : NEGF;
@@ -175,20 +195,19 @@ __device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K,
             v = lse3(prev[s + 2], prev[s + 1], a2);
           }
           // alpha stores the value with the emission, beta stores it without; the running
-          // quantity carried to the next step always includes the emission.
-          const float carried = fmaxf(v + ly, NEGF);
+          // quantity carried to the next step always includes the emission.  (NEGF = -1e30 absorbs
+          // every finite addend, so unreachable states need no clamping.)
+          const float carried = v + ly;
           cur[s + 2] = carried;
-          const int sidx = (DIR == 0) ? s : (S - 1 - s);
-          tab[(size_t)t * ws.Sp + sidx] = (DIR == 0) ? carried : fmaxf(v, NEGF);
+          *tp[j] = (DIR == 0) ? carried : v;
+          tp[j] += tstride;
         }
       }
       // refill this ring slot with the emission of step + CTC_PF
-      {
-        const int nstep = step + CTC_PF;
-        const int nt = (DIR == 0) ? nstep : (Tb - 1 - nstep);
 #pragma unroll
-        for (int j = 0; j < NS; ++j)
-          if (nstep < Tb && on_j[j]) xq[u][j] = __ldg(logits + ((size_t)nt * B + b) * K + cls_j[j]);
+      for (int j = 0; j < NS; ++j) {
+        if (step + CTC_PF < Tb && on_j[j]) xq[u][j] = __ldg(xp[j]);
+        xp[j] += xstride;
       }
       __syncthreads();
       if ((step % RENORM) == RENORM - 1 || step == Tb - 1) {
@@ -208,14 +227,14 @@ __device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K,
             const float aL = cur[S - 1 + 2];
             const float aL1 = (S > 1) ? cur[S - 2 + 2] : NEGF;
             const float mx = fmaxf(aL, aL1);
-            const double lp = (double)mx + log((double)__expf(aL - mx) + (double)__expf(aL1 - mx)) + cum;
+            const double lp = (double)mx + log2((double)exp2f(aL - mx) + (double)exp2f(aL1 - mx)) + cum;   // log2 p
             ws.logp[b] = lp;
-            loss[b] = (float)(-lp);
+            loss[b] = (float)(-lp * LN2);
           }
         } else {
 #pragma unroll
           for (int j = 0; j < NS; ++j)
-            if (on_j[j]) cur[tid + j * nthr + 2] = fmaxf(cur[tid + j * nthr + 2] - mm, NEGF);
+            if (on_j[j]) cur[tid + j * nthr + 2] -= mm;
           cum += (double)mm;
           __syncthreads();
         }
@@ -275,7 +294,7 @@ ctc_grad_kernel(const float* __restrict__ logits, int T, int B, int K, const int
     const float* br = ws.beta + ((size_t)b * T + t) * ws.Sp;
     float blank_sum = 0.f;
     for (int s = lane; s < S; s += 32) {
-      const float v = __expf(fminf(ar[s] + br[s] + c, 0.f + 1e-3f));
+      const float v = exp2f(fminf(ar[s] + br[s] + c, 1e-3f));     // tables, offsets and log p are in log2 units
       e[s] = v;
       if (!(s & 1)) blank_sum += v;
     }
@@ -341,7 +360,11 @@ int ctc_launch(const float* logits, int T, int B, int K, const int* labels, int 
               workspace_bytes, need);
   DS2_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, DS2_ERR_BAD_ARG, "ds2_ctc: workspace must be 256-byte aligned");
   const int Smax = 2 * Lmax + 1;
-  int threads = ((Smax + 31) / 32) * 32;
+  // states per thread: 2 gives every thread two independent log-sum-exp chains (the loop is latency bound)
+  // and halves the number of warps at the per-step barrier
+  int ns_pref = 2;
+  if (const char* e = getenv("DS2_CTC_NS")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) ns_pref = v; }
+  int threads = (((Smax + ns_pref - 1) / ns_pref + 31) / 32) * 32;
   if (threads < 64) threads = 64;
   if (threads > 1024) threads = 1024;
   size_t smem = sizeof(float) * (2 * (size_t)(Smax + 2) + T + 32) + sizeof(int) * (size_t)(Lmax > 0 ? Lmax : 1);
