@@ -83,6 +83,17 @@ def gemm_nt(A: torch.Tensor, B: torch.Tensor, *, a_mn: bool = False, b_mn: bool 
     return out
 
 
+def gemm_wgrad(A, B, M, N, K, lda, ldb, out, alpha=1.0):
+    """out[M,N] (fp32) = alpha * A^T.B with both operands MN-major ([K,M] / [K,N] row-major): the weight-gradient
+    shape (few output tiles, very long K).  Tensor cores with automatic split-K when the operands allow it."""
+    if (A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16 and lda % 8 == 0 and ldb % 8 == 0
+            and A.data_ptr() % 16 == 0 and B.data_ptr() % 16 == 0 and K >= 8 and out.dtype == torch.float32):
+        check(lib.ds2_gemm_bf16_splitk(_p(A), lda, 1, _p(B), ldb, 1, _p(out), out.stride(0), M, N, K, alpha, None, 0, _stream()),
+              "ds2_gemm_bf16_splitk")
+        return out
+    return gemm_nt(A, B, a_mn=True, b_mn=True, M=M, N=N, K=K, lda=lda, ldb=ldb, out=out, alpha=alpha)
+
+
 def cast(x: torch.Tensor, dtype) -> torch.Tensor:
     if x.dtype == dtype:
         return x
@@ -359,7 +370,8 @@ class _BiRNNLayerFn(torch.autograd.Function):
                                    RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_bwd")
         db = colsum(dz, T * B, ND * H, ND * H).view(ND, H)
         # dW = scale * dz^T x ; dx = scale * dz W   (both directions in one GEMM each)
-        dW = gemm_nt(dz, xg.view(T * B, I), a_mn=True, b_mn=True, alpha=SBN_SCALE)            # [ND*H, I]
+        dW = torch.empty((ND * H, I), dtype=torch.float32, device=dev)
+        gemm_wgrad(dz, xg.view(T * B, I), ND * H, I, T * B, ND * H, I, dW, alpha=SBN_SCALE)    # [ND*H, I]
         dx = None
         if ctx.needs_input_grad[0]:
             dx = gemm_nt(dz, Wg, b_mn=True, alpha=SBN_SCALE).view(T, B, I)                   # [TB, I] fp32
@@ -373,7 +385,7 @@ class _BiRNNLayerFn(torch.autograd.Function):
                 a_off = (0 if rev else B * ND * H) + d * H           # dz rows t = 1.. (fw) / 0..T-2 (bw)
                 A = dz.view(-1)[a_off:]
                 Bm = hs[d].reshape(T * B, H)[(B if rev else 0):]
-                gemm_nt(A, Bm, a_mn=True, b_mn=True, M=H, N=H, K=(T - 1) * B, lda=ND * H, ldb=H, out=dU[d])
+                gemm_wgrad(A, Bm, H, H, (T - 1) * B, ND * H, H, dU[d])
             else:
                 dU[d].zero_()
         return dx, dW, dU, db, None, None, None, None
