@@ -62,190 +62,13 @@ __device__ __forceinline__ float lse3(float a, float b, float c) {
 static constexpr float LOG2E = 1.4426950408889634f;
 static constexpr double LN2 = 0.6931471805599453;
 
-// dynamic smem: float buf[2][Smax+2] | float lse[T] | int lab[Lmax] | float red[32]
 static constexpr int CTC_NSMAX = 4;   // lattice states per thread (S <= 4096)
-static constexpr int CTC_PF = 4;      // emission prefetch distance (time steps)
 
-template <int DIR, int NS>
-__device__ void ctc_chain(const float* __restrict__ logits, int T, int B, int K, const int* __restrict__ labels, int Lmax,
-                          const int* __restrict__ label_lens, const int* __restrict__ seq_lens, float* __restrict__ loss,
-                          CtcWs ws, float* smem) {
-  const int b = blockIdx.x;
-  const int tid = threadIdx.x, nthr = blockDim.x;
-  const int lane = tid & 31, warp = tid >> 5, nwarps = nthr >> 5;
-  const int Tb = min(seq_lens[b], T);
-  const int L = label_lens[b];
-  const int S = 2 * L + 1;
-  const int blank = K - 1;
-  const int Smax = 2 * Lmax + 1;
-  float* buf0 = smem;                       // [Smax+2], entries 0,1 are NEG padding
-  float* buf1 = buf0 + (Smax + 2);
-  float* lse = buf1 + (Smax + 2);           // [T]
-  int* lab = reinterpret_cast<int*>(lse + T);   // [Lmax]  (reversed for DIR==1)
-  float* red = reinterpret_cast<float*>(lab + (Lmax > 0 ? Lmax : 1));   // [32]
-  float* tab = (DIR == 0 ? ws.alpha : ws.beta) + (size_t)b * T * ws.Sp;
-  double* coff = ws.coff + ((size_t)b * 2 + DIR) * ws.NB;
+}  // namespace ds2
 
-  for (int i = tid; i < L; i += nthr) lab[i] = labels[(size_t)b * Lmax + (DIR == 0 ? i : L - 1 - i)];
-  // row log-sum-exp: one THREAD per row so that every thread has a whole row of independent loads in
-  // flight (a warp-per-row loop serialises one DRAM latency per row); this pass also pulls the
-  // utterance's logits into L2 for the recursion below.
-  for (int t = tid; t < Tb; t += nthr) {
-    const float* row = logits + ((size_t)t * B + b) * K;
-    float m = -INFINITY, s = 0.f;
-    if (K <= 32) {
-      float v[32];
-#pragma unroll
-      for (int k = 0; k < 32; ++k) v[k] = (k < K) ? __ldg(row + k) : -INFINITY;
-#pragma unroll
-      for (int k = 0; k < 32; ++k) m = fmaxf(m, v[k]);
-#pragma unroll
-      for (int k = 0; k < 32; ++k) s += __expf(v[k] - m);
-    } else {
-      for (int k = 0; k < K; ++k) m = fmaxf(m, __ldg(row + k));
-      for (int k = 0; k < K; ++k) s += __expf(__ldg(row + k) - m);
-    }
-    lse[t] = (m + __logf(s)) * LOG2E;     // row log-sum-exp in log2 units
-  }
-  if (tid < 2) { buf0[tid] = NEGF; buf1[tid] = NEGF; }
-  __syncthreads();
-  if (DIR == 0 && warp == 0) {
-    // class-sorted (stable) permutation of label positions for the gradient kernel:
-    // lane k owns class k (chunks of 32 classes), counting pass + warp scan + fill pass.
-    int* cls = ws.cls_off + (size_t)b * (K + 1);
-    int* perm = ws.perm + (size_t)b * Lmax;
-    int base = 0;
-    for (int k0 = 0; k0 < K; k0 += 32) {
-      const int k = k0 + lane;
-      int cnt = 0;
-      for (int i = 0; i < L; ++i) cnt += (lab[i] == k);
-      int incl = cnt;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        int v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += v;
-      }
-      int c = base + incl - cnt;
-      if (k < K) cls[k] = c;
-      for (int i = 0; i < L; ++i)
-        if (lab[i] == k) perm[c++] = i;
-      base += __shfl_sync(0xffffffffu, incl, 31);
-    }
-    if (lane == 0) cls[K] = base;
-  }
-  if (Tb <= 0) {
-    if (DIR == 0 && tid == 0) { ws.logp[b] = 0.0; loss[b] = 0.f; }
-    return;
-  }
+#include "ds2_ctc_chain.cuh"
 
-  // Per-thread lattice states s = tid + j*nthr: class and skip-transition flag are loop-invariant.
-  int cls_j[NS];
-  bool skip_j[NS], on_j[NS];
-#pragma unroll
-  for (int j = 0; j < NS; ++j) {
-    const int s = tid + j * nthr;
-    on_j[j] = s < S;
-    cls_j[j] = (on_j[j] && (s & 1)) ? lab[s >> 1] : blank;
-    skip_j[j] = on_j[j] && (s & 1) && s >= 2 && lab[s >> 1] != lab[(s >> 1) - 1];
-  }
-  // per-thread streaming pointers (no 64-bit index arithmetic on the per-step path)
-  const long xstride = (DIR == 0) ? (long)B * K : -(long)B * K;
-  const long tstride = (DIR == 0) ? (long)ws.Sp : -(long)ws.Sp;
-  const int t_first = (DIR == 0) ? 0 : (Tb - 1);
-  const float* xp[NS];       // emission of the step being prefetched (CTC_PF ahead)
-  float* tp[NS];             // table cell of the current step
-#pragma unroll
-  for (int j = 0; j < NS; ++j) {
-    const int s = tid + j * nthr;
-    xp[j] = logits + ((size_t)t_first * B + b) * K + cls_j[j];
-    tp[j] = tab + (size_t)t_first * ws.Sp + ((DIR == 0) ? s : (S - 1 - s));
-  }
-  // emission prefetch ring (raw logits; scaled to log2 units and the row lse subtracted at use)
-  float xq[CTC_PF][NS];
-#pragma unroll
-  for (int u = 0; u < CTC_PF; ++u) {
-#pragma unroll
-    for (int j = 0; j < NS; ++j) {
-      xq[u][j] = (u < Tb && on_j[j]) ? __ldg(xp[j]) : 0.f;
-      xp[j] += xstride;
-    }
-  }
-  double cum = 0.0;                          // cumulative renorm offset (uniform across threads), log2 units
-  float* prev = buf0;
-  float* cur = buf1;
-  const float* lsep = lse + t_first;
-  const int lstride = (DIR == 0) ? 1 : -1;
-  for (int base = 0; base < Tb; base += CTC_PF) {
-#pragma unroll
-    for (int u = 0; u < CTC_PF; ++u) {
-      const int step = base + u;
-      if (step >= Tb) break;
-      const float l = *lsep;
-      lsep += lstride;
-#pragma unroll
-      for (int j = 0; j < NS; ++j) {
-        if (on_j[j]) {
-          const int s = tid + j * nthr;
-          const float ly = fmaf(xq[u][j], LOG2E, -l);
-          float v;
-          if (step == 0) {
-            v = (s < 2) ? 0.f : NEGF;
-          } else {
-            const float a2 = skip_j[j] ? prev[s] : NEGF;
-            v = lse3(prev[s + 2], prev[s + 1], a2);
-          }
-          // alpha stores the value with the emission, beta stores it without; the running
-          // quantity carried to the next step always includes the emission.  (NEGF = -1e30 absorbs
-          // every finite addend, so unreachable states need no clamping.)
-          const float carried = v + ly;
-          cur[s + 2] = carried;
-          *tp[j] = (DIR == 0) ? carried : v;
-          tp[j] += tstride;
-        }
-      }
-      // refill this ring slot with the emission of step + CTC_PF
-#pragma unroll
-      for (int j = 0; j < NS; ++j) {
-        if (step + CTC_PF < Tb && on_j[j]) xq[u][j] = __ldg(xp[j]);
-        xp[j] += xstride;
-      }
-      __syncthreads();
-      if ((step % RENORM) == RENORM - 1 || step == Tb - 1) {
-        // block max of the carried values -> subtract, accumulate offset in fp64
-        float m = NEGF;
-#pragma unroll
-        for (int j = 0; j < NS; ++j)
-          if (on_j[j]) m = fmaxf(m, cur[tid + j * nthr + 2]);
-        m = warp_max(m);
-        if (lane == 0) red[warp] = m;
-        __syncthreads();
-        float mm = red[0];
-        for (int w = 1; w < nwarps; ++w) mm = fmaxf(mm, red[w]);
-        if (step == Tb - 1) {
-          if (DIR == 0 && tid == 0) {
-            // log p = logsumexp(alpha_{T-1}(S-1), alpha_{T-1}(S-2)) + offsets
-            const float aL = cur[S - 1 + 2];
-            const float aL1 = (S > 1) ? cur[S - 2 + 2] : NEGF;
-            const float mx = fmaxf(aL, aL1);
-            const double lp = (double)mx + log2((double)exp2f(aL - mx) + (double)exp2f(aL1 - mx)) + cum;   // log2 p
-            ws.logp[b] = lp;
-            loss[b] = (float)(-lp * LN2);
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < NS; ++j)
-            if (on_j[j]) cur[tid + j * nthr + 2] -= mm;
-          cum += (double)mm;
-          __syncthreads();
-        }
-      }
-      // offset that applies to the rows written from the NEXT step on
-      if (tid == 0 && ((step + 1) % RENORM) == 0) coff[(step + 1) / RENORM] = cum;
-      float* tmp = prev; prev = cur; cur = tmp;
-    }
-  }
-  if (tid == 0) coff[0] = 0.0;
-}
+namespace ds2 {
 
 // NS = lattice states per thread (1 whenever 2*Lmax+1 <= 1024): the recursion is instruction-latency bound
 // (ncu: ~70 % of issue slots lost to fixed-latency / MUFU dependencies), so the common case must not carry
@@ -367,7 +190,7 @@ int ctc_launch(const float* logits, int T, int B, int K, const int* labels, int 
   int threads = (((Smax + ns_pref - 1) / ns_pref + 31) / 32) * 32;
   if (threads < 64) threads = 64;
   if (threads > 1024) threads = 1024;
-  size_t smem = sizeof(float) * (2 * (size_t)(Smax + 2) + T + 32) + sizeof(int) * (size_t)(Lmax > 0 ? Lmax : 1);
+  const size_t smem = ctc_smem_layout(T, Lmax, K, ws.Sp).bytes;
   DS2_REQUIRE(Smax <= 1024 * CTC_NSMAX, DS2_ERR_BAD_SHAPE, "ds2_ctc: Lmax=%d exceeds the supported label length %d", Lmax, (1024 * CTC_NSMAX - 1) / 2);
   DS2_REQUIRE(smem <= 200 * 1024, DS2_ERR_BAD_SHAPE, "ds2_ctc: T=%d / Lmax=%d need %zu bytes of shared memory (> 200 KB)", T, Lmax, smem);
   static bool attr_done = false;
