@@ -185,7 +185,7 @@ int ctc_launch(const float* logits, int T, int B, int K, const int* labels, int 
   const int Smax = 2 * Lmax + 1;
   // states per thread: 2 gives every thread two independent log-sum-exp chains (the loop is latency bound)
   // and halves the number of warps at the per-step barrier
-  int ns_pref = 2;
+  int ns_pref = 1;
   if (const char* e = getenv("DS2_CTC_NS")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) ns_pref = v; }
   int threads = (((Smax + ns_pref - 1) / ns_pref + 31) / 32) * 32;
   if (threads < 64) threads = 64;
