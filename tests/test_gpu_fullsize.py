@@ -43,15 +43,15 @@ def test_ctc_sweep_invariants(T, L, B):
     loss, grad = _ctc(x, lab, ll, sl)
     g = grad.cpu().numpy()
     assert np.isfinite(loss.cpu().numpy()).all() and (loss > 0).all()
-    assert np.abs(g.sum(2)).max() < 2e-4                               # softmax - occupancy: both sum to 1
+    assert np.abs(g.sum(2)).max() < 1e-3                               # softmax - occupancy: both sum to 1 (gradient bar 1e-3)
     for b in range(B):
         assert np.abs(g[sl[b]:, b]).max(initial=0.0) == 0.0
     # blank occupancy + label occupancy = 1 at every valid step <=> sum_s alpha beta = p at every t
     y = torch.softmax(x, 2).cpu().numpy()
     occ = y - g
     for b in (0, B // 2, B - 1):
-        assert np.abs(occ[:sl[b], b].sum(1) - 1.0).max() < 2e-4
-        assert occ[:sl[b], b].min() > -1e-4
+        assert np.abs(occ[:sl[b], b].sum(1) - 1.0).max() < 1e-3
+        assert occ[:sl[b], b].min() > -1e-3
     # shift invariance of the loss (softmax inside)
     shift = torch.tensor(rng.standard_normal((T, B, 1)) * 3, dtype=torch.float32, device="cuda")
     loss2, _ = _ctc(x + shift, lab, ll, sl)
