@@ -21,56 +21,83 @@ __global__ void __launch_bounds__(256)
 im2col_kernel(const float* __restrict__ x, const float* __restrict__ mean, const float* __restrict__ rstd,
               const float* __restrict__ gamma, const float* __restrict__ beta, float cap, int clip,
               __nv_bfloat16* __restrict__ P, ColGeom g) {
-  const long kvec = g.ldp / 8;
-  const long total = (long)g.B * g.To * g.Fo * kvec;
+  // per-channel affine of the fused batch norm: y = x * sc[c] + sh[c]
+  __shared__ __align__(16) float sc[256], sh[256];
+  if (BN) {
+    for (int c = threadIdx.x; c < g.Ci; c += blockDim.x) {
+      const float a = rstd[c] * gamma[c];
+      sc[c] = a;
+      sh[c] = beta[c] - mean[c] * a;
+    }
+    __syncthreads();
+  }
+  // 32-bit index math only: a block works on rows_per_block patch rows at a time, the thread's 8-wide K chunk is fixed
+  const int kvec = (int)(g.ldp / 8);
+  const int rows_per_block = blockDim.x / kvec > 0 ? blockDim.x / kvec : 1;
+  const int M = g.B * g.To * g.Fo;
   const bool vec = (g.Ci % 8) == 0;
-  for (long idx = blockIdx.x * (long)blockDim.x + threadIdx.x; idx < total; idx += (long)gridDim.x * blockDim.x) {
-    const long m = idx / kvec;
-    const int k8 = (int)(idx % kvec) * 8;
-    const int fo = m % g.Fo;
-    const long r = m / g.Fo;
-    const int to = r % g.To;
-    const int b = (int)(r / g.To);
-    float v[8];
-    if (vec && k8 + 8 <= g.K) {
-      const int ci = k8 % g.Ci;
+  for (int kv0 = 0; kv0 < kvec; kv0 += blockDim.x) {          // more than one pass only when kvec > blockDim
+    const int rl = (kvec <= (int)blockDim.x) ? (int)threadIdx.x / kvec : 0;
+    const int kv = (kvec <= (int)blockDim.x) ? (int)threadIdx.x - rl * kvec : kv0 + (int)threadIdx.x;
+    if (rl >= rows_per_block || kv >= kvec) continue;
+    const int k8 = kv * 8;
+    // tap decomposition of this thread's chunk (row independent)
+    const bool fast = vec && k8 + 8 <= g.K;
+    int ci = 0, kf = 0, kt = 0;
+    if (fast) {
+      ci = k8 % g.Ci;
       const int q = k8 / g.Ci;
-      const int kf = q % g.KF, kt = q / g.KF;
-      const float* src = x + (((long)b * g.Ti + (to * g.st + kt)) * g.Fi + (fo * g.sf + kf)) * g.Ci + ci;
-      const float4 a = __ldg(reinterpret_cast<const float4*>(src));
-      const float4 c = __ldg(reinterpret_cast<const float4*>(src) + 1);
-      v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = c.x; v[5] = c.y; v[6] = c.z; v[7] = c.w;
-      if (BN) {
+      kf = q % g.KF;
+      kt = q / g.KF;
+    }
+    float s8[8], h8[8];
+    if (BN && fast) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          float t = (v[i] - mean[ci + i]) * rstd[ci + i] * gamma[ci + i] + beta[ci + i];
-          v[i] = clip ? fminf(fmaxf(t, 0.f), cap) : t;
-        }
-      }
-    } else {
+      for (int i = 0; i < 8; ++i) { s8[i] = sc[ci + i]; h8[i] = sh[ci + i]; }
+    }
+    for (int m = blockIdx.x * rows_per_block + rl; m < M; m += gridDim.x * rows_per_block) {
+      const int fo = m % g.Fo;
+      const int r = m / g.Fo;
+      const int to = r % g.To;
+      const int b = r / g.To;
+      float v[8];
+      if (fast) {
+        const float* src = x + (((long)b * g.Ti + (to * g.st + kt)) * g.Fi + (fo * g.sf + kf)) * g.Ci + ci;
+        const float4 a = __ldg(reinterpret_cast<const float4*>(src));
+        const float4 c = __ldg(reinterpret_cast<const float4*>(src) + 1);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = c.x; v[5] = c.y; v[6] = c.z; v[7] = c.w;
+        if (BN) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int k = k8 + i;
-        float t = 0.f;
-        if (k < g.K) {
-          const int ci = k % g.Ci;
-          const int q = k / g.Ci;
-          const int kf = q % g.KF, kt = q / g.KF;
-          t = __ldg(x + (((long)b * g.Ti + (to * g.st + kt)) * g.Fi + (fo * g.sf + kf)) * g.Ci + ci);
-          if (BN) {
-            t = (t - mean[ci]) * rstd[ci] * gamma[ci] + beta[ci];
-            if (clip) t = fminf(fmaxf(t, 0.f), cap);
+          for (int i = 0; i < 8; ++i) {
+            const float t = fmaf(v[i], s8[i], h8[i]);
+            v[i] = clip ? fminf(fmaxf(t, 0.f), cap) : t;
           }
         }
-        v[i] = t;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int k = k8 + i;
+          float t = 0.f;
+          if (k < g.K) {
+            const int c1 = k % g.Ci;
+            const int q = k / g.Ci;
+            const int kf1 = q % g.KF, kt1 = q / g.KF;
+            t = __ldg(x + (((long)b * g.Ti + (to * g.st + kt1)) * g.Fi + (fo * g.sf + kf1)) * g.Ci + c1);
+            if (BN) {
+              t = fmaf(t, sc[c1], sh[c1]);
+              if (clip) t = fminf(fmaxf(t, 0.f), cap);
+            }
+          }
+          v[i] = t;
+        }
       }
+      uint4 pk;
+      __nv_bfloat162 b0 = __floats2bfloat162_rn(v[0], v[1]), b1 = __floats2bfloat162_rn(v[2], v[3]);
+      __nv_bfloat162 b2 = __floats2bfloat162_rn(v[4], v[5]), b3 = __floats2bfloat162_rn(v[6], v[7]);
+      pk.x = *reinterpret_cast<uint32_t*>(&b0); pk.y = *reinterpret_cast<uint32_t*>(&b1);
+      pk.z = *reinterpret_cast<uint32_t*>(&b2); pk.w = *reinterpret_cast<uint32_t*>(&b3);
+      *reinterpret_cast<uint4*>(P + (long)m * g.ldp + k8) = pk;
     }
-    uint4 pk;
-    __nv_bfloat162 b0 = __floats2bfloat162_rn(v[0], v[1]), b1 = __floats2bfloat162_rn(v[2], v[3]);
-    __nv_bfloat162 b2 = __floats2bfloat162_rn(v[4], v[5]), b3 = __floats2bfloat162_rn(v[6], v[7]);
-    pk.x = *reinterpret_cast<uint32_t*>(&b0); pk.y = *reinterpret_cast<uint32_t*>(&b1);
-    pk.z = *reinterpret_cast<uint32_t*>(&b2); pk.w = *reinterpret_cast<uint32_t*>(&b3);
-    *reinterpret_cast<uint4*>(P + m * g.ldp + k8) = pk;
   }
 }
 
@@ -78,13 +105,13 @@ im2col_kernel(const float* __restrict__ x, const float* __restrict__ mean, const
 __global__ void __launch_bounds__(256)
 col2im_kernel(const __nv_bfloat16* __restrict__ dP, float* __restrict__ dx, ColGeom g) {
   const int cvec = g.Ci / 8;
-  const long total = (long)g.B * g.Ti * g.Fi * cvec;
-  for (long idx = blockIdx.x * (long)blockDim.x + threadIdx.x; idx < total; idx += (long)gridDim.x * blockDim.x) {
-    const int ci = (int)(idx % cvec) * 8;
-    long r = idx / cvec;
+  const int total = g.B * g.Ti * g.Fi * cvec;              // < 2^31 (checked by the host wrapper): 32-bit index math
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int ci = (idx % cvec) * 8;
+    int r = idx / cvec;
     const int fi = r % g.Fi; r /= g.Fi;
     const int ti = r % g.Ti;
-    const int b = (int)(r / g.Ti);
+    const int b = r / g.Ti;
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (int kt = 0; kt < g.KT; ++kt) {
       const int tn = ti - kt;
@@ -140,7 +167,11 @@ extern "C" int ds2_im2col(const float* x, const float* mean, const float* rstd, 
   DS2_REQUIRE(x && P, DS2_ERR_BAD_ARG, "ds2_im2col: null pointer");
   DS2_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(P) & 15) == 0, DS2_ERR_BAD_ARG,
               "ds2_im2col: pointers must be 16-byte aligned");
-  const long total = (long)g.B * g.To * g.Fo * (ldp / 8);
+  DS2_REQUIRE(Ci <= 256, DS2_ERR_BAD_SHAPE, "ds2_im2col: at most 256 input channels (got %d)", Ci);
+  DS2_REQUIRE((long)g.B * g.To * g.Fo < 2147483647L, DS2_ERR_BAD_SHAPE, "ds2_im2col: too many patch rows");
+  const int kvec_h = (int)(ldp / 8);
+  const int rpb = 256 / kvec_h > 0 ? 256 / kvec_h : 1;
+  const long total = ((long)g.B * g.To * g.Fo + rpb - 1) / rpb * 256;      // one block-iteration per rows_per_block rows
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   if (mean) {
     DS2_REQUIRE(rstd && gamma && beta, DS2_ERR_BAD_ARG, "ds2_im2col: incomplete batch-norm parameters");
@@ -161,6 +192,7 @@ extern "C" int ds2_col2im(const void* dP, long ldp, float* dx, int B, int Ti, in
   DS2_REQUIRE(dP && dx, DS2_ERR_BAD_ARG, "ds2_col2im: null pointer");
   DS2_REQUIRE(Ci % 8 == 0, DS2_ERR_UNSUPPORTED, "ds2_col2im: input channels (%d) must be a multiple of 8", Ci);
   const long total = (long)g.B * g.Ti * g.Fi * (g.Ci / 8);
+  DS2_REQUIRE(total < 2147483647L, DS2_ERR_BAD_SHAPE, "ds2_col2im: tensor too large for 32-bit indexing");
   col2im_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(dP), dx, g);
   DS2_LAUNCH_CHECK("col2im_kernel");
   count_launch();

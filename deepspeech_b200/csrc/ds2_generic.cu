@@ -175,6 +175,14 @@ struct ActMap {
   long sb, st, sf, sc;
 };
 __device__ __forceinline__ long act_index(const ActMap& m, long r, int c) {
+  if (r < 2147483647L) {                      // 32-bit divisions (64-bit ones cost ~100 instructions each)
+    const unsigned int ru = (unsigned int)r;
+    const unsigned int q = ru / (unsigned int)m.F;
+    const unsigned int f = ru - q * (unsigned int)m.F;
+    const unsigned int b = q / (unsigned int)m.T;
+    const unsigned int t = q - b * (unsigned int)m.T;
+    return (long)b * m.sb + (long)t * m.st + (long)f * m.sf + (long)c * m.sc;
+  }
   const int f = r % m.F;
   const long q = r / m.F;
   const int t = q % m.T;
@@ -223,11 +231,14 @@ __global__ void __launch_bounds__(256)
 bn_clip_fwd_kernel(const float* __restrict__ x, long R, const float* __restrict__ mean, const float* __restrict__ rstd,
                    const float* __restrict__ gamma, const float* __restrict__ beta, float cap, int clip, TO* __restrict__ out,
                    ActMap m) {
-  const long total = R * m.C;
-  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int c = i % m.C;
-    const long r = i / m.C;
-    float v = (x[i] - mean[c]) * rstd[c] * gamma[c] + beta[c];
+  // thread <-> fixed channel (blockDim is a multiple of C), rows strided over the grid
+  const int C = m.C;
+  const int c = threadIdx.x % C;
+  const int rl = threadIdx.x / C, rstep = blockDim.x / C;
+  const float a = rstd[c] * gamma[c];
+  const float sh = beta[c] - mean[c] * a;
+  for (long r = (long)blockIdx.x * rstep + rl; r < R; r += (long)gridDim.x * rstep) {
+    float v = fmaf(x[r * C + c], a, sh);
     if (clip) v = fminf(fmaxf(v, 0.f), cap);
     stf(out + act_index(m, r, c), v);
   }
@@ -273,21 +284,22 @@ bn_clip_bwd_apply_kernel(const float* __restrict__ x, long R, const float* __res
                          const float* __restrict__ gamma, const float* __restrict__ beta, float cap, int clip,
                          const TG* __restrict__ dout, ActMap m, const double* __restrict__ sums, float* __restrict__ dx,
                          float* __restrict__ dgamma, float* __restrict__ dbeta) {
-  const long total = R * m.C;
-  const double invR = 1.0 / (double)R;
-  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int c = i % m.C;
-    const long r = i / m.C;
-    const float xh = (x[i] - mean[c]) * rstd[c];
-    const float bn = xh * gamma[c] + beta[c];
+  const int C = m.C;
+  const int c = threadIdx.x % C;
+  const int rl = threadIdx.x / C, rstep = blockDim.x / C;
+  const float mu = mean[c], rs = rstd[c], g = gamma[c], be = beta[c];
+  const float m1 = (float)(sums[c] / (double)R), m2 = (float)(sums[C + c] / (double)R);
+  const float gr = g * rs;
+  for (long r = (long)blockIdx.x * rstep + rl; r < R; r += (long)gridDim.x * rstep) {
+    const float xh = (x[r * C + c] - mu) * rs;
+    const float bn = fmaf(xh, g, be);
     float d = ldf(dout + act_index(m, r, c));
     if (clip && !(bn > 0.f && bn < cap)) d = 0.f;
-    const float m1 = (float)(sums[c] * invR), m2 = (float)(sums[m.C + c] * invR);
-    dx[i] = gamma[c] * rstd[c] * (d - m1 - xh * m2);
+    dx[r * C + c] = gr * (d - m1 - xh * m2);
   }
-  if (blockIdx.x == 0 && threadIdx.x < m.C) {
+  if (blockIdx.x == 0 && threadIdx.x < C) {
     if (dbeta) dbeta[threadIdx.x] = (float)sums[threadIdx.x];
-    if (dgamma) dgamma[threadIdx.x] = (float)sums[m.C + threadIdx.x];
+    if (dgamma) dgamma[threadIdx.x] = (float)sums[C + threadIdx.x];
   }
 }
 
@@ -472,9 +484,9 @@ extern "C" int ds2_bn_clip_fwd(const float* x, int B, int T, int F, int C, const
   const long R = (long)B * T * F;
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   if (out_dtype == DS2_F32)
-    bn_clip_fwd_kernel<float><<<ew_grid(R * C), 256, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, static_cast<float*>(out), m);
+    bn_clip_fwd_kernel<float><<<ew_grid(R * C), (256 / C) * C, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, static_cast<float*>(out), m);
   else
-    bn_clip_fwd_kernel<__nv_bfloat16><<<ew_grid(R * C), 256, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, static_cast<__nv_bfloat16*>(out), m);
+    bn_clip_fwd_kernel<__nv_bfloat16><<<ew_grid(R * C), (256 / C) * C, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, static_cast<__nv_bfloat16*>(out), m);
   DS2_LAUNCH_CHECK("bn_clip_fwd_kernel");
   count_launch();
   return DS2_OK;
@@ -497,12 +509,12 @@ extern "C" int ds2_bn_clip_bwd(const float* x, int B, int T, int F, int C, const
     const float* d = static_cast<const float*>(dout);
     bn_clip_bwd_reduce_kernel<float><<<grid, (256 / C) * C, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, d, m, sums_scratch);
     DS2_LAUNCH_CHECK("bn_clip_bwd_reduce_kernel");
-    bn_clip_bwd_apply_kernel<float><<<ew_grid(R * C), 256, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, d, m, sums_scratch, dx, dgamma, dbeta);
+    bn_clip_bwd_apply_kernel<float><<<ew_grid(R * C), (256 / C) * C, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, d, m, sums_scratch, dx, dgamma, dbeta);
   } else {
     const __nv_bfloat16* d = static_cast<const __nv_bfloat16*>(dout);
     bn_clip_bwd_reduce_kernel<__nv_bfloat16><<<grid, (256 / C) * C, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, d, m, sums_scratch);
     DS2_LAUNCH_CHECK("bn_clip_bwd_reduce_kernel");
-    bn_clip_bwd_apply_kernel<__nv_bfloat16><<<ew_grid(R * C), 256, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, d, m, sums_scratch, dx, dgamma, dbeta);
+    bn_clip_bwd_apply_kernel<__nv_bfloat16><<<ew_grid(R * C), (256 / C) * C, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, d, m, sums_scratch, dx, dgamma, dbeta);
   }
   DS2_LAUNCH_CHECK("bn_clip_bwd_apply_kernel");
   count_launch(2);
