@@ -321,21 +321,19 @@ extern "C" int ds2_gemm_bf16(const void* A, long lda, int a_mn_major, const void
 extern "C" int ds2_gemm_bf16_splitk(const void* A, long lda, int a_mn_major, const void* B, long ldb, int b_mn_major, float* C,
                                     long ldc, int M, int N, int K, float alpha, const float* bias, int splits, void* stream) {
   if (splits <= 0) {
-    // auto: the split count (<= 8, each split keeping >= 8 K-blocks) that wastes the fewest CTA-slots in the
-    // last wave of the persistent grid; ties go to fewer splits (less atomic traffic)
+    // auto: split K only when the output has too few tiles to occupy half the SMs (the red.add epilogue and the
+    // zero-fill cost more than a partially filled last wave: measured on dW [3520x2400] / dU [1760x1760]);
+    // then use as many splits as fit the SMs, each keeping at least 8 K-blocks.
     const int bn = (N <= 32) ? 32 : (N <= 128 ? 128 : 256);
     const int tiles = ((M + ds2::BM - 1) / ds2::BM) * ((N + bn - 1) / bn);
     const int sms = ds2::num_sms();
     const int num_kb = (K + ds2::BK - 1) / ds2::BK;
-    double best = 1e30;
     splits = 1;
-    for (int s = 1; s <= 8; ++s) {
-      if (s > 1 && num_kb / s < 8) break;
-      const long work = (long)tiles * s;
-      const long waves = (work + sms - 1) / sms;
-      // time ~ waves * (K-blocks per split + fixed per-tile cost of ~6 K-blocks for prologue/epilogue)
-      const double cost = (double)waves * ((double)num_kb / s + 6.0);
-      if (cost < best * 0.97) { best = cost; splits = s; }
+    if (tiles * 2 <= sms) {
+      splits = sms / tiles;
+      if (splits > 32) splits = 32;
+      if (splits > num_kb / 8) splits = num_kb / 8;
+      if (splits < 1) splits = 1;
     }
   }
   return ds2::gemm_bf16_launch(A, lda, a_mn_major, B, ldb, b_mn_major, C, DS2_F32, ldc, M, N, K, alpha, 0.f, bias, splits,
