@@ -43,6 +43,10 @@ _SIGS = {
     "ds2_rnn_relu_persistent_supported": (I, [I, I, I]),
     "ds2_gru_fwd": (I, [P, F, P, P, P, P, P, P, I, I, I, I, I, I, P]),
     "ds2_gru_bwd": (I, [P, P, P, P, P, P, P, P, I, I, I, I, I, I, P]),
+    "ds2_gru_persistent_supported": (I, [I, I, I]),
+    "ds2_gru_workspace_bytes": (SZ, [I, I, I, I]),
+    "ds2_gru_persistent_fwd": (I, [P, F, P, P, P, P, P, P, I, I, I, I, I, P, SZ, P]),
+    "ds2_gru_persistent_bwd": (I, [P, P, P, P, P, P, P, I, I, I, I, I, P, SZ, P]),
     "ds2_conv2d_fwd": (I, [P, I, P, P, P, I, I, I, I, I, I, I, I, I, P]),
     "ds2_conv2d_dgrad": (I, [P, P, P, I, I, I, I, I, I, I, I, I, P]),
     "ds2_conv2d_wgrad": (I, [P, I, P, P, P, I, I, I, I, I, I, I, I, I, P]),

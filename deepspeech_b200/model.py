@@ -119,12 +119,12 @@ class DeepSpeech2(torch.nn.Module):
             W, U, Bv = self.rnn_W[l][d * G * H:(d + 1) * G * H], self.rnn_U[l][d:d + 1], self.rnn_B[l][d:d + 1]
             BU = self.rnn_BU[l][d:d + 1] if self.cell == "gru" else None
         if self.cell == "gru":
-            return ops.bigru_layer(x, W, U, Bv, BU, self._lens, reverse_mask, out_dtype)
+            return ops.bigru_layer(x, W, U, Bv, BU, self._lens, reverse_mask, self.use_bf16, out_dtype)
         return ops.birnn_layer(x, W, U, Bv, self._lens, reverse_mask, self.use_bf16, out_dtype)
 
     def recurrent_stack(self, x: torch.Tensor, rnn_lens_dev: torch.Tensor) -> torch.Tensor:
         self._lens = rnn_lens_dev
-        act = torch.bfloat16 if (self.use_bf16 and self.cell != "gru") else torch.float32
+        act = torch.bfloat16 if self.use_bf16 else torch.float32
         if self.wiring == "as_written":                      # only the last layer is live
             return self._layer(x, self.L - 1, (0, 1), 0b10, act)
         if self.wiring == "stacked":

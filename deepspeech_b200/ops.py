@@ -396,61 +396,89 @@ def birnn_layer(x, Wcat, U, bias, lens, reverse_mask: int, want_bf16: bool, out_
     return _BiRNNLayerFn.apply(x, Wcat.contiguous(), U.contiguous(), bias.contiguous(), lens, reverse_mask, want_bf16, out_dtype)
 
 
+def gru_path_dtype(B: int, H: int, ND: int, want_bf16: bool):
+    """bf16 (persistent tcgen05 GRU kernel) when requested and the shape is taken, else fp32."""
+    if want_bf16 and lib.ds2_gru_persistent_supported(B, H, ND):
+        return torch.bfloat16
+    return torch.float32
+
+
 class _BiGRULayerFn(torch.autograd.Function):
-    """GRU analogue of _BiRNNLayerFn (build-defined, see include/ds2_b200.h).  fp32 path."""
+    """GRU analogue of _BiRNNLayerFn (build-defined, see include/ds2_b200.h).
+       x [T,B,I]; Wcat [ND*3H, I]; U [ND,3H,H]; bw, bu [ND,3H].  bf16 path: tcgen05 GEMMs for W x, dW, dx, dU and the
+       persistent recurrence kernels; fp32 path: strided GEMMs and per-step kernels."""
 
     @staticmethod
-    def forward(ctx, x, Wcat, U, bw, bu, lens, reverse_mask, out_dtype):
+    def forward(ctx, x, Wcat, U, bw, bu, lens, reverse_mask, want_bf16, out_dtype):
         T, B, I = x.shape
         ND, H = U.shape[0], U.shape[2]
         dev = x.device
-        xg = cast(x.contiguous(), torch.float32)
-        wx = gemm_nt(xg.view(T * B, I), Wcat)                                      # [TB, ND*3H]
-        hs = torch.empty((ND, T, B, H), dtype=torch.float32, device=dev)
-        gates = torch.empty((ND, T, B, 4 * H), dtype=torch.float32, device=dev)
-        check(lib.ds2_gru_fwd(_p(wx), SBN_SCALE, _p(U), _p(bw), _p(bu), _p(lens), _p(hs), _p(gates), DS2_F32, T, B, H, ND,
-                              reverse_mask, _stream()), "ds2_gru_fwd")
+        cdt = gru_path_dtype(B, H, ND, want_bf16)
+        hs = torch.empty((ND, T, B, H), dtype=cdt, device=dev)
+        gates = torch.empty((ND, T, B, 4 * H), dtype=cdt, device=dev)
+        if cdt == torch.bfloat16:
+            xg, Wg, Ug = cast(x.contiguous(), torch.bfloat16), cast(Wcat, torch.bfloat16), cast(U, torch.bfloat16)
+            wx = gemm_nt(xg.view(T * B, I), Wg)                                    # [TB, ND*3H] fp32
+            wsb = lib.ds2_gru_workspace_bytes(T, B, H, ND)
+            ws = _workspace(wsb, dev, "gru")
+            check(lib.ds2_gru_persistent_fwd(_p(wx), SBN_SCALE, _p(Ug), _p(bw), _p(bu), _p(lens), _p(hs), _p(gates), T, B, H,
+                                             ND, reverse_mask, _p(ws), wsb, _stream()), "ds2_gru_persistent_fwd")
+        else:
+            xg, Wg, Ug = cast(x.contiguous(), torch.float32), Wcat, U
+            wx = gemm_nt(xg.view(T * B, I), Wg)
+            check(lib.ds2_gru_fwd(_p(wx), SBN_SCALE, _p(Ug), _p(bw), _p(bu), _p(lens), _p(hs), _p(gates), DS2_F32, T, B, H, ND,
+                                  reverse_mask, _stream()), "ds2_gru_fwd")
         out = add2(hs[0], hs[1], out_dtype) if ND == 2 else cast(hs[0], out_dtype)
-        ctx.save_for_backward(xg, Wcat, U, hs, gates, lens)
+        ctx.save_for_backward(xg, Wg, Ug, hs, gates, lens)
         ctx.meta = (T, B, I, H, ND, reverse_mask, x.dtype)
         return out
 
     @staticmethod
     def backward(ctx, dout):
-        xg, Wcat, U, hs, gates, lens = ctx.saved_tensors
+        xg, Wg, Ug, hs, gates, lens = ctx.saved_tensors
         T, B, I, H, ND, reverse_mask, xdtype = ctx.meta
         dev = xg.device
+        cdt = hs.dtype
+        G = ND * 3 * H
         dout = cast(dout.contiguous(), torch.float32)
-        dgi = torch.empty((T * B, ND * 3 * H), dtype=torch.float32, device=dev)
-        dgh = torch.empty((T * B, ND * 3 * H), dtype=torch.float32, device=dev)
-        dhz = torch.zeros((ND, B, H), dtype=torch.float32, device=dev)
-        check(lib.ds2_gru_bwd(_p(dout), _p(U), _p(lens), _p(hs), _p(gates), _p(dgi), _p(dgh), _p(dhz), DS2_F32, T, B, H, ND,
-                              reverse_mask, _stream()), "ds2_gru_bwd")
-        dbw = colsum(dgi, T * B, ND * 3 * H, ND * 3 * H).view(ND, 3 * H)
-        dbu = colsum(dgh, T * B, ND * 3 * H, ND * 3 * H).view(ND, 3 * H)
-        dW = gemm_nt(dgi, xg.view(T * B, I), a_mn=True, b_mn=True, alpha=SBN_SCALE)
+        dgi = torch.empty((T * B, G), dtype=cdt, device=dev)
+        dgh = torch.empty((T * B, G), dtype=cdt, device=dev)
+        if cdt == torch.bfloat16:
+            wsb = lib.ds2_gru_workspace_bytes(T, B, H, ND)
+            ws = _workspace(wsb, dev, "gru")
+            check(lib.ds2_gru_persistent_bwd(_p(dout), _p(Ug), _p(lens), _p(hs), _p(gates), _p(dgi), _p(dgh), T, B, H, ND,
+                                             reverse_mask, _p(ws), wsb, _stream()), "ds2_gru_persistent_bwd")
+        else:
+            dhz = torch.zeros((ND, B, H), dtype=torch.float32, device=dev)
+            check(lib.ds2_gru_bwd(_p(dout), _p(Ug), _p(lens), _p(hs), _p(gates), _p(dgi), _p(dgh), _p(dhz), DS2_F32, T, B, H,
+                                  ND, reverse_mask, _stream()), "ds2_gru_bwd")
+        dbw = colsum(dgi, T * B, G, G).view(ND, 3 * H)
+        dbu = colsum(dgh, T * B, G, G).view(ND, 3 * H)
+        dW = torch.empty((G, I), dtype=torch.float32, device=dev)
+        gemm_wgrad(dgi, xg.view(T * B, I), G, I, T * B, G, I, dW, alpha=SBN_SCALE)
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = gemm_nt(dgi, Wcat, b_mn=True, alpha=SBN_SCALE).view(T, B, I)
+            dx = gemm_nt(dgi, Wg, b_mn=True, alpha=SBN_SCALE).view(T, B, I)
             if xdtype != torch.float32:
                 dx = cast(dx, xdtype)
+        # dU[d] = sum_t dgh[d,t]^T h[d,t_prev]
         dU = torch.empty((ND, 3 * H, H), dtype=torch.float32, device=dev)
         for d in range(ND):
             rev = (reverse_mask >> d) & 1
             if T > 1:
-                a_off = (0 if rev else B * ND * 3 * H) + d * 3 * H
+                a_off = (0 if rev else B * G) + d * 3 * H
                 A = dgh.view(-1)[a_off:]
                 Bm = hs[d].reshape(T * B, H)[(B if rev else 0):]
-                gemm_nt(A, Bm, a_mn=True, b_mn=True, M=3 * H, N=H, K=(T - 1) * B, lda=ND * 3 * H, ldb=H, out=dU[d])
+                gemm_wgrad(A, Bm, 3 * H, H, (T - 1) * B, G, H, dU[d])
             else:
                 dU[d].zero_()
-        return dx, dW, dU, dbw, dbu, None, None, None
+        return dx, dW, dU, dbw, dbu, None, None, None, None
 
 
-def bigru_layer(x, Wcat, U, bw, bu, lens, reverse_mask: int, out_dtype):
+def bigru_layer(x, Wcat, U, bw, bu, lens, reverse_mask: int, want_bf16: bool, out_dtype):
     _need_cuda(x, Wcat, U, bw, bu, lens)
     return _BiGRULayerFn.apply(x, Wcat.contiguous(), U.contiguous(), bw.contiguous(), bu.contiguous(), lens, reverse_mask,
-                               out_dtype)
+                               want_bf16, out_dtype)
 
 
 # ------------------------------------------------------------------------------------ linear

@@ -116,6 +116,18 @@ int ds2_gru_fwd(const float* wx, float scale, const void* u, const float* bw, co
                 void* gates, int dtype, int T, int B, int H, int ND, int reverse_mask, void* stream);
 int ds2_gru_bwd(const float* dout, const void* u, const int* lens, const void* hs, const void* gates, void* dgi, void* dgh,
                 float* dhz_scratch, int dtype, int T, int B, int H, int ND, int reverse_mask, void* stream);
+/* Persistent tcgen05 form of the same GRU (one launch per layer and pass, U resident in TMEM): u, hs, gates, dgi, dgh
+ * are bf16, wx/dout/bw/bu fp32, same layouts as above.  ds2_gru_persistent_supported says whether (B,H,ND) fits
+ * (B in {16,32}, H%8==0, 3 gates x H/4 columns of U + accumulators within 512 TMEM columns: H <= 1024 at B=32);
+ * workspace = ds2_gru_workspace_bytes (step counters + U^T for the backward), the caller owns it. */
+int ds2_gru_persistent_supported(int B, int H, int ND);
+size_t ds2_gru_workspace_bytes(int T, int B, int H, int ND);
+int ds2_gru_persistent_fwd(const float* wx, float scale, const void* u, const float* bw, const float* bu, const int* lens,
+                           void* hs, void* gates, int T, int B, int H, int ND, int reverse_mask, void* workspace,
+                           size_t workspace_bytes, void* stream);
+int ds2_gru_persistent_bwd(const float* dout, const void* u, const int* lens, const void* hs, const void* gates, void* dgi,
+                           void* dgh, int T, int B, int H, int ND, int reverse_mask, void* workspace, size_t workspace_bytes,
+                           void* stream);
 
 /* ---- conv front-end -------------------------------------------------------------------------
  * tf.nn.conv2d + bias_add at src/deepSpeech_NCHW.py:120-127,:142-151 (src/deepSpeech.py:120-126,

@@ -292,7 +292,7 @@ def test_bigru_layer_fp32_vs_oracle(T, B, I, H, lens):
     stk = lambda k: torch.stack([lp["fw"][k], lp["bw"][k]], 0).detach().float().to(dev).requires_grad_(True)
     x = x64.detach().float().to(dev).requires_grad_(True)
     W, U, BW, BU = cat("W"), stk("U"), stk("BW"), stk("BU")
-    out = ops.bigru_layer(x, W, U, BW, BU, torch.tensor(lens, dtype=torch.int32, device=dev), 0b10, torch.float32)
+    out = ops.bigru_layer(x, W, U, BW, BU, torch.tensor(lens, dtype=torch.int32, device=dev), 0b10, False, torch.float32)
     (out * g.float().to(dev)).sum().backward()
     assert relerr(out.detach().cpu().numpy(), ref.detach().numpy()) < 1e-5
     assert relerr(x.grad.cpu().numpy(), x64.grad.numpy()) < 1e-3
@@ -384,3 +384,48 @@ def test_birnn_layer_bf16_persistent_vs_oracle(T, B, I, H, ragged):
     check(lib.ds2_rnn_relu_bwd(p(dout), p(U32), p(lens_d), p(hs32), p(dz_f), DS2_F32, T, B, H, 2, 2, 20.0, None, 0, st()), "bwd32")
     torch.cuda.synchronize()
     assert relerr(dz_b.float().cpu().numpy(), dz_f.cpu().numpy()) < 2e-2
+
+
+@pytest.mark.parametrize("T,B,I,H,ragged", [(5, 32, 64, 64, False), (9, 32, 128, 256, True), (7, 16, 72, 200, True),
+                                             (4, 32, 256, 800, False), (20, 32, 64, 1024, True), (6, 64, 64, 328, True)])
+def test_bigru_layer_bf16_persistent_vs_oracle(T, B, I, H, ragged):
+    """Persistent tcgen05 GRU (bf16 operands, fp32 accumulation and gate math) against the fp64 oracle on the SAME
+    bf16-rounded weights: outputs <= 1e-2 of the output scale; the GRU has no hard mask, so gradients are compared
+    element-wise too (<= 3e-2 of each gradient's scale: activations and gate gradients are stored in bf16)."""
+    ops = _ops()
+    from deepspeech_b200._lib import lib
+    assert lib.ds2_gru_persistent_supported(B, H, 2) == 1
+    rng = np.random.default_rng(T * 17 + H)
+    bf = lambda a: torch.tensor(a, dtype=torch.float32).to(torch.bfloat16).double()
+    lp = {}
+    for d in ("fw", "bw"):
+        lp[d] = {"W": bf(rng.standard_normal((3 * H, I)) * (1.0 / np.sqrt(I))).requires_grad_(True),
+                 "U": bf(rng.standard_normal((3 * H, H)) * (1.0 / np.sqrt(H))).requires_grad_(True),
+                 "BW": torch.tensor(rng.standard_normal(3 * H) * 0.1).float().double().requires_grad_(True),
+                 "BU": torch.tensor(rng.standard_normal(3 * H) * 0.1).float().double().requires_grad_(True)}
+    x64 = bf(rng.standard_normal((T, B, I))).requires_grad_(True)
+    lens = [T] * B
+    if ragged:
+        lens = [T] + [int(v) for v in rng.integers(1, T + 1, size=B - 1)]
+    ref = O.rnn_direction(x64, lens, lp["fw"], False, cell="gru") + O.rnn_direction(x64, lens, lp["bw"], True, cell="gru")
+    g = torch.tensor(rng.standard_normal((T, B, H)))
+    (ref * g).sum().backward()
+    dev = "cuda"
+    x = x64.detach().to(torch.bfloat16).to(dev).requires_grad_(True)
+    cat = lambda k: torch.cat([lp["fw"][k], lp["bw"][k]], 0).detach().float().to(dev).requires_grad_(True)
+    stk = lambda k: torch.stack([lp["fw"][k], lp["bw"][k]], 0).detach().float().to(dev).requires_grad_(True)
+    W, U, BW, BU = cat("W"), stk("U"), stk("BW"), stk("BU")
+    n0 = lib.ds2_launch_count()
+    out = ops.bigru_layer(x, W, U, BW, BU, torch.tensor(lens, dtype=torch.int32, device=dev), 0b10, True, torch.float32)
+    (out * g.float().to(dev)).sum().backward()
+    torch.cuda.synchronize()
+    assert lib.ds2_launch_count() - n0 < 40          # one recurrence launch per pass, not one per step
+    o = out.detach().cpu().numpy()
+    assert relerr(o, ref.detach().numpy()) < 1e-2
+    for b, n in enumerate(lens):
+        assert np.abs(o[n:, b]).max(initial=0.0) == 0.0
+    assert relerr(x.grad.float().cpu().numpy(), x64.grad.numpy()) < 3e-2
+    assert relerr(W.grad.cpu().numpy(), torch.cat([lp["fw"]["W"].grad, lp["bw"]["W"].grad], 0).numpy()) < 3e-2
+    assert relerr(U.grad.cpu().numpy(), torch.stack([lp["fw"]["U"].grad, lp["bw"]["U"].grad], 0).numpy()) < 3e-2
+    assert relerr(BW.grad.cpu().numpy(), torch.stack([lp["fw"]["BW"].grad, lp["bw"]["BW"].grad], 0).numpy()) < 3e-2
+    assert relerr(BU.grad.cpu().numpy(), torch.stack([lp["fw"]["BU"].grad, lp["bw"]["BU"].grad], 0).numpy()) < 3e-2

@@ -92,6 +92,63 @@ def test_model_fp32_loss_and_grads_vs_oracle(layout, wiring, cell):
         assert g["rnn.0.W"] is None           # dead layers get no gradient, as in the reference (TF prunes them)
 
 
+def test_model_uni_dir_vs_oracle():
+    """rnn_type='uni-dir' (src/deepSpeech.py:173-177): the forward stack alone; the backward-direction weights get
+    no gradient."""
+    from deepspeech_b200 import deepSpeech as mod
+    p, layers, feats, seq_lens, sparse = _small_case(29, wiring="two_stack")
+    cfg = dict(layout="NHWC", wiring="two_stack", bidirectional=False)
+    ref_loss, ref_logits = _oracle_run(feats, seq_lens, sparse, p, layers, cfg)
+    params = SimpleNamespace(use_fp16=False, num_filters=4, batch_size=3, num_hidden=16, num_rnn_layers=2, engine="mkl",
+                             rnn_type="uni-dir", wiring="two_stack", seed=3)
+    m = mod.model(params)
+    m.load_oracle_params({k: v.detach() for k, v in p.items()},
+                         [{d: {k: v.detach() for k, v in q.items()} for d, q in lp.items()} for lp in layers])
+    m.zero_grad(set_to_none=True)
+    logits = mod.inference(None, torch.tensor(feats, device="cuda"), seq_lens, params)
+    loss = mod.loss(logits, sparse, seq_lens)
+    loss.backward()
+    torch.cuda.synchronize()
+    assert abs(loss.item() - ref_loss) <= 1e-4 * abs(ref_loss)
+    assert relerr(logits.detach().cpu().numpy(), ref_logits) < 1e-4
+    g = m.oracle_grads()
+    H = 16
+    for l, lp in enumerate(layers):
+        assert relerr(g["rnn.%d.W" % l][:H], lp["fw"]["W"].grad.numpy()) < 1e-3
+        assert relerr(g["rnn.%d.U" % l][0], lp["fw"]["U"].grad.numpy()) < 1e-3
+        assert lp["bw"]["U"].grad is None or float(lp["bw"]["U"].grad.abs().max()) == 0.0
+        assert np.abs(g["rnn.%d.U" % l][1]).max() == 0.0
+
+
+@pytest.mark.parametrize("cell", ["relu_clip", "gru"])
+def test_model_bf16_persistent_kernels_vs_oracle(cell):
+    """bf16 model at a batch the persistent recurrence kernels take (B=16): logits <= 1e-2 against the fp64 oracle,
+    and the per-layer recurrence really is one launch (launch count far below T per layer)."""
+    from deepspeech_b200 import deepSpeech_NCHW as mod
+    from deepspeech_b200._lib import lib
+    p, layers, feats, seq_lens, sparse = _small_case(31, B=16, T=101, nf=8, H=64, L=2, cell=cell, ragged=True)
+    ref_loss, ref_logits = _oracle_run(feats, seq_lens, sparse, p, layers, dict(layout="NCHW", wiring="stacked", cell=cell))
+    params = SimpleNamespace(use_fp16=True, num_filters=8, batch_size=16, num_hidden=64, num_rnn_layers=2, engine="mkl",
+                             rnn_type="bi-dir", wiring="stacked", cell=cell, seed=5)
+    m = mod.model(params)
+    m.load_oracle_params({k: v.detach() for k, v in p.items()},
+                         [{d: {k: v.detach() for k, v in q.items()} for d, q in lp.items()} for lp in layers])
+    m.zero_grad(set_to_none=True)
+    n0 = lib.ds2_launch_count()
+    logits = mod.inference(None, torch.tensor(feats, device="cuda"), seq_lens, params)
+    loss = mod.loss(logits, sparse, seq_lens)
+    loss.backward()
+    torch.cuda.synchronize()
+    assert lib.ds2_launch_count() - n0 < 150
+    assert relerr(logits.detach().cpu().numpy(), ref_logits) < 1e-2
+    assert abs(loss.item() - ref_loss) <= 2e-2 * abs(ref_loss)
+    g = m.oracle_grads()
+    lp = layers[0]
+    a = g["rnn.0.U"].ravel()
+    b = torch.stack([lp["fw"]["U"].grad, lp["bw"]["U"].grad], 0).numpy().ravel()
+    assert float(a @ b / (np.linalg.norm(a) * np.linalg.norm(b))) > 0.99
+
+
 def test_model_bf16_logits_vs_fp32_oracle():
     """bf16 tensor-core path against the fp64 oracle: <= 1e-2 on logits (of the logits' scale)."""
     from deepspeech_b200 import deepSpeech_NCHW as mod
