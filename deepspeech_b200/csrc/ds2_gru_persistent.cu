@@ -38,6 +38,7 @@ struct GruParams {
   int NC, NI, tiles_m, ksl, nbox;   // batch chunks, instances per chunk, M tiles per direction, K-slice length
                                     // (multiple of 64), boxes per slice
   float scale;
+  int fenced;                   // see RnnPersistParams::fenced (ds2_rnn_persistent.cu)
 };
 
 __device__ __forceinline__ uint32_t g_cluster_ctarank() {
@@ -101,8 +102,8 @@ __device__ __forceinline__ void g_unpack4(uint2 v, float (&o)[4]) {
 __device__ __forceinline__ uint2 g_pack4(const float (&o)[4]) {
   uint2 pk;
   __nv_bfloat162 a = __floats2bfloat162_rn(o[0], o[1]), b = __floats2bfloat162_rn(o[2], o[3]);
-  pk.x = *reinterpret_cast<uint32_t*>(&a);
-  pk.y = *reinterpret_cast<uint32_t*>(&b);
+  pk.x = scrub_fill(*reinterpret_cast<uint32_t*>(&a));
+  pk.y = scrub_fill(*reinterpret_cast<uint32_t*>(&b));
   return pk;
 }
 
@@ -145,6 +146,9 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
   uint64_t* slab_bar = b_ready + 2;
   uint8_t* sB = smem + L.b_off + inst * nbox * (GBP * 128);
   float* slab = reinterpret_cast<float*>(smem + L.slab_off) + inst * GKS * 32 * NG * GBP;
+  // shared-space addresses used inside the step loop, computed once
+  const uint32_t b_ready_a = keep_reg(smem_u32(b_ready)), mma_bar_a = b_ready_a + 8, slab_bar_a = b_ready_a + 16;
+  const uint32_t sB_addr = keep_reg(smem_u32(sB)), slab_local = keep_reg(smem_u32(slab));
 
   const uint32_t rank = g_cluster_ctarank();
   const int mt = blockIdx.y, chunk = blockIdx.z / p.ND, d = blockIdx.z % p.ND;
@@ -210,10 +214,10 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
   if (w_in == 0) {
     // =========================== control warp of this instance: MMA issue ===========================
     const uint32_t idesc = umma_idesc_bf16(128, GBP, 0, 0);
-    const uint32_t b0 = smem_u32(sB);
+    const uint32_t b0 = sB_addr;
     uint32_t ph = 0;
     for (int step = 1; step < T; ++step) {
-      mbar_wait(b_ready, ph, 30);
+      mbar_wait(b_ready_a, ph, 30);
       tc_fence_after();
       if (elect_one_sync()) {
 #pragma unroll
@@ -225,7 +229,7 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
                              umma_smem_desc_sw128(b0 + i * (GBP * 128) + k * 32, 16, 1024), idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
         }
-        umma_commit(mma_bar);
+        umma_commit(mma_bar_a);
       }
       __syncwarp();
       ph ^= 1;
@@ -240,8 +244,7 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
     const int j = m0 + 32 * (int)rank + 4 * jg;  // first of 4 consecutive hidden units
     const bool jvalid = j < H;
     const int len_b = p.lens[b];
-    const uint32_t slab_local = smem_u32(slab);
-    const uint32_t slab_bar_local = smem_u32(slab_bar);
+    const uint32_t slab_bar_local = slab_bar_a;
     // moving operand: forward h_{t-1} (rows of hs[d]), backward dgh_{t+1} (rows of dgh, direction offset d*3H)
     const __nv_bfloat16* src_dir = BWD ? p.dgh + (size_t)d * 3 * H : p.hs + (size_t)d * T * Bn * H;
     const long src_pitch = BWD ? (long)ND * 3 * H : (long)H;
@@ -301,12 +304,17 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) acc[g][i] = 0.f;
       if (step > 0) {
-        if (et == 0) mbar_arrive_expect_tx(slab_bar, GKS * 32 * NG * GBP * 4);
+        if (et == 0) mbar_arrive_expect_tx(slab_bar_a, GKS * 32 * NG * GBP * 4);
         if (et == 0) {
           const unsigned int need = ctas_per_dir * (unsigned int)step;
-          if (g_ld_acquire_u32(ctr) < need) {
+          if (p.fenced) {
+            if (g_ld_acquire_u32(ctr) < need) {
+              SpinGuard sg;
+              while (g_ld_acquire_u32(ctr) < need) sg.check(20);
+            }
+          } else if (ld_relaxed_gpu_u32(ctr) < need) {
             SpinGuard sg;
-            while (g_ld_acquire_u32(ctr) < need) sg.check(20);
+            while (ld_relaxed_gpu_u32(ctr) < need) sg.check(21);
           }
         }
         asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
@@ -318,13 +326,26 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
             v[m] = make_uint4(0u, 0u, 0u, 0u);
             if (goff[m] >= 0) v[m] = g_ld_relaxed_v4(rows + goff[m]);
           }
+          if (!p.fenced) {
+            // relaxed step counter: a row may still show the host's fill (common.cuh); reload until it landed
+#pragma unroll
+            for (int m = 0; m < GMAX_UNITS; ++m) {
+              if (goff[m] >= 0 && unit_stale(v[m])) {
+                SpinGuard sg;
+                do {
+                  v[m] = g_ld_relaxed_v4(rows + goff[m]);
+                  sg.check(22);
+                } while (unit_stale(v[m]));
+              }
+            }
+          }
 #pragma unroll
           for (int m = 0; m < GMAX_UNITS; ++m)
-            if (soff[m] >= 0) *reinterpret_cast<uint4*>(sB + soff[m]) = v[m];
+            if (soff[m] >= 0) sts_v4(sB_addr + soff[m], v[m]);
           fence_proxy_async();
-          mbar_arrive(b_ready);
+          mbar_arrive(b_ready_a);
         }
-        mbar_wait(mma_bar, ph, 40);
+        mbar_wait(mma_bar_a, ph, 40);
         tc_fence_after();
         // partial sums of this CTA's K slice -> the cluster CTA that finishes those 32 units (all gates)
 #pragma unroll
@@ -339,13 +360,13 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
           for (int c = 0; c < 4; ++c) g_st_async_v4(dst + c * 16, rbar, r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
         }
         tc_fence_before();
-        mbar_wait(slab_bar, ph, 50);
+        mbar_wait(slab_bar_a, ph, 50);
 #pragma unroll
         for (int s = 0; s < GKS; ++s)
 #pragma unroll
           for (int g = 0; g < NG; ++g)
 #pragma unroll
-            for (int i = 0; i < 4; ++i) acc[g][i] += slab[((s * 32 + 4 * jg + i) * NG + g) * GBP + bl];
+            for (int i = 0; i < 4; ++i) acc[g][i] += lds_f32(slab_local + (((s * 32 + 4 * jg + i) * NG + g) * GBP + bl) * 4);
         ph ^= 1;
       }
       if (jvalid) {
@@ -404,7 +425,10 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
         }
       }
       asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
-      if (et == 0) g_red_release_add(ctr, 1u);
+      if (et == 0) {
+        if (p.fenced) g_red_release_add(ctr, 1u);
+        else red_relaxed_gpu_add(ctr, 1u);
+      }
     }
   }
   tc_fence_before();
@@ -502,6 +526,8 @@ int gru_fwd_persist(const float* wx, float scale, const void* u, const float* bw
   p.gates = static_cast<__nv_bfloat16*>(gates); p.dgi = nullptr; p.dgh = nullptr;
   p.ctr = static_cast<unsigned int*>(ws);
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = scale;
+  p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
+  if (!p.fenced) DS2_CUDA(cudaMemsetAsync(hs, DS2_FILL_BYTE, (size_t)ND * T * B * H * 2, st));
   return gru_launch<false>(ta, p, smem, st);
 }
 
@@ -531,6 +557,8 @@ int gru_bwd_persist(const float* dout, const void* u, const int* lens, const voi
   p.dgi = static_cast<__nv_bfloat16*>(dgi); p.dgh = static_cast<__nv_bfloat16*>(dgh);
   p.ctr = static_cast<unsigned int*>(ws);
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = 1.f;
+  p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
+  if (!p.fenced) DS2_CUDA(cudaMemsetAsync(dgh, DS2_FILL_BYTE, (size_t)T * B * ND * 3 * H * 2, st));
   return gru_launch<true>(ta, p, smem, st);
 }
 

@@ -50,6 +50,9 @@ struct RnnPersistParams {
   int NI;                  // instances = B / BP
   int tiles_m, ksl, nbox;  // M tiles per direction, K-slice length (multiple of 64), boxes per slice
   float scale, cap;
+  int exp;                 // timing experiments (DS2_RNN_EXP, results are NOT valid when set)
+  int fenced;              // 1: release/acquire step counters (DS2_RNN_FENCED=1); 0: relaxed counters + self-validating
+                           // rows (see common.cuh, `out` must have been filled with DS2_FILL_BYTE)
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -81,16 +84,6 @@ __device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
 }
 __device__ __forceinline__ void red_release_add(unsigned int* p, unsigned int v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ bool has_sentinel(uint32_t w) { return ((w & 0xFFFFu) == 0xFFFFu) || ((w >> 16) == 0xFFFFu); }
-__device__ __forceinline__ bool unit_ready(const uint4& v) {
-  return !(has_sentinel(v.x) || has_sentinel(v.y) || has_sentinel(v.z) || has_sentinel(v.w));
-}
-// never emit the "not written yet" pattern: a negative NaN payload 0xFFFF becomes the positive one
-__device__ __forceinline__ uint32_t scrub_sentinel(uint32_t w) {
-  if ((w & 0xFFFFu) == 0xFFFFu) w &= 0xFFFF7FFFu;
-  if ((w >> 16) == 0xFFFFu) w &= 0x7FFFFFFFu;
-  return w;
 }
 // smem (matrix descriptor, same format as the MMA operand descriptors) -> TMEM, 128 lanes x 256 bits
 __device__ __forceinline__ void tmem_cp_128x256b(uint32_t taddr, uint64_t sdesc) {
@@ -130,8 +123,10 @@ __host__ __device__ inline RnnSmem rnn_smem_layout(int nbox, int NI) {
   return s;
 }
 
-template <bool BWD>
-__global__ void __launch_bounds__(INST_THREADS * MAX_NI, 1)
+// NIMAX bounds the block size (INST_THREADS * NI threads) and with it the registers a thread may use: the common
+// two-instance launch (B = 32) gets 168 registers, the four-instance one (B = 64) has to live with 96.
+template <bool BWD, int NIMAX>
+__global__ void __launch_bounds__(INST_THREADS * NIMAX, 1)
 rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p) {
   extern __shared__ uint8_t rnn_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(rnn_smem_raw) + 1023) & ~uintptr_t(1023));
@@ -151,6 +146,9 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
                                                             // cannot be a step ahead: it first acquires the step counter
   uint8_t* sB = smem + L.b_off + inst * nbox * (BP * 128);
   float* slab = reinterpret_cast<float*>(smem + L.slab_off) + inst * KS * 32 * BP;
+  // shared-space addresses used inside the step loop, computed once
+  const uint32_t b_ready_a = keep_reg(smem_u32(b_ready)), mma_bar_a = b_ready_a + 8, slab_bar_a = b_ready_a + 16;
+  const uint32_t sB_addr = keep_reg(smem_u32(sB)), slab_local = keep_reg(smem_u32(slab));
 
   const uint32_t rank = cluster_ctarank();                  // K slice owned by this CTA, rows it finishes
   const int mt = blockIdx.y, d = blockIdx.z;
@@ -201,10 +199,10 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
     mbar_wait(acp_bar, 0, 11);       // every instance's control warp: U is resident in TMEM
     tc_fence_after();
     const uint32_t idesc = umma_idesc_bf16(128, BP, 0, 0);
-    const uint32_t b0 = smem_u32(sB);
+    const uint32_t b0 = sB_addr;
     uint32_t ph = 0;
     for (int step = 1; step < T; ++step) {
-      mbar_wait(b_ready, ph, 30);    // loaders have written h_{t-1} (generic proxy) and fenced it to the async proxy
+      mbar_wait(b_ready_a, ph, 30);    // loaders have written h_{t-1} (generic proxy) and fenced it to the async proxy
       tc_fence_after();
       if (elect_one_sync()) {
         if (prof_cta && step < 1024) p.prof[step * 16 + 0] = dev_clock();
@@ -214,7 +212,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
             umma_bf16_ts(d_tmem, tmem_base + (i * 4 + k) * 8, umma_smem_desc_sw128(b0 + i * (BP * 128) + k * 32, 16, 1024), idesc,
                          (i > 0 || k > 0) ? 1u : 0u);
         }
-        umma_commit(mma_bar);
+        umma_commit(mma_bar_a);
         if (prof_cta && step < 1024) p.prof[step * 16 + 1] = dev_clock();
       }
       __syncwarp();
@@ -233,15 +231,14 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
 #pragma unroll
     for (int i = 0; i < 4; ++i) bias4[i] = (!BWD && jvalid) ? p.bias[d * H + j + i] : 0.f;
     const int len_b = p.lens[b];
-    const uint32_t slab_local = smem_u32(slab);
-    const uint32_t slab_bar_local = smem_u32(slab_bar);
+    const uint32_t slab_bar_local = slab_bar_a;
     // loader role: 16-byte units (8 consecutive k of one utterance) of this CTA's K slice
     const int cpr = p.ksl / 8;                   // units per utterance row
     const int nunits = BP * cpr;
     const __nv_bfloat16* src_dir = p.out + (size_t)d * p.out_dir_stride;
     // per-thread unit table, computed once: global element offset inside the step's row block (-1: no load,
     // the unit lies beyond H and is zero-filled) and swizzled byte offset inside this instance's B tile
-    long goff[MAX_UNITS];
+    int goff[MAX_UNITS];
     int soff[MAX_UNITS];
 #pragma unroll
     for (int m = 0; m < MAX_UNITS; ++m) {
@@ -252,7 +249,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
         const int ub = u / cpr, uc = u - ub * cpr;
         // box (uc/8) of [16 rows x 128 B], 16-byte chunk (uc%8) XOR-swizzled with the row (SWIZZLE_128B)
         soff[m] = (uc >> 3) * (BP * 128) + ub * 128 + (((uc & 7) ^ (ub & 7)) << 4);
-        if ((int)rank * p.ksl + uc * 8 < H) goff[m] = (long)ub * p.out_row_pitch + uc * 8;
+        if ((int)rank * p.ksl + uc * 8 < H) goff[m] = ub * (int)p.out_row_pitch + uc * 8;
       }
     }
     uint32_t ph = 0;
@@ -271,7 +268,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
       }
       float acc[4] = {0.f, 0.f, 0.f, 0.f};
       if (step > 0) {
-        if (et == 0) mbar_arrive_expect_tx(slab_bar, KS * 32 * BP * 4);           // arm this step's slab barrier
+        if (et == 0) mbar_arrive_expect_tx(slab_bar_a, KS * 32 * BP * 4);           // arm this step's slab barrier
         // ---- loader: poll h_{t-1}[inst's utterances][this CTA's K slice] until written, stage into smem
         if (pr) p.prof[step * 16 + 8] = dev_clock();
         {
@@ -280,9 +277,14 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
           // the named barrier hands that visibility to the other 127 loader threads
           if (et == 0) {
             const unsigned int need = ctas_per_dir * (unsigned int)step;
-            if (ld_acquire_u32(ctr) < need) {
+            if (p.fenced) {
+              if (!(p.exp & 2) && ld_acquire_u32(ctr) < need) {
+                SpinGuard g;
+                while (ld_acquire_u32(ctr) < need) g.check(20);
+              }
+            } else if (!(p.exp & 2) && ld_relaxed_gpu_u32(ctr) < need) {
               SpinGuard g;
-              while (ld_acquire_u32(ctr) < need) g.check(20);
+              while (ld_relaxed_gpu_u32(ctr) < need) g.check(21);
             }
           }
           asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
@@ -291,20 +293,33 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
 #pragma unroll
           for (int m = 0; m < MAX_UNITS; ++m) {
             v[m] = make_uint4(0u, 0u, 0u, 0u);
-            if (goff[m] >= 0) v[m] = ld_relaxed_v4(rows + goff[m]);
+            if (goff[m] >= 0 && !(p.exp & 4)) v[m] = ld_relaxed_v4(rows + goff[m]);
           }
           if (pr) p.prof[step * 16 + 9] = dev_clock();
+          if (!p.fenced && !(p.exp & 6)) {
+            // the counter was published without a fence: a row may still show the host's fill; reload until it landed
+#pragma unroll
+            for (int m = 0; m < MAX_UNITS; ++m) {
+              if (goff[m] >= 0 && unit_stale(v[m])) {
+                SpinGuard g;
+                do {
+                  v[m] = ld_relaxed_v4(rows + goff[m]);
+                  g.check(22);
+                } while (unit_stale(v[m]));
+              }
+            }
+          }
 #pragma unroll
           for (int m = 0; m < MAX_UNITS; ++m)
-            if (soff[m] >= 0) *reinterpret_cast<uint4*>(sB + soff[m]) = v[m];
+            if (soff[m] >= 0) sts_v4(sB_addr + soff[m], v[m]);
           if (pr) p.prof[step * 16 + 13] = dev_clock();
           fence_proxy_async();       // generic-proxy smem writes -> visible to the tensor core (async proxy)
           if (pr) p.prof[step * 16 + 14] = dev_clock();
-          mbar_arrive(b_ready);
+          mbar_arrive(b_ready_a);
         }
         if (pr) p.prof[step * 16 + 10] = dev_clock();
         // ---- epilogue part 1: partial sums of this CTA's K slice -> the CTA that finishes those rows
-        mbar_wait(mma_bar, ph, 40);
+        mbar_wait(mma_bar_a, ph, 40);
         tc_fence_after();
         if (pr) p.prof[step * 16 + 3] = dev_clock();
         uint32_t r[16];
@@ -321,13 +336,12 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
         }
         if (pr) p.prof[step * 16 + 12] = dev_clock();
         // ---- epilogue part 2: wait for the KS slabs of this step, reduce
-        mbar_wait(slab_bar, ph, 50);
+        mbar_wait(slab_bar_a, ph, 50);
         if (pr) p.prof[step * 16 + 5] = dev_clock();
-        const float* sl = slab;
 #pragma unroll
         for (int s = 0; s < KS; ++s) {
-          const float* sp = sl + (s * 32 + 4 * jg) * BP + bl;
-          acc[0] += sp[0]; acc[1] += sp[BP]; acc[2] += sp[2 * BP]; acc[3] += sp[3 * BP];
+          const uint32_t sp = slab_local + ((s * 32 + 4 * jg) * BP + bl) * 4;
+          acc[0] += lds_f32(sp); acc[1] += lds_f32(sp + BP * 4); acc[2] += lds_f32(sp + 2 * BP * 4); acc[3] += lds_f32(sp + 3 * BP * 4);
         }
         ph ^= 1;
       }
@@ -351,16 +365,19 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
         }
         uint2 pk;
         __nv_bfloat162 b0v = __floats2bfloat162_rn(o[0], o[1]), b1v = __floats2bfloat162_rn(o[2], o[3]);
-        pk.x = *reinterpret_cast<uint32_t*>(&b0v);
-        pk.y = *reinterpret_cast<uint32_t*>(&b1v);
+        pk.x = scrub_fill(*reinterpret_cast<uint32_t*>(&b0v));
+        pk.y = scrub_fill(*reinterpret_cast<uint32_t*>(&b1v));
         __nv_bfloat16* dstp = p.out + (size_t)d * p.out_dir_stride + ((size_t)t * Bn + b) * p.out_row_pitch + j;
         *reinterpret_cast<uint2*>(dstp) = pk;
       }
       if (pr) p.prof[step * 16 + 6] = dev_clock();
       // publish: the instance's 128 threads' stores -> one release increment of its step counter
       // (the CTA-level barrier orders their stores before thread 0's gpu-scope release: cumulativity)
-      asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
-      if (et == 0) red_release_add(ctr, 1u);
+      if (!(p.exp & 8)) asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
+      if (et == 0) {
+        if (p.fenced) red_release_add(ctr, 1u);
+        else red_relaxed_gpu_add(ctr, 1u);
+      }
       if (pr) p.prof[step * 16 + 7] = dev_clock();
     }
   }
@@ -407,13 +424,13 @@ size_t rnn_persist_workspace_bytes(int T, int B, int H, int ND) {
   return WS_CTR_BYTES + WS_PROF_BYTES + (size_t)ND * H * H * 2;
 }
 
-template <bool BWD>
-static int persist_launch(const CUtensorMap& ta, RnnPersistParams& p, size_t smem, cudaStream_t st) {
-  auto kern = rnn_persist_kernel<BWD>;
-  static bool attr_done[2] = {false, false};
-  if (!attr_done[BWD]) {
+template <bool BWD, int NIMAX>
+static int persist_launch_n(const CUtensorMap& ta, RnnPersistParams& p, size_t smem, cudaStream_t st) {
+  auto kern = rnn_persist_kernel<BWD, NIMAX>;
+  static bool attr_done = false;
+  if (!attr_done) {
     DS2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
-    attr_done[BWD] = true;
+    attr_done = true;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(KS, p.tiles_m, p.ND);
@@ -442,6 +459,11 @@ static int persist_launch(const CUtensorMap& ta, RnnPersistParams& p, size_t sme
   return DS2_OK;
 }
 
+template <bool BWD>
+static int persist_launch(const CUtensorMap& ta, RnnPersistParams& p, size_t smem, cudaStream_t st) {
+  return p.NI <= 2 ? persist_launch_n<BWD, 2>(ta, p, smem, st) : persist_launch_n<BWD, MAX_NI>(ta, p, smem, st);
+}
+
 static int persist_common(RnnPersistParams& p, size_t* smem, int T, int B, int H, int ND, void* ws, size_t ws_bytes, const char* who,
                           cudaStream_t st) {
   DS2_REQUIRE(persist_geometry(B, H, ND, &p.tiles_m, &p.ksl, &p.nbox, &p.NI, smem), DS2_ERR_UNSUPPORTED,
@@ -450,6 +472,8 @@ static int persist_common(RnnPersistParams& p, size_t* smem, int T, int B, int H
   DS2_REQUIRE(ws && ws_bytes >= need, DS2_ERR_WORKSPACE, "%s: workspace of %zu bytes required", who, need);
   DS2_CUDA(cudaMemsetAsync(ws, 0, WS_CTR_BYTES, st));
   p.ctr = static_cast<unsigned int*>(ws);
+  p.exp = getenv("DS2_RNN_EXP") ? atoi(getenv("DS2_RNN_EXP")) : 0;
+  p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
   p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(static_cast<char*>(ws) + WS_CTR_BYTES) : nullptr;
   return DS2_OK;
 }
@@ -466,6 +490,7 @@ int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const floa
   p.add_in = wx; p.bias = bias; p.lens = lens; p.hs_in = nullptr; p.out = static_cast<__nv_bfloat16*>(hs);
   p.out_row_pitch = H; p.out_dir_stride = (long)T * B * H;
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = scale; p.cap = cap;
+  if (!p.fenced) DS2_CUDA(cudaMemsetAsync(hs, DS2_FILL_BYTE, (size_t)ND * T * B * H * 2, st));
   return persist_launch<false>(ta, p, smem, st);
 }
 
@@ -489,6 +514,7 @@ int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, cons
   p.out = static_cast<__nv_bfloat16*>(dz);
   p.out_row_pitch = (long)ND * H; p.out_dir_stride = H;
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = 1.f; p.cap = cap;
+  if (!p.fenced) DS2_CUDA(cudaMemsetAsync(dz, DS2_FILL_BYTE, (size_t)T * B * ND * H * 2, st));
   return persist_launch<true>(ta, p, smem, st);
 }
 
