@@ -31,7 +31,8 @@ int cuda_fail(cudaError_t e, const char* what);
     }                                                              \
   } while (0)
 
-int num_sms();
+int num_sms();              // SM count of the current device, capped by ds2_set_sm_limit
+int set_sm_limit(int n);
 void count_launch(int n = 1);
 
 // ------------------------------------------------------------------ small device helpers

@@ -20,16 +20,25 @@ int cuda_fail(cudaError_t e, const char* what) {
   set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
   return DS2_ERR_CUDA;
 }
+static thread_local int g_sm_limit = 0;     // ds2_set_sm_limit: 0 = whole device
 int num_sms() {
   static int n[64] = {0};
   int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
-  if (!n[dev]) {
-    int v = 0;
-    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
-    n[dev] = v;
+  int v = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64) {
+    if (!n[dev]) {
+      int q = 0;
+      if (cudaDeviceGetAttribute(&q, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || q <= 0) q = 148;
+      n[dev] = q;
+    }
+    v = n[dev];
   }
-  return n[dev];
+  return (g_sm_limit > 0 && g_sm_limit < v) ? g_sm_limit : v;
+}
+int set_sm_limit(int n) {
+  const int prev = g_sm_limit;
+  g_sm_limit = n > 0 ? n : 0;
+  return prev;
 }
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
@@ -94,4 +103,6 @@ extern "C" size_t ds2_rnn_workspace_bytes(int T, int B, int H, int ND, int dtype
   if (dtype != DS2_BF16) return 0;
   return rnn_persist_workspace_bytes(T, B, H, ND);
 }
+extern "C" int ds2_set_sm_limit(int n) { return set_sm_limit(n); }
+
 extern "C" int ds2_rnn_relu_persistent_supported(int B, int H, int ND) { return rnn_persist_supported(B, H, ND); }

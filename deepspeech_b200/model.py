@@ -128,6 +128,14 @@ class DeepSpeech2(torch.nn.Module):
         if self.wiring == "as_written":                      # only the last layer is live
             return self._layer(x, self.L - 1, (0, 1), 0b10, act)
         if self.wiring == "stacked":
+            B = x.shape[1]
+            if self.use_bf16 and ops.rec_stack_supported(self.cell, B, self.H, 2):
+                # bf16 tensor-core path: the whole stack as one autograd node (backward overlaps dW/dU with recurrences)
+                if self.cell == "gru":
+                    lp = [(self.rnn_W[l], self.rnn_U[l], self.rnn_B[l], self.rnn_BU[l]) for l in range(self.L)]
+                else:
+                    lp = [(self.rnn_W[l], self.rnn_U[l], self.rnn_B[l]) for l in range(self.L)]
+                return ops.rec_stack(x, self._lens, self.cell, 0b10, act, lp)
             for l in range(self.L):
                 x = self._layer(x, l, (0, 1), 0b10, act)
             return x

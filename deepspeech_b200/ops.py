@@ -481,6 +481,202 @@ def bigru_layer(x, Wcat, U, bw, bu, lens, reverse_mask: int, want_bf16: bool, ou
                                want_bf16, out_dtype)
 
 
+# ------------------------------------------------------------------------------------ whole recurrent stack
+_aux_streams = {}
+OVERLAP_WGRAD = True          # weight-gradient GEMMs on a side stream next to the following layer's recurrence
+STACK_TRACE = None            # set to a list to collect (tag, layer, start_event, end_event) of the stack backward
+
+
+def _streams(device):
+    """(rec, side): a high-priority stream for the persistent recurrence kernels and a lowest-priority one for the
+    work that is off the critical path of the backward pass."""
+    key = torch.device(device).index
+    st = _aux_streams.get(key)
+    if st is None:
+        lo, hi = torch.cuda.Stream.priority_range() if hasattr(torch.cuda.Stream, "priority_range") else (0, -1)
+        st = (torch.cuda.Stream(device=device, priority=hi), torch.cuda.Stream(device=device, priority=lo))
+        _aux_streams[key] = st
+    return st
+
+
+def rec_stack_supported(cell: str, B: int, H: int, ND: int) -> bool:
+    if cell == "gru":
+        return bool(lib.ds2_gru_persistent_supported(B, H, ND))
+    return bool(lib.ds2_rnn_relu_persistent_supported(B, H, ND))
+
+
+def _rec_ctas(cell: str, B: int, H: int, ND: int) -> int:
+    """CTAs (= SMs) a persistent recurrence launch occupies: 4-CTA clusters x 128-unit tiles x directions x chunks."""
+    chunks = max(1, B // 32) if cell == "gru" else 1
+    return 4 * ((H + 127) // 128) * ND * chunks
+
+
+class _RecStackFn(torch.autograd.Function):
+    """The 'stacked' wiring (src/custom_ops.py:76-95 applied layer after layer) as ONE autograd node, bf16 path:
+         per layer  wx = x W^T (tcgen05 GEMM) -> persistent recurrence -> out = sum_d hs[d]  (bf16, next layer's x)
+       The backward is scheduled over three streams: the recurrence of layer l on a high-priority stream, dx of
+       layer l (the only GEMM the next recurrence waits for) on the caller's stream, and db/dW/dU of layer l on a
+       low-priority stream limited to the SMs the recurrence of layer l-1 leaves free, so they run in its shadow.
+       All streams are joined before the gradients are returned.  Gradients between layers stay fp32.
+       params: per layer (Wcat [ND*G*H, I], U [ND,G*H,H], bias [ND,G*H]) + (bu [ND,3H]) for the GRU."""
+
+    @staticmethod
+    def forward(ctx, x, lens, cell, reverse_mask, out_dtype, L, *params):
+        T, B, _ = x.shape
+        dev = x.device
+        gru = cell == "gru"
+        npl = 4 if gru else 3
+        saved, metas = [], []
+        cur = cast(x.contiguous(), torch.bfloat16)
+        for l in range(L):
+            W, U = params[l * npl], params[l * npl + 1]
+            ND, H = U.shape[0], U.shape[2]
+            I = cur.shape[2]
+            Wg, Ug = cast(W, torch.bfloat16), cast(U, torch.bfloat16)
+            wx = gemm_nt(cur.view(T * B, I), Wg)
+            hs = torch.empty((ND, T, B, H), dtype=torch.bfloat16, device=dev)
+            if gru:
+                bw, bu = params[l * npl + 2], params[l * npl + 3]
+                gates = torch.empty((ND, T, B, 4 * H), dtype=torch.bfloat16, device=dev)
+                wsb = lib.ds2_gru_workspace_bytes(T, B, H, ND)
+                ws = _workspace(wsb, dev, "gru")
+                check(lib.ds2_gru_persistent_fwd(_p(wx), SBN_SCALE, _p(Ug), _p(bw), _p(bu), _p(lens), _p(hs), _p(gates), T, B,
+                                                 H, ND, reverse_mask, _p(ws), wsb, _stream()), "ds2_gru_persistent_fwd")
+                saved += [cur, Wg, Ug, hs, gates]
+            else:
+                bias = params[l * npl + 2]
+                wsb = lib.ds2_rnn_workspace_bytes(T, B, H, ND, DS2_BF16)
+                ws = _workspace(wsb, dev, "rnn")
+                check(lib.ds2_rnn_relu_fwd(_p(wx), SBN_SCALE, _p(Ug), _p(bias), _p(lens), _p(hs), DS2_BF16, T, B, H, ND,
+                                           reverse_mask, RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_fwd")
+                saved += [cur, Wg, Ug, hs]
+            metas.append((I, H, ND))
+            last = l == L - 1
+            odt = out_dtype if last else torch.bfloat16
+            cur = add2(hs[0], hs[1], odt) if ND == 2 else cast(hs[0], odt)
+        ctx.save_for_backward(lens, *saved)
+        ctx.meta = (T, B, gru, reverse_mask, L, metas, x.dtype)
+        return cur
+
+    @staticmethod
+    def backward(ctx, dout):
+        lens, *saved = ctx.saved_tensors
+        T, B, gru, reverse_mask, L, metas, xdtype = ctx.meta
+        dev = dout.device
+        per = 5 if gru else 4
+        npl = 4 if gru else 3
+        main = torch.cuda.current_stream()
+        rec, side = _streams(dev)
+        sm_total = torch.cuda.get_device_properties(dev).multi_processor_count
+        # Measured (tools/stack_overlap.py, profiles/r1_stack_overlap.txt): GEMMs running next to a recurrence raise its
+        # L2 latency; with H=1760 (112 of 148 SMs busy) the recurrence slows by as much as the GEMMs hide, with the
+        # GRU at H=800 (56 SMs busy) the overlap gains ~9% of the backward.  Overlap only when most SMs are free.
+        rec_sms = max(_rec_ctas("gru" if gru else "relu", B, m[1], m[2]) for m in metas)
+        overlap = OVERLAP_WGRAD and L > 1 and (sm_total - rec_sms) * 2 >= sm_total
+        if not overlap:
+            rec = side = main
+        grads = [None] * (L * npl)
+        keep = []                                   # everything the side streams touch stays alive until the join
+        d_cur = cast(dout.contiguous(), torch.float32)
+        side_done = {}                              # layer -> event: its db/dW/dU have finished
+        for l in range(L - 1, -1, -1):
+            xg, Wg, Ug, hs = saved[l * per:l * per + 4]
+            gates = saved[l * per + 4] if gru else None
+            I, H, ND = metas[l]
+            G = ND * (3 if gru else 1) * H
+            # ---- recurrence of layer l (high priority).  It starts together with the side work of layer l+1 and, having
+            #      priority, places its clusters first; the side work of layer l+2 must be gone by then, or its CTAs,
+            #      scattered over the SMs, could keep some clusters from being placed
+            dz = torch.empty((T * B, G), dtype=torch.bfloat16, device=dev)
+            dgh = torch.empty((T * B, G), dtype=torch.bfloat16, device=dev) if gru else dz
+            keep += [dz, dgh, d_cur]
+            if overlap:
+                rec.wait_stream(main)
+                if l + 2 in side_done:
+                    rec.wait_event(side_done[l + 2])
+            with torch.cuda.stream(rec):
+                if STACK_TRACE is not None:
+                    ev0 = torch.cuda.Event(enable_timing=True)
+                    ev0.record()
+                if gru:
+                    wsb = lib.ds2_gru_workspace_bytes(T, B, H, ND)
+                    ws = _workspace(wsb, dev, "gru")
+                    check(lib.ds2_gru_persistent_bwd(_p(d_cur), _p(Ug), _p(lens), _p(hs), _p(gates), _p(dz), _p(dgh), T, B, H,
+                                                     ND, reverse_mask, _p(ws), wsb, _stream()), "ds2_gru_persistent_bwd")
+                else:
+                    wsb = lib.ds2_rnn_workspace_bytes(T, B, H, ND, DS2_BF16)
+                    ws = _workspace(wsb, dev, "rnn")
+                    check(lib.ds2_rnn_relu_bwd(_p(d_cur), _p(Ug), _p(lens), _p(hs), _p(dz), DS2_BF16, T, B, H, ND,
+                                               reverse_mask, RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_bwd")
+                if STACK_TRACE is not None:
+                    ev1 = torch.cuda.Event(enable_timing=True)
+                    ev1.record()
+                    STACK_TRACE.append(("rec", l, ev0, ev1))
+            if overlap:
+                main.wait_stream(rec)
+            # ---- dx of layer l: the critical path
+            if l > 0 or ctx.needs_input_grad[0]:
+                d_cur = gemm_nt(dz, Wg, b_mn=True, alpha=SBN_SCALE)                      # [TB, I] fp32
+            dx_done = torch.cuda.Event()
+            dx_done.record(main)
+            # ---- db, dW, dU of layer l: off the critical path
+            if overlap:
+                side.wait_event(dx_done)
+                # the SMs the recurrence of layer l-1 leaves free; the last side work has the device to itself
+                free = sm_total - _rec_ctas("gru" if gru else "relu", B, metas[l - 1][1], metas[l - 1][2]) if l > 0 else 0
+                prev_limit = lib.ds2_set_sm_limit(max(8, free) if l > 0 else 0)
+            with torch.cuda.stream(side):
+                if STACK_TRACE is not None:
+                    ev2 = torch.cuda.Event(enable_timing=True)
+                    ev2.record()
+                dW = torch.empty((G, I), dtype=torch.float32, device=dev)
+                gemm_wgrad(dz, xg.view(T * B, I), G, I, T * B, G, I, dW, alpha=SBN_SCALE)
+                GH = G // ND
+                dU = torch.empty((ND, GH, H), dtype=torch.float32, device=dev)
+                for d in range(ND):
+                    rev = (reverse_mask >> d) & 1
+                    if T > 1:
+                        a_off = (0 if rev else B * G) + d * GH
+                        gemm_wgrad(dgh.view(-1)[a_off:], hs[d].reshape(T * B, H)[(B if rev else 0):], GH, H, (T - 1) * B, G, H,
+                                   dU[d])
+                    else:
+                        dU[d].zero_()
+                db = colsum(dz, T * B, G, G).view(ND, GH)
+                outs = [dW, dU, db]
+                if gru:
+                    outs.append(colsum(dgh, T * B, G, G).view(ND, GH))
+                if STACK_TRACE is not None:
+                    ev3 = torch.cuda.Event(enable_timing=True)
+                    ev3.record()
+                    STACK_TRACE.append(("side", l, ev2, ev3))
+            if overlap:
+                lib.ds2_set_sm_limit(prev_limit)
+                side_done[l] = torch.cuda.Event()
+                side_done[l].record(side)
+                for t in outs:
+                    t.record_stream(main)
+            grads[l * npl:l * npl + npl] = outs
+        if overlap:
+            main.wait_stream(side)
+            main.wait_stream(rec)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = d_cur.view(T, B, metas[0][0])
+            if xdtype != torch.float32:
+                dx = cast(dx, xdtype)
+        del keep
+        return (dx, None, None, None, None, None, *grads)
+
+
+def rec_stack(x, lens, cell: str, reverse_mask: int, out_dtype, layer_params):
+    """layer_params: list over layers of (Wcat, U, bias) or (Wcat, U, bw, bu) for cell == 'gru'."""
+    flat = []
+    for lp in layer_params:
+        flat += [t.contiguous() for t in lp]
+    _need_cuda(x, lens, *flat)
+    return _RecStackFn.apply(x, lens, cell, reverse_mask, out_dtype, len(layer_params), *flat)
+
+
 # ------------------------------------------------------------------------------------ linear
 class _LinearFn(torch.autograd.Function):
     """y[R,N] = x[R,K] . W[N,K]^T + b  (fp32 out).  src/deepSpeech_NCHW.py:195-198, custom_ops._linear."""

@@ -37,6 +37,11 @@ const char* ds2_last_error(void);
 int ds2_version(void);
 /* number of kernels this library has launched in this process (bench.py's gpu_launches) */
 long long ds2_launch_count(void);
+/* Caps the number of CTAs that grid-sized (persistent / grid-stride) kernels launched afterwards from THIS host
+ * thread use: n SMs' worth, 0 = the whole device.  Returns the previous value.  No counterpart in the reference:
+ * the host layer uses it to run weight-gradient GEMMs on a low-priority side stream next to a recurrence kernel
+ * that occupies a fixed set of SMs (deepspeech_b200/ops.py, recurrent stack backward). */
+int ds2_set_sm_limit(int n);
 
 /* ---- CTC ------------------------------------------------------------------------------------
  * tf.nn.ctc_loss(labels, inputs=float32 logits [T,B,K], sequence_length, time_major=True) as
