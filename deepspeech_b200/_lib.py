@@ -51,6 +51,12 @@ _SIGS = {
     "ds2_conv2d_fwd": (I, [P, I, P, P, P, I, I, I, I, I, I, I, I, I, P]),
     "ds2_conv2d_dgrad": (I, [P, P, P, I, I, I, I, I, I, I, I, I, P]),
     "ds2_conv2d_wgrad": (I, [P, I, P, P, P, I, I, I, I, I, I, I, I, I, P]),
+    "ds2_conv_window_supported": (I, [I, I, I, I, I, I]),
+    "ds2_conv_window_weights": (I, [P, P, P, I, I, P]),
+    "ds2_conv_window_pad_cast": (I, [P, P, L, I, I, P]),
+    "ds2_conv_window_fwd": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "ds2_conv_window_dgrad": (I, [P, P, P, I, I, I, I, I, I, P]),
+    "ds2_conv_window_wgrad": (I, [P, P, P, I, I, I, I, I, I, P]),
     "ds2_bn_stats": (I, [P, L, I, F, P, P, P, P]),
     "ds2_bn_clip_fwd": (I, [P, I, I, I, I, P, P, P, P, F, I, P, I, L, L, L, L, P]),
     "ds2_bn_clip_bwd": (I, [P, I, I, I, I, P, P, P, P, F, I, P, I, L, L, L, L, P, P, P, P, P]),

@@ -1,0 +1,507 @@
+// Implicit-GEMM 2-D convolution for 32-channel layers with unit stride along frequency (conv2 of the reference:
+// tf.nn.conv2d at src/deepSpeech_NCHW.py:142-151 / src/deepSpeech.py:143-149, filter [10,5,32,32], strides (2,1)),
+// forward, data gradient and weight gradient, WITHOUT a patch matrix (the explicit im2col route writes and re-reads
+// 2.8 GB per pass at the reference's batch).
+//
+// The trick is the tensor map.  With channel-last bf16 activations a[R rows = (b,t)][P positions f][32 ch], the
+// K-major A row of output position f for filter row kt is the contiguous run a[row][f .. f+KF-1][0..31]: windows of
+// neighbouring positions OVERLAP, shifted by one position = 64 bytes.  A 3-D TMA view {64 elements, P, R} with strides
+// {64 B, row pitch} describes exactly that: box {64, 128, 1} at (0, f0 + 2c, row) lands 128 windows of 64 elements
+// (two filter taps x 32 channels) as a 128-byte-swizzled K-major tile, one per output position.  A filter row of KF
+// taps is KF/2 such chunks plus a half chunk (32 elements: only two of the four K=16 MMA steps are issued).
+// Positions beyond the row are out of bounds for the map and arrive as zeros.
+//   forward : tile = output row (b,to), M = 128 positions (Fo valid), N = 32 filters, K-blocks = KT x chunks,
+//             source rows b*Ti + to*st + kt, weights Wt[co][(kt,kf,ci)].
+//   dgrad   : tile = input row (b,t1), source = dy zero-padded by KF-1 positions on both sides, K-blocks over the
+//             kt with (t1-kt) % st == 0 and to = (t1-kt)/st in range, weights Wd[ci][(kt,KF-1-kf,co)].
+//   wgrad   : dW[(kt,kf,ci)][co] = sum over tiles of window^T . dy : the same boxes read as MN-major A operands
+//             (M = 64 window elements per box, two boxes per MMA block), dy rows as the MN-major B operand, all
+//             KT*KF*32 x 32 partial sums of a CTA resident in TMEM (15 blocks x 32 columns) until it has run out of
+//             tiles, then red.add into dW.
+#include "common.cuh"
+
+namespace ds2 {
+
+static constexpr int CW_THREADS = 256;
+static constexpr int CW_C = 32;                  // channels in and out
+static constexpr int CW_BOX = 128 * 128;         // one window box: 128 positions x 64 elements bf16
+static constexpr int CW_WBOX = 32 * 128;         // weight tile: 32 rows x 64 elements
+static constexpr int CW_STAGES = 8;
+static constexpr int CW_STAGE_BYTES = CW_BOX + CW_WBOX;
+static constexpr int CW_SMEM = CW_STAGES * CW_STAGE_BYTES + 1024 + 256;
+static constexpr int CWG_STAGES = 4;             // wgrad: two window boxes + one dy box per stage
+static constexpr int CWG_STAGE_BYTES = 3 * CW_BOX;
+static constexpr int CWG_SMEM = CWG_STAGES * CWG_STAGE_BYTES + 1024 + 256;
+
+struct WinParams {
+  float* out;            // fwd: y [B,Rout,Pout,32] ; dgrad: da [B,Rout,Pout,32] ; wgrad: dW [KT*KF*32][32]
+  const float* bias;     // fwd only
+  int n_tiles;           // B * Rout
+  int Rout, Rsrc;        // rows per batch item of the output / of the source
+  int Pout;              // valid positions per output row
+  int KT, st;
+  int nfull, half;       // 64-element chunks per filter row, and whether a 32-element one follows
+  int kstride;           // K elements per filter row (KF * 32)
+  int win0;              // first window position of output position 0 (wgrad: position of dy's first valid column)
+  int dgrad;
+};
+
+// K-blocks of a tile, the same enumeration for the producer and the MMA warp.
+struct KtIter {
+  int kt, row;           // filter row and source row; row < 0: none left
+};
+__device__ __forceinline__ bool kt_source(const WinParams& p, int b, int r, int kt, int* src_row) {
+  if (!p.dgrad) {
+    *src_row = b * p.Rsrc + r * p.st + kt;
+    return true;
+  }
+  const int d = r - kt;
+  if (d < 0 || d % p.st != 0) return false;
+  const int to = d / p.st;
+  if (to >= p.Rsrc) return false;
+  *src_row = b * p.Rsrc + to;
+  return true;
+}
+
+__global__ void __launch_bounds__(CW_THREADS, 1)
+conv_window_kernel(const __grid_constant__ CUtensorMap tmap_src, const __grid_constant__ CUtensorMap tmap_w, WinParams p) {
+  extern __shared__ __align__(1024) uint8_t cw_smem_raw[];
+  const uint32_t sbase = (smem_u32(cw_smem_raw) + 1023u) & ~1023u;
+  const uint32_t bars = sbase + CW_STAGES * CW_STAGE_BYTES;
+  const uint32_t full_bar = bars, empty_bar = bars + 8 * CW_STAGES, tfull_bar = bars + 16 * CW_STAGES,
+                 tempty_bar = tfull_bar + 16;
+  const uint32_t slot_addr = tempty_bar + 16;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(cw_smem_raw + (slot_addr - smem_u32(cw_smem_raw)));
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
+  const int nch = p.nfull + p.half;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_src);
+    tma_prefetch_desc(&tmap_w);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < CW_STAGES; ++i) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full_bar + 8 * i), "r"(1));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(empty_bar + 8 * i), "r"(1));
+    }
+    for (int i = 0; i < 2; ++i) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(tfull_bar + 8 * i), "r"(1));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(tempty_bar + 8 * i), "r"(4));
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 64);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one_sync()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+        const int b = tile / p.Rout, r = tile - b * p.Rout;
+        for (int kt = 0; kt < p.KT; ++kt) {
+          int src_row;
+          if (!kt_source(p, b, r, kt, &src_row)) continue;
+          for (int c = 0; c < nch; ++c) {
+            mbar_wait(empty_bar + 8 * stage, phase ^ 1, 100 + stage);
+            const uint32_t sa = sbase + stage * CW_STAGE_BYTES;
+            mbar_arrive_expect_tx(full_bar + 8 * stage, CW_BOX + CW_WBOX);
+            asm volatile(
+                "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                ::"r"(sa), "l"(reinterpret_cast<uint64_t>(&tmap_src)), "r"(full_bar + 8 * stage), "r"(0), "r"(p.win0 + 2 * c),
+                "r"(src_row)
+                : "memory");
+            asm volatile(
+                "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                ::"r"(sa + CW_BOX), "l"(reinterpret_cast<uint64_t>(&tmap_w)), "r"(full_bar + 8 * stage),
+                "r"(kt * p.kstride + c * 64), "r"(0)
+                : "memory");
+            if (++stage == CW_STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc = umma_idesc_bf16(128, CW_C, 0, 0);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      const int b = tile / p.Rout, r = tile - b * p.Rout;
+      mbar_wait(tempty_bar + 8 * acc, acc_phase ^ 1, 200 + acc);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * CW_C;
+      bool first = true;
+      for (int kt = 0; kt < p.KT; ++kt) {
+        int src_row;
+        if (!kt_source(p, b, r, kt, &src_row)) continue;
+        for (int c = 0; c < nch; ++c) {
+          mbar_wait(full_bar + 8 * stage, phase, 300 + stage);
+          tc_fence_after();
+          if (elect_one_sync()) {
+            const uint32_t sa = sbase + stage * CW_STAGE_BYTES;
+            const uint32_t sb = sa + CW_BOX;
+            const int ksteps = c < p.nfull ? 4 : 2;
+            for (int k = 0; k < ksteps; ++k) {
+              umma_bf16(d_tmem, umma_smem_desc_sw128(sa + k * 32, 16, 1024), umma_smem_desc_sw128(sb + k * 32, 16, 1024), idesc,
+                        (first && k == 0) ? 0u : 1u);
+            }
+            umma_commit(empty_bar + 8 * stage);
+          }
+          __syncwarp();
+          first = false;
+          if (++stage == CW_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+      if (elect_one_sync()) umma_commit(tfull_bar + 8 * acc);   // also fires when the tile had no K-block at all
+      __syncwarp();
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue: TMEM -> registers -> 128 contiguous bytes per output position =====================
+    const int wq = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    float bias[CW_C];
+#pragma unroll
+    for (int j = 0; j < CW_C; ++j) bias[j] = p.bias ? __ldg(p.bias + j) : 0.f;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      const int b = tile / p.Rout, r = tile - b * p.Rout;
+      bool any = false;
+      for (int kt = 0; kt < p.KT; ++kt) {
+        int src_row;
+        any |= kt_source(p, b, r, kt, &src_row);
+      }
+      mbar_wait(tfull_bar + 8 * acc, acc_phase, 400 + acc);
+      tc_fence_after();
+      uint32_t v[32];
+      tmem_ld_32x32(tmem_base + acc * CW_C + (static_cast<uint32_t>(wq * 32) << 16), v);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar + 8 * acc);
+      const int pos = wq * 32 + lane;
+      if (pos < p.Pout) {
+        float4* dst = reinterpret_cast<float4*>(p.out + ((size_t)tile * p.Pout + pos) * CW_C);
+#pragma unroll
+        for (int j = 0; j < CW_C; j += 4) {
+          float4 o;
+          o.x = (any ? __uint_as_float(v[j]) : 0.f) + bias[j];
+          o.y = (any ? __uint_as_float(v[j + 1]) : 0.f) + bias[j + 1];
+          o.z = (any ? __uint_as_float(v[j + 2]) : 0.f) + bias[j + 2];
+          o.w = (any ? __uint_as_float(v[j + 3]) : 0.f) + bias[j + 3];
+          dst[j / 4] = o;
+        }
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 64);
+  }
+}
+
+// ------------------------------------------------------------------ weight gradient
+__global__ void __launch_bounds__(CW_THREADS, 1)
+conv_window_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_dy, WinParams p) {
+  extern __shared__ __align__(1024) uint8_t cwg_smem_raw[];
+  const uint32_t sbase = (smem_u32(cwg_smem_raw) + 1023u) & ~1023u;
+  const uint32_t bars = sbase + CWG_STAGES * CWG_STAGE_BYTES;
+  const uint32_t full_bar = bars, empty_bar = bars + 8 * CWG_STAGES, done_bar = bars + 16 * CWG_STAGES;
+  const uint32_t slot_addr = done_bar + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(cwg_smem_raw + (slot_addr - smem_u32(cwg_smem_raw)));
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
+  const int nch = p.nfull + p.half;
+  const int ngroups = p.KT * nch;                  // 64-wide groups of window elements; two per MMA block
+  const int nblocks = (ngroups + 1) / 2;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_dy);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < CWG_STAGES; ++i) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full_bar + 8 * i), "r"(1));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(empty_bar + 8 * i), "r"(1));
+    }
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(done_bar), "r"(1));
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const bool has_tiles = (int)blockIdx.x < p.n_tiles;
+
+  if (warp == 0) {
+    if (elect_one_sync()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+        const int b = tile / p.Rout, r = tile - b * p.Rout;        // Rout = To here
+        for (int blk = 0; blk < nblocks; ++blk) {
+          mbar_wait(empty_bar + 8 * stage, phase ^ 1, 100 + stage);
+          const uint32_t sa = sbase + stage * CWG_STAGE_BYTES;
+          const int ng = min(2, ngroups - 2 * blk);
+          mbar_arrive_expect_tx(full_bar + 8 * stage, (ng + 1) * CW_BOX);
+          for (int g = 0; g < ng; ++g) {
+            const int gi = 2 * blk + g, kt = gi / nch, c = gi - kt * nch;
+            asm volatile(
+                "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                ::"r"(sa + g * CW_BOX), "l"(reinterpret_cast<uint64_t>(&tmap_a)), "r"(full_bar + 8 * stage), "r"(0), "r"(2 * c),
+                "r"(b * p.Rsrc + r * p.st + kt)
+                : "memory");
+          }
+          asm volatile(
+              "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+              ::"r"(sa + 2 * CW_BOX), "l"(reinterpret_cast<uint64_t>(&tmap_dy)), "r"(full_bar + 8 * stage), "r"(0), "r"(p.win0),
+              "r"(tile)
+              : "memory");
+          if (++stage == CWG_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc = umma_idesc_bf16(128, CW_C, 1, 1);
+    int stage = 0;
+    uint32_t phase = 0;
+    bool first_tile = true;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      for (int blk = 0; blk < nblocks; ++blk) {
+        mbar_wait(full_bar + 8 * stage, phase, 300 + stage);
+        tc_fence_after();
+        if (elect_one_sync()) {
+          const uint32_t sa = sbase + stage * CWG_STAGE_BYTES;
+          const uint32_t sb = sa + 2 * CW_BOX;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            // contraction over the 128 positions of the row: 16 positions (16 x 128 B) per K step
+            umma_bf16(tmem_base + blk * CW_C, umma_smem_desc_sw128(sa + k * 2048, CW_BOX, 1024),
+                      umma_smem_desc_sw128(sb + k * 2048, CW_BOX, 1024), idesc, (first_tile && k == 0) ? 0u : 1u);
+          }
+          umma_commit(empty_bar + 8 * stage);
+        }
+        __syncwarp();
+        if (++stage == CWG_STAGES) { stage = 0; phase ^= 1; }
+      }
+      first_tile = false;
+    }
+    if (elect_one_sync()) umma_commit(done_bar);
+    __syncwarp();
+  } else if (warp >= 4 && has_tiles) {
+    // ===================== after the last tile: TMEM partial sums -> red.add into dW =====================
+    const int wq = warp & 3;
+    mbar_wait(done_bar, 0, 400);
+    tc_fence_after();
+    const int ml = wq * 32 + lane;                 // row of the MMA block = window element
+    const int g = ml >> 6, e = ml & 63;
+    for (int blk = 0; blk < nblocks; ++blk) {
+      uint32_t v[32];
+      tmem_ld_32x32(tmem_base + blk * CW_C + (static_cast<uint32_t>(wq * 32) << 16), v);
+      tmem_ld_wait();
+      const int gi = 2 * blk + g;
+      if (gi < ngroups) {
+        const int kt = gi / nch, c = gi - kt * nch;
+        if (c < p.nfull || e < 32) {
+          float* dst = p.out + ((size_t)kt * p.kstride + c * 64 + e) * CW_C;
+#pragma unroll
+          for (int j = 0; j < CW_C; ++j) atomicAdd(dst + j, __uint_as_float(v[j]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------ small helpers
+// dy fp32 [R, P, 32] -> bf16 [R, P + 2*pad, 32] with zero borders (the data gradient's and weight gradient's source)
+__global__ void conv_pad_cast_kernel(const float* __restrict__ dy, __nv_bfloat16* __restrict__ out, long R, int P, int pad) {
+  const int Pp = P + 2 * pad;
+  const long n4 = R * Pp * (CW_C / 4);
+  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
+    const int c4 = (int)(i % (CW_C / 4));
+    const long rp = i / (CW_C / 4);
+    const int pp = (int)(rp % Pp);
+    const long r = rp / Pp;
+    const int pos = pp - pad;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (pos >= 0 && pos < P) v = __ldg(reinterpret_cast<const float4*>(dy + ((r * P + pos) * CW_C)) + c4);
+    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+    uint2 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&a);
+    pk.y = *reinterpret_cast<uint32_t*>(&b);
+    *reinterpret_cast<uint2*>(out + (rp * CW_C) + c4 * 4) = pk;
+  }
+}
+
+// HWIO fp32 w[kt][kf][ci][co] -> wt[co][(kt,kf,ci)] (forward) and wd[ci][(kt,KF-1-kf,co)] (data gradient), bf16
+__global__ void conv_window_weights_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wt, __nv_bfloat16* __restrict__ wd,
+                                           int KT, int KF) {
+  const int K = KT * KF * CW_C;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < K * CW_C; i += gridDim.x * blockDim.x) {
+    const int co = i % CW_C;
+    const int ci = (i / CW_C) % CW_C;
+    const int kf = (i / (CW_C * CW_C)) % KF;
+    const int kt = i / (CW_C * CW_C * KF);
+    const __nv_bfloat16 v = __float2bfloat16(w[i]);
+    wt[(size_t)co * K + (kt * KF + kf) * CW_C + ci] = v;
+    wd[(size_t)ci * K + (kt * KF + (KF - 1 - kf)) * CW_C + co] = v;
+  }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*PFN_encodeTiledW)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                     const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// window view of a channel-last bf16 tensor [R][P][32] with row pitch `pitch` elements: {64, P, R} / {64 B, pitch}
+static int make_tmap_window(CUtensorMap* out, const void* base, uint64_t P, uint64_t R, uint64_t pitch_elems) {
+  static PFN_encodeTiledW enc = nullptr;
+  if (!enc) {
+    void* fp = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fp, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      enc = reinterpret_cast<PFN_encodeTiledW>(fp);
+  }
+  DS2_REQUIRE(enc != nullptr, DS2_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available from the driver");
+  DS2_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (pitch_elems * 2) % 16 == 0, DS2_ERR_BAD_ARG,
+              "conv window operand must be 16-byte aligned with a 16-byte multiple row pitch");
+  cuuint64_t dims[3] = {64, P, R};
+  cuuint64_t strides[2] = {CW_C * 2, pitch_elems * 2};
+  cuuint32_t box[3] = {64, 128, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DS2_REQUIRE(r == CUDA_SUCCESS, DS2_ERR_CUDA, "cuTensorMapEncodeTiled (window view) failed with CUresult %d (P=%llu R=%llu pitch=%llu)",
+              (int)r, (unsigned long long)P, (unsigned long long)R, (unsigned long long)pitch_elems);
+  return DS2_OK;
+}
+
+static int window_shape_ok(const char* who, int B, int Ti, int Fi, int Ci, int Co, int KT, int KF, int st, int sf) {
+  DS2_REQUIRE(B > 0 && Ti >= KT && Fi >= KF && KT > 0 && KF > 0 && st > 0, DS2_ERR_BAD_SHAPE, "%s: bad shape", who);
+  DS2_REQUIRE(Ci == CW_C && Co == CW_C && sf == 1, DS2_ERR_UNSUPPORTED, "%s: needs 32 channels in and out and unit stride along "
+              "frequency (Ci=%d Co=%d sf=%d)", who, Ci, Co, sf);
+  DS2_REQUIRE(Fi <= 128, DS2_ERR_UNSUPPORTED, "%s: at most 128 positions per row (Fi=%d)", who, Fi);
+  DS2_REQUIRE(KT * ((KF + 1) / 2) <= 32, DS2_ERR_UNSUPPORTED, "%s: filter %dx%d too large for the resident weight gradient", who, KT, KF);
+  return DS2_OK;
+}
+
+static void fill_common(WinParams& p, int KT, int KF, int st) {
+  p.KT = KT; p.st = st; p.nfull = KF / 2; p.half = KF & 1; p.kstride = KF * CW_C;
+}
+
+}  // namespace ds2
+
+using namespace ds2;
+
+extern "C" int ds2_conv_window_supported(int Ci, int Co, int Fi, int KT, int KF, int sf) {
+  return Ci == CW_C && Co == CW_C && sf == 1 && Fi <= 128 && Fi >= KF && KT * ((KF + 1) / 2) <= 32;
+}
+
+extern "C" int ds2_conv_window_weights(const float* w, void* wt, void* wd, int KT, int KF, void* stream) {
+  DS2_REQUIRE(w && wt && wd && KT > 0 && KF > 0, DS2_ERR_BAD_ARG, "ds2_conv_window_weights: bad argument");
+  conv_window_weights_kernel<<<(KT * KF * CW_C * CW_C + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      w, static_cast<__nv_bfloat16*>(wt), static_cast<__nv_bfloat16*>(wd), KT, KF);
+  DS2_LAUNCH_CHECK("conv_window_weights_kernel");
+  count_launch();
+  return DS2_OK;
+}
+
+extern "C" int ds2_conv_window_pad_cast(const float* dy, void* out, long R, int P, int pad, void* stream) {
+  DS2_REQUIRE(dy && out && R > 0 && P > 0 && pad >= 0, DS2_ERR_BAD_ARG, "ds2_conv_window_pad_cast: bad argument");
+  long n4 = R * (P + 2 * pad) * (CW_C / 4);
+  long grid = (n4 + 255) / 256;
+  if (grid > (long)num_sms() * 16) grid = (long)num_sms() * 16;
+  conv_pad_cast_kernel<<<(int)grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, static_cast<__nv_bfloat16*>(out), R, P, pad);
+  DS2_LAUNCH_CHECK("conv_pad_cast_kernel");
+  count_launch();
+  return DS2_OK;
+}
+
+static int window_attr() {
+  static bool done = false;
+  if (!done) {
+    DS2_CUDA(cudaFuncSetAttribute(conv_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CW_SMEM));
+    DS2_CUDA(cudaFuncSetAttribute(conv_window_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CWG_SMEM));
+    done = true;
+  }
+  return DS2_OK;
+}
+
+extern "C" int ds2_conv_window_fwd(const void* a, const void* wt, const float* bias, float* y, int B, int Ti, int Fi, int KT, int KF,
+                                   int st, void* stream) {
+  DS2_REQUIRE(a && wt && y, DS2_ERR_BAD_ARG, "ds2_conv_window_fwd: null pointer");
+  int rc = window_shape_ok("ds2_conv_window_fwd", B, Ti, Fi, CW_C, CW_C, KT, KF, st, 1);
+  if (rc) return rc;
+  if ((rc = window_attr())) return rc;
+  const int To = (Ti - KT) / st + 1, Fo = Fi - KF + 1;
+  CUtensorMap ts, tw;
+  if ((rc = make_tmap_window(&ts, a, Fi, (uint64_t)B * Ti, (uint64_t)Fi * CW_C))) return rc;
+  if ((rc = make_tmap_2d_bf16(&tw, wt, (uint64_t)KT * KF * CW_C, CW_C, (uint64_t)KT * KF * CW_C, 64, CW_C))) return rc;
+  WinParams p = {};
+  fill_common(p, KT, KF, st);
+  p.out = y; p.bias = bias; p.n_tiles = B * To; p.Rout = To; p.Rsrc = Ti; p.Pout = Fo; p.win0 = 0; p.dgrad = 0;
+  const int grid = p.n_tiles < num_sms() ? p.n_tiles : num_sms();
+  conv_window_kernel<<<grid, CW_THREADS, CW_SMEM, static_cast<cudaStream_t>(stream)>>>(ts, tw, p);
+  DS2_LAUNCH_CHECK("conv_window_kernel<fwd>");
+  count_launch();
+  return DS2_OK;
+}
+
+extern "C" int ds2_conv_window_dgrad(const void* dyp, const void* wd, float* da, int B, int Ti, int Fi, int KT, int KF, int st,
+                                     void* stream) {
+  DS2_REQUIRE(dyp && wd && da, DS2_ERR_BAD_ARG, "ds2_conv_window_dgrad: null pointer");
+  int rc = window_shape_ok("ds2_conv_window_dgrad", B, Ti, Fi, CW_C, CW_C, KT, KF, st, 1);
+  if (rc) return rc;
+  if ((rc = window_attr())) return rc;
+  const int To = (Ti - KT) / st + 1, Fo = Fi - KF + 1, Pp = Fo + 2 * (KF - 1);
+  CUtensorMap ts, tw;
+  if ((rc = make_tmap_window(&ts, dyp, Pp, (uint64_t)B * To, (uint64_t)Pp * CW_C))) return rc;
+  if ((rc = make_tmap_2d_bf16(&tw, wd, (uint64_t)KT * KF * CW_C, CW_C, (uint64_t)KT * KF * CW_C, 64, CW_C))) return rc;
+  WinParams p = {};
+  fill_common(p, KT, KF, st);
+  p.out = da; p.bias = nullptr; p.n_tiles = B * Ti; p.Rout = Ti; p.Rsrc = To; p.Pout = Fi; p.win0 = 0; p.dgrad = 1;
+  const int grid = p.n_tiles < num_sms() ? p.n_tiles : num_sms();
+  conv_window_kernel<<<grid, CW_THREADS, CW_SMEM, static_cast<cudaStream_t>(stream)>>>(ts, tw, p);
+  DS2_LAUNCH_CHECK("conv_window_kernel<dgrad>");
+  count_launch();
+  return DS2_OK;
+}
+
+extern "C" int ds2_conv_window_wgrad(const void* a, const void* dyp, float* dw, int B, int Ti, int Fi, int KT, int KF, int st,
+                                     void* stream) {
+  DS2_REQUIRE(a && dyp && dw, DS2_ERR_BAD_ARG, "ds2_conv_window_wgrad: null pointer");
+  int rc = window_shape_ok("ds2_conv_window_wgrad", B, Ti, Fi, CW_C, CW_C, KT, KF, st, 1);
+  if (rc) return rc;
+  if ((rc = window_attr())) return rc;
+  const int To = (Ti - KT) / st + 1, Fo = Fi - KF + 1, Pp = Fo + 2 * (KF - 1);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  DS2_CUDA(cudaMemsetAsync(dw, 0, (size_t)KT * KF * CW_C * CW_C * sizeof(float), s));
+  CUtensorMap ta, td;
+  if ((rc = make_tmap_window(&ta, a, Fi, (uint64_t)B * Ti, (uint64_t)Fi * CW_C))) return rc;
+  if ((rc = make_tmap_window(&td, dyp, Pp, (uint64_t)B * To, (uint64_t)Pp * CW_C))) return rc;
+  WinParams p = {};
+  fill_common(p, KT, KF, st);
+  p.out = dw; p.bias = nullptr; p.n_tiles = B * To; p.Rout = To; p.Rsrc = Ti; p.Pout = Fo; p.win0 = KF - 1; p.dgrad = 0;
+  const int grid = p.n_tiles < num_sms() ? p.n_tiles : num_sms();
+  conv_window_wgrad_kernel<<<grid, CW_THREADS, CWG_SMEM, s>>>(ta, td, p);
+  DS2_LAUNCH_CHECK("conv_window_wgrad_kernel");
+  count_launch();
+  return DS2_OK;
+}

@@ -303,6 +303,121 @@ bn_clip_bwd_apply_kernel(const float* __restrict__ x, long R, const float* __res
   }
 }
 
+// ---- the same three passes for the plain channel-last case (activation side contiguous like x, C % 4 == 0):
+// four channels per thread, 16-byte accesses, no index arithmetic.  Thread <-> fixed channel quad, rows strided.
+template <typename T> __device__ __forceinline__ float4 ld4(const T* p);
+template <> __device__ __forceinline__ float4 ld4<float>(const float* p) { return *reinterpret_cast<const float4*>(p); }
+template <> __device__ __forceinline__ float4 ld4<__nv_bfloat16>(const __nv_bfloat16* p) {
+  const uint2 u = *reinterpret_cast<const uint2*>(p);
+  const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&u.x), b = *reinterpret_cast<const __nv_bfloat162*>(&u.y);
+  return make_float4(__low2float(a), __high2float(a), __low2float(b), __high2float(b));
+}
+__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ void st4(__nv_bfloat16* p, float4 v) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&a);
+  u.y = *reinterpret_cast<uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+struct Quad { float v[4]; };
+__device__ __forceinline__ Quad q4(float4 f) { Quad q; q.v[0] = f.x; q.v[1] = f.y; q.v[2] = f.z; q.v[3] = f.w; return q; }
+
+template <typename TO>
+__global__ void __launch_bounds__(256)
+bn_clip_fwd_vec_kernel(const float* __restrict__ x, long R, int C, const float* __restrict__ mean, const float* __restrict__ rstd,
+                       const float* __restrict__ gamma, const float* __restrict__ beta, float cap, int clip, TO* __restrict__ out) {
+  const int Q = C / 4;
+  const int c = (threadIdx.x % Q) * 4;
+  const int rl = threadIdx.x / Q, rstep = blockDim.x / Q;
+  float a[4], sh[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { a[i] = rstd[c + i] * gamma[c + i]; sh[i] = beta[c + i] - mean[c + i] * a[i]; }
+  for (long r = (long)blockIdx.x * rstep + rl; r < R; r += (long)gridDim.x * rstep) {
+    const Quad xv = q4(ld4(x + r * C + c));
+    float o[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      o[i] = fmaf(xv.v[i], a[i], sh[i]);
+      if (clip) o[i] = fminf(fmaxf(o[i], 0.f), cap);
+    }
+    st4(out + r * C + c, make_float4(o[0], o[1], o[2], o[3]));
+  }
+}
+
+template <typename TG>
+__global__ void __launch_bounds__(256)
+bn_clip_bwd_reduce_vec_kernel(const float* __restrict__ x, long R, int C, const float* __restrict__ mean, const float* __restrict__ rstd,
+                              const float* __restrict__ gamma, const float* __restrict__ beta, float cap, int clip,
+                              const TG* __restrict__ dout, double* __restrict__ sums) {
+  const int Q = C / 4;
+  const int c = (threadIdx.x % Q) * 4;
+  const int rl = threadIdx.x / Q, rstep = blockDim.x / Q;
+  float mu[4], rs[4], g[4], be[4], s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { mu[i] = mean[c + i]; rs[i] = rstd[c + i]; g[i] = gamma[c + i]; be[i] = beta[c + i]; }
+  const long rows_per_block = (R + gridDim.x - 1) / gridDim.x;
+  const long r0 = blockIdx.x * rows_per_block, r1 = min(R, r0 + rows_per_block);
+#pragma unroll 4
+  for (long r = r0 + rl; r < r1; r += rstep) {
+    const Quad xv = q4(ld4(x + r * C + c)), dv = q4(ld4(dout + r * C + c));
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float xh = (xv.v[i] - mu[i]) * rs[i];
+      const float bn = fmaf(xh, g[i], be[i]);
+      const float d = (clip && !(bn > 0.f && bn < cap)) ? 0.f : dv.v[i];
+      s1[i] += d;
+      s2[i] = fmaf(d, xh, s2[i]);
+    }
+  }
+  __shared__ float sh1[4][256], sh2[4][256];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { sh1[i][threadIdx.x] = s1[i]; sh2[i][threadIdx.x] = s2[i]; }
+  __syncthreads();
+  if (threadIdx.x < C) {
+    // channel threadIdx.x: quad q = ch / 4, component i = ch % 4, held by threads q, q + Q, q + 2Q, ...
+    const int q = threadIdx.x / 4, i = threadIdx.x % 4;
+    double a = 0, b = 0;
+    for (int t = q; t < blockDim.x; t += Q) { a += sh1[i][t]; b += sh2[i][t]; }
+    atomicAdd(sums + threadIdx.x, a);
+    atomicAdd(sums + C + threadIdx.x, b);
+  }
+}
+
+template <typename TG>
+__global__ void __launch_bounds__(256)
+bn_clip_bwd_apply_vec_kernel(const float* __restrict__ x, long R, int C, const float* __restrict__ mean, const float* __restrict__ rstd,
+                             const float* __restrict__ gamma, const float* __restrict__ beta, float cap, int clip,
+                             const TG* __restrict__ dout, const double* __restrict__ sums, float* __restrict__ dx,
+                             float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  const int Q = C / 4;
+  const int c = (threadIdx.x % Q) * 4;
+  const int rl = threadIdx.x / Q, rstep = blockDim.x / Q;
+  float mu[4], rs[4], g[4], be[4], m1[4], m2[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    mu[i] = mean[c + i]; rs[i] = rstd[c + i]; g[i] = gamma[c + i]; be[i] = beta[c + i];
+    m1[i] = (float)(sums[c + i] / (double)R);
+    m2[i] = (float)(sums[C + c + i] / (double)R);
+  }
+  for (long r = (long)blockIdx.x * rstep + rl; r < R; r += (long)gridDim.x * rstep) {
+    const Quad xv = q4(ld4(x + r * C + c)), dv = q4(ld4(dout + r * C + c));
+    float o[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float xh = (xv.v[i] - mu[i]) * rs[i];
+      const float bn = fmaf(xh, g[i], be[i]);
+      const float d = (clip && !(bn > 0.f && bn < cap)) ? 0.f : dv.v[i];
+      o[i] = g[i] * rs[i] * (d - m1[i] - xh * m2[i]);
+    }
+    st4(dx + r * C + c, make_float4(o[0], o[1], o[2], o[3]));
+  }
+  if (blockIdx.x == 0 && threadIdx.x < C) {
+    if (dbeta) dbeta[threadIdx.x] = (float)sums[threadIdx.x];
+    if (dgamma) dgamma[threadIdx.x] = (float)sums[C + threadIdx.x];
+  }
+}
+
 // ------------------------------------------------------------------ element-wise helpers
 template <typename TI, typename TO>
 __global__ void __launch_bounds__(256) cast_kernel(const TI* __restrict__ in, TO* __restrict__ out, long n) {
@@ -459,6 +574,13 @@ static int act_map(ActMap* m, int T, int F, int C, long sb, long st, long sf, lo
   return DS2_OK;
 }
 
+// activation side laid out exactly like x ([B,T,F,C] contiguous)?
+static bool act_contiguous(const ActMap& m, int B) {
+  (void)B;
+  return m.sc == 1 && m.sf == m.C && m.st == (long)m.F * m.C && m.sb == (long)m.T * m.F * m.C;
+}
+static bool vec_channels(int C) { return C % 4 == 0 && 256 % (C / 4) == 0; }
+
 extern "C" int ds2_bn_stats(const float* x, long R, int C, float eps, double* sums_scratch, float* mean, float* rstd, void* stream) {
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   DS2_REQUIRE(x && sums_scratch && mean && rstd && R > 0, DS2_ERR_BAD_ARG, "ds2_bn_stats: bad argument");
@@ -483,6 +605,16 @@ extern "C" int ds2_bn_clip_fwd(const float* x, int B, int T, int F, int C, const
   if (rc) return rc;
   const long R = (long)B * T * F;
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  if (act_contiguous(m, B) && vec_channels(C)) {
+    const int threads = (256 / (C / 4)) * (C / 4);
+    if (out_dtype == DS2_F32)
+      bn_clip_fwd_vec_kernel<float><<<ew_grid(R * C / 4), threads, 0, cs>>>(x, R, C, mean, rstd, gamma, beta, cap, clip, static_cast<float*>(out));
+    else
+      bn_clip_fwd_vec_kernel<__nv_bfloat16><<<ew_grid(R * C / 4), threads, 0, cs>>>(x, R, C, mean, rstd, gamma, beta, cap, clip, static_cast<__nv_bfloat16*>(out));
+    DS2_LAUNCH_CHECK("bn_clip_fwd_vec_kernel");
+    count_launch();
+    return DS2_OK;
+  }
   if (out_dtype == DS2_F32)
     bn_clip_fwd_kernel<float><<<ew_grid(R * C), (256 / C) * C, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, static_cast<float*>(out), m);
   else
@@ -505,6 +637,23 @@ extern "C" int ds2_bn_clip_bwd(const float* x, int B, int T, int F, int C, const
   long rows_per = 256 / C * 16;
   int grid = (int)((R + rows_per - 1) / rows_per);
   if (grid > num_sms() * 8) grid = num_sms() * 8;
+  if (act_contiguous(m, B) && vec_channels(C)) {
+    const int threads = (256 / (C / 4)) * (C / 4);
+    if (dout_dtype == DS2_F32) {
+      const float* d = static_cast<const float*>(dout);
+      bn_clip_bwd_reduce_vec_kernel<float><<<grid, threads, 0, cs>>>(x, R, C, mean, rstd, gamma, beta, cap, clip, d, sums_scratch);
+      DS2_LAUNCH_CHECK("bn_clip_bwd_reduce_vec_kernel");
+      bn_clip_bwd_apply_vec_kernel<float><<<ew_grid(R * C / 4), threads, 0, cs>>>(x, R, C, mean, rstd, gamma, beta, cap, clip, d, sums_scratch, dx, dgamma, dbeta);
+    } else {
+      const __nv_bfloat16* d = static_cast<const __nv_bfloat16*>(dout);
+      bn_clip_bwd_reduce_vec_kernel<__nv_bfloat16><<<grid, threads, 0, cs>>>(x, R, C, mean, rstd, gamma, beta, cap, clip, d, sums_scratch);
+      DS2_LAUNCH_CHECK("bn_clip_bwd_reduce_vec_kernel");
+      bn_clip_bwd_apply_vec_kernel<__nv_bfloat16><<<ew_grid(R * C / 4), threads, 0, cs>>>(x, R, C, mean, rstd, gamma, beta, cap, clip, d, sums_scratch, dx, dgamma, dbeta);
+    }
+    DS2_LAUNCH_CHECK("bn_clip_bwd_apply_vec_kernel");
+    count_launch(2);
+    return DS2_OK;
+  }
   if (dout_dtype == DS2_F32) {
     const float* d = static_cast<const float*>(dout);
     bn_clip_bwd_reduce_kernel<float><<<grid, (256 / C) * C, 0, cs>>>(x, R, mean, rstd, gamma, beta, cap, clip, d, m, sums_scratch);

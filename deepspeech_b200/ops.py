@@ -308,11 +308,90 @@ class _ConvGemmFn(torch.autograd.Function):
         return dx, dw, db, None, None, dgamma, dbeta, None, None
 
 
+def _slack_bf16(shape, device):
+    """bf16 tensor of `shape` whose storage extends 64 zeroed bytes past the last element (the window view of
+    ds2_conv_window_* reads them with its last box)."""
+    n = int(np.prod(shape))
+    flat = torch.empty(n + 32, dtype=torch.bfloat16, device=device)
+    flat[n:].zero_()
+    return flat[:n].view(shape)
+
+
+class _ConvWindowFn(torch.autograd.Function):
+    """Same contract as _ConvGemmFn, without a patch matrix: a = f(x) is written once in bf16 and the tensor cores read
+    overlapping filter windows of it through a strided TMA view (ds2_conv_window_*; 32 channels in and out, sf = 1)."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias, st, gamma, beta, eps, cap):
+        B, Ti, Fi, Ci = x.shape
+        KT, KF, _, Co = w.shape
+        To, Fo = (Ti - KT) // st + 1, Fi - KF + 1
+        if To <= 0 or Fo <= 0:
+            raise ValueError("conv2d: input %dx%d smaller than the %dx%d filter" % (Ti, Fi, KT, KF))
+        dev = x.device
+        has_bn = gamma is not None
+        mean = rstd = None
+        a = _slack_bf16((B, Ti, Fi, Ci), dev)
+        if has_bn:
+            mean, rstd = bn_stats(x, Ci, eps)
+            omap = (Ti * Fi * Ci, Fi * Ci, Ci, 1)
+            check(lib.ds2_bn_clip_fwd(_p(x), B, Ti, Fi, Ci, _p(mean), _p(rstd), _p(gamma), _p(beta), float(cap or 0.0),
+                                      int(cap is not None), _p(a), DS2_BF16, *omap, _stream()), "ds2_bn_clip_fwd")
+        else:
+            check(lib.ds2_cast(_p(x), DS2_F32, _p(a), DS2_BF16, x.numel(), _stream()), "ds2_cast")
+        K = KT * KF * Ci
+        wt = torch.empty((Co, K), dtype=torch.bfloat16, device=dev)
+        wd = torch.empty((Ci, K), dtype=torch.bfloat16, device=dev)
+        check(lib.ds2_conv_window_weights(_p(w), _p(wt), _p(wd), KT, KF, _stream()), "ds2_conv_window_weights")
+        y = torch.empty((B, To, Fo, Co), dtype=torch.float32, device=dev)
+        check(lib.ds2_conv_window_fwd(_p(a), _p(wt), _p(bias), _p(y), B, Ti, Fi, KT, KF, st, _stream()), "ds2_conv_window_fwd")
+        ctx.save_for_backward(x, gamma, beta, mean, rstd, a, wd)
+        ctx.geom = (B, Ti, Fi, Ci, KT, KF, st, To, Fo, Co)
+        ctx.misc = (eps, cap, has_bn, bias is not None, tuple(w.shape))
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, gamma, beta, mean, rstd, a, wd = ctx.saved_tensors
+        B, Ti, Fi, Ci, KT, KF, st, To, Fo, Co = ctx.geom
+        eps, cap, has_bn, has_bias, wshape = ctx.misc
+        dev = x.device
+        dy = cast(dy.contiguous(), torch.float32)
+        pad = KF - 1
+        dyp = _slack_bf16((B * To, Fo + 2 * pad, Co), dev)
+        check(lib.ds2_conv_window_pad_cast(_p(dy), _p(dyp), B * To, Fo, pad, _stream()), "ds2_conv_window_pad_cast")
+        dw = torch.empty(wshape, dtype=torch.float32, device=dev)
+        check(lib.ds2_conv_window_wgrad(_p(a), _p(dyp), _p(dw), B, Ti, Fi, KT, KF, st, _stream()), "ds2_conv_window_wgrad")
+        db = colsum(dy.view(B * To * Fo, Co), B * To * Fo, Co, Co) if has_bias else None
+        dx = dgamma = dbeta = None
+        if ctx.needs_input_grad[0]:
+            da = torch.empty(x.shape, dtype=torch.float32, device=dev)
+            check(lib.ds2_conv_window_dgrad(_p(dyp), _p(wd), _p(da), B, Ti, Fi, KT, KF, st, _stream()), "ds2_conv_window_dgrad")
+            if has_bn:
+                dx = torch.empty_like(x)
+                dgamma = torch.empty_like(gamma)
+                dbeta = torch.empty_like(beta)
+                omap = (Ti * Fi * Ci, Fi * Ci, Ci, 1)
+                check(lib.ds2_bn_clip_bwd(_p(x), B, Ti, Fi, Ci, _p(mean), _p(rstd), _p(gamma), _p(beta), float(cap or 0.0),
+                                          int(cap is not None), _p(da), DS2_F32, *omap, _p(_bn_scratch(dev)), _p(dx), _p(dgamma),
+                                          _p(dbeta), _stream()), "ds2_bn_clip_bwd")
+            else:
+                dx = da
+        return dx, dw, db, None, dgamma, dbeta, None, None
+
+
+USE_CONV_WINDOW = True
+
+
 def conv2d_gemm(x, w, bias, st, sf, gamma=None, beta=None, eps=1e-3, cap=None):
-    """Tensor-core convolution of f(x): f = clip(BN(x)) when gamma/beta are given, identity otherwise."""
+    """Tensor-core convolution of f(x): f = clip(BN(x)) when gamma/beta are given, identity otherwise.
+    32-channel layers with sf = 1 take the implicit (window) form, everything else the explicit patch matrix."""
     _need_cuda(x, w)
     if x.dtype != torch.float32:
         raise ValueError("conv2d_gemm: fp32 input expected")
+    KT, KF, Ci, Co = w.shape
+    if USE_CONV_WINDOW and lib.ds2_conv_window_supported(Ci, Co, x.shape[2], KT, KF, sf):
+        return _ConvWindowFn.apply(x.contiguous(), w.contiguous(), bias, st, gamma, beta, eps, cap)
     return _ConvGemmFn.apply(x.contiguous(), w.contiguous(), bias, st, sf, gamma, beta, eps, cap)
 
 

@@ -155,6 +155,25 @@ int ds2_im2col(const float* x, const float* mean, const float* rstd, const float
 int ds2_col2im(const void* dP, long ldp, float* dx, int B, int Ti, int Fi, int Ci, int KT, int KF, int st, int sf,
                void* stream);
 
+/* Implicit-GEMM form of the same convolution for 32-channel layers with unit frequency stride (the reference's
+ * conv2: filter [10,5,32,32], strides (2,1)): no patch matrix, the tensor cores read overlapping windows of the
+ * channel-last activation through a strided TMA view (deepspeech_b200/csrc/ds2_conv_window.cu).
+ *   a    bf16 [B,Ti,Fi,32]  - the layer input (for conv2: clip(BN(conv1)), written by ds2_bn_clip_fwd); the buffer
+ *                             must extend 64 bytes past its last element (the last window reads them, unused);
+ *   wt   bf16 [32][KT*KF*32] - filters as wt[co][(kt,kf,ci)],  wd bf16 [32][KT*KF*32] - wd[ci][(kt,KF-1-kf,co)],
+ *                             both made from the HWIO fp32 filter by ds2_conv_window_weights;
+ *   dyp  bf16 [B*To, Fo+2*(KF-1), 32] - dL/dy with KF-1 zero positions on both sides of every row
+ *                             (ds2_conv_window_pad_cast), 64 bytes of slack after the last element as for `a`;
+ *   y    f32 [B,To,Fo,32], da f32 [B,Ti,Fi,32] (every element written), dw f32 HWIO [KT,KF,32,32].
+ * ds2_conv_window_supported tells whether a shape is taken. */
+int ds2_conv_window_supported(int Ci, int Co, int Fi, int KT, int KF, int sf);
+int ds2_conv_window_weights(const float* w, void* wt, void* wd, int KT, int KF, void* stream);
+int ds2_conv_window_pad_cast(const float* dy, void* dyp, long R, int P, int pad, void* stream);
+int ds2_conv_window_fwd(const void* a, const void* wt, const float* bias, float* y, int B, int Ti, int Fi, int KT, int KF, int st,
+                        void* stream);
+int ds2_conv_window_dgrad(const void* dyp, const void* wd, float* da, int B, int Ti, int Fi, int KT, int KF, int st, void* stream);
+int ds2_conv_window_wgrad(const void* a, const void* dyp, float* dw, int B, int Ti, int Fi, int KT, int KF, int st, void* stream);
+
 /* batch_norm2 / batch_norm (src/custom_ops.py:107-160, :163-181; training mode, biased batch
  * variance over all rows of the channel-last [R,C] tensor) fused with relux(.., capping)
  * (src/custom_ops.py:99-104).  C <= 256.  sums_scratch: 2*C doubles.

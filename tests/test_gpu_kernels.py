@@ -201,6 +201,77 @@ def test_conv_gemm_route_vs_fp64():
         assert abs(np.linalg.norm(got.grad.cpu().numpy()) / np.linalg.norm(ref.grad.numpy()) - 1) < 3e-2, name
 
 
+@pytest.mark.parametrize("B,Ti,Fi,KT,KF,st", [(2, 31, 79, 10, 5, 2), (1, 12, 9, 3, 2, 1), (3, 22, 128, 4, 7, 3), (2, 741, 79, 10, 5, 2)])
+def test_conv_window_kernels_vs_fp64(B, Ti, Fi, KT, KF, st):
+    """Implicit-GEMM conv (forward, data gradient, weight gradient through the strided TMA window view) against an fp64
+    convolution of the SAME bf16-rounded operands: only fp32 accumulation order differs (<= 1e-4 of the scale)."""
+    ops = _ops()
+    from deepspeech_b200._lib import check, lib
+    C = 32
+    assert lib.ds2_conv_window_supported(C, C, Fi, KT, KF, 1) == 1
+    rng = np.random.default_rng(Ti * 3 + KF)
+    To, Fo = (Ti - KT) // st + 1, Fi - KF + 1
+    bf = lambda t: t.to(torch.bfloat16).float()
+    x = bf(torch.tensor(rng.standard_normal((B, Ti, Fi, C)), dtype=torch.float32, device="cuda"))
+    w = bf(torch.tensor(rng.standard_normal((KT, KF, C, C)) * 0.1, dtype=torch.float32, device="cuda"))
+    bias = torch.tensor(rng.standard_normal(C), dtype=torch.float32, device="cuda")
+    dy = bf(torch.tensor(rng.standard_normal((B, To, Fo, C)), dtype=torch.float32, device="cuda"))
+    p, st_ = ops._p, ops._stream
+    a = ops._slack_bf16((B, Ti, Fi, C), "cuda")
+    a.copy_(x)
+    K = KT * KF * C
+    wt = torch.empty((C, K), dtype=torch.bfloat16, device="cuda")
+    wd = torch.empty((C, K), dtype=torch.bfloat16, device="cuda")
+    check(lib.ds2_conv_window_weights(p(w), p(wt), p(wd), KT, KF, st_()), "weights")
+    y = torch.full((B, To, Fo, C), float("nan"), dtype=torch.float32, device="cuda")
+    check(lib.ds2_conv_window_fwd(p(a), p(wt), p(bias), p(y), B, Ti, Fi, KT, KF, st, st_()), "fwd")
+    dyp = ops._slack_bf16((B * To, Fo + 2 * (KF - 1), C), "cuda")
+    dyp.fill_(float("nan"))
+    check(lib.ds2_conv_window_pad_cast(p(dy), p(dyp), B * To, Fo, KF - 1, st_()), "pad")
+    dw = torch.full((KT, KF, C, C), float("nan"), dtype=torch.float32, device="cuda")
+    check(lib.ds2_conv_window_wgrad(p(a), p(dyp), p(dw), B, Ti, Fi, KT, KF, st, st_()), "wgrad")
+    da = torch.full((B, Ti, Fi, C), float("nan"), dtype=torch.float32, device="cuda")
+    check(lib.ds2_conv_window_dgrad(p(dyp), p(wd), p(da), B, Ti, Fi, KT, KF, st, st_()), "dgrad")
+    torch.cuda.synchronize()
+    xr = x.double().cpu().permute(0, 3, 1, 2).requires_grad_(True)
+    wr = w.double().cpu().requires_grad_(True)
+    yr = torch.nn.functional.conv2d(xr, wr.permute(3, 2, 0, 1), bias.double().cpu(), stride=(st, 1))
+    (yr * dy.double().cpu().permute(0, 3, 1, 2)).sum().backward()
+    assert relerr(y.cpu().permute(0, 3, 1, 2).numpy(), yr.detach().numpy()) < 1e-4
+    assert relerr(dw.cpu().numpy(), wr.grad.numpy()) < 1e-4
+    assert relerr(da.cpu().permute(0, 3, 1, 2).numpy(), xr.grad.numpy()) < 1e-4
+
+
+def test_conv_window_route_matches_patch_matrix_route():
+    """The autograd wrappers: window form and explicit patch-matrix form of conv2 (with the fused BN1 + clip) agree to
+    bf16 rounding of the operands (both round the same values; only summation order differs)."""
+    ops = _ops()
+    rng = np.random.default_rng(5)
+    B, Ti, Fi, C = 2, 41, 79, 32
+    res = {}
+    for use in (True, False):
+        ops.USE_CONV_WINDOW = use
+        x = torch.tensor(rng.standard_normal((B, Ti, Fi, C)) * 4 if use else res["x"], dtype=torch.float32, device="cuda").requires_grad_(True)
+        if use:
+            res["x"] = x.detach().cpu().numpy()
+            res["w"] = rng.standard_normal((10, 5, C, C)) * 0.05
+            res["b"] = rng.standard_normal(C) * 0.1
+            res["g"] = rng.uniform(0.6, 1.4, C)
+            res["be"] = rng.standard_normal(C) * 0.3
+            res["dy"] = None
+        mk = lambda k: torch.tensor(res[k], dtype=torch.float32, device="cuda").requires_grad_(True)
+        w, b, g, be = mk("w"), mk("b"), mk("g"), mk("be")
+        y = ops.conv2d_gemm(x, w, b, 2, 1, g, be, 1e-3, 20.0)
+        if res["dy"] is None:
+            res["dy"] = rng.standard_normal(tuple(y.shape))
+        (y * torch.tensor(res["dy"], dtype=torch.float32, device="cuda")).sum().backward()
+        torch.cuda.synchronize()
+        res[use] = [t.detach().cpu().numpy() for t in (y, x.grad, w.grad, b.grad, g.grad, be.grad)]
+    ops.USE_CONV_WINDOW = True
+    for got, ref, name in zip(res[True], res[False], ("y", "dx", "dw", "db", "dgamma", "dbeta")):
+        assert relerr(got, ref) < 2e-2, name
+
+
 @pytest.mark.parametrize("order", ["nhwc", "cf", "fc"])
 def test_bn_clip_fwd_bwd_vs_oracle(order):
     ops = _ops()
