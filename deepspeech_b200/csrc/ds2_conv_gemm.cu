@@ -55,6 +55,23 @@ im2col_kernel(const float* __restrict__ x, const float* __restrict__ mean, const
 #pragma unroll
       for (int i = 0; i < 8; ++i) { s8[i] = sc[ci + i]; h8[i] = sh[ci + i]; }
     }
+    // slow path (Ci not a multiple of 8, e.g. the single-channel conv1): the tap of each of the 8 elements is row
+    // independent too, so its input offset relative to the patch origin is computed once, not per row
+    int off8[8];
+    if (!fast) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int k = k8 + i;
+        off8[i] = -1;
+        if (k < g.K) {
+          const int c1 = k % g.Ci;
+          const int q = k / g.Ci;
+          const int kf1 = q % g.KF, kt1 = q / g.KF;
+          off8[i] = (kt1 * g.Fi + kf1) * g.Ci + c1;
+          if (BN) { s8[i] = sc[c1]; h8[i] = sh[c1]; }
+        }
+      }
+    }
     for (int m = blockIdx.x * rows_per_block + rl; m < M; m += gridDim.x * rows_per_block) {
       const int fo = m % g.Fo;
       const int r = m / g.Fo;
@@ -74,17 +91,14 @@ im2col_kernel(const float* __restrict__ x, const float* __restrict__ mean, const
           }
         }
       } else {
+        const float* src = x + (((long)b * g.Ti + to * g.st) * g.Fi + fo * g.sf) * g.Ci;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const int k = k8 + i;
           float t = 0.f;
-          if (k < g.K) {
-            const int c1 = k % g.Ci;
-            const int q = k / g.Ci;
-            const int kf1 = q % g.KF, kt1 = q / g.KF;
-            t = __ldg(x + (((long)b * g.Ti + (to * g.st + kt1)) * g.Fi + (fo * g.sf + kf1)) * g.Ci + c1);
+          if (off8[i] >= 0) {
+            t = __ldg(src + off8[i]);
             if (BN) {
-              t = fmaf(t, sc[c1], sh[c1]);
+              t = fmaf(t, s8[i], h8[i]);
               if (clip) t = fminf(fmaxf(t, 0.f), cap);
             }
           }

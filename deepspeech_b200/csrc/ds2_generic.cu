@@ -418,6 +418,96 @@ bn_clip_bwd_apply_vec_kernel(const float* __restrict__ x, long R, int C, const f
   }
 }
 
+// ---- the three passes when the activation side is the RECURRENT layout [T,B,feat]: one (b,t) row of F*C values at a
+// time goes through shared memory, so that both sides are read / written contiguously.  feat = c*F+f (NCHW model,
+// src/deepSpeech_NCHW.py:166-168: the row is transposed on the way) or f*C+c (NHWC model, src/deepSpeech.py:162-164).
+// Row r = b*T + t of x lives at out row t*B + b.  Thread <-> fixed channel (256 % C == 0); smem holds F*C floats.
+struct RowMap {
+  int B, T, F, C;
+  int cf;              // 1: feat = c*F + f, 0: feat = f*C + c
+};
+__device__ __forceinline__ long rnn_row(const RowMap& m, int r) {
+  const int b = r / m.T, t = r - b * m.T;
+  return ((long)t * m.B + b) * ((long)m.F * m.C);
+}
+__device__ __forceinline__ int feat_slot(const RowMap& m, int f, int c) { return m.cf ? c * m.F + f : f * m.C + c; }
+
+template <typename TO>
+__global__ void __launch_bounds__(256)
+bn_clip_fwd_rows_kernel(const float* __restrict__ x, int R, const float* __restrict__ mean, const float* __restrict__ rstd,
+                        const float* __restrict__ gamma, const float* __restrict__ beta, float cap, int clip, TO* __restrict__ out,
+                        RowMap m) {
+  extern __shared__ float bn_row[];
+  const int C = m.C, FC = m.F * m.C;
+  const int c = threadIdx.x % C, fl = threadIdx.x / C, fstep = blockDim.x / C;
+  const float a = rstd[c] * gamma[c];
+  const float sh = beta[c] - mean[c] * a;
+  for (int r = blockIdx.x; r < R; r += gridDim.x) {
+    const float* xr = x + (long)r * FC;
+    for (int f = fl; f < m.F; f += fstep) {
+      float v = fmaf(xr[f * C + c], a, sh);
+      if (clip) v = fminf(fmaxf(v, 0.f), cap);
+      bn_row[feat_slot(m, f, c)] = v;
+    }
+    __syncthreads();
+    TO* orow = out + rnn_row(m, r);
+    for (int j = threadIdx.x; j < FC; j += blockDim.x) stf(orow + j, bn_row[j]);
+    __syncthreads();
+  }
+}
+
+template <typename TG, bool APPLY>
+__global__ void __launch_bounds__(256)
+bn_clip_bwd_rows_kernel(const float* __restrict__ x, int R, const float* __restrict__ mean, const float* __restrict__ rstd,
+                        const float* __restrict__ gamma, const float* __restrict__ beta, float cap, int clip,
+                        const TG* __restrict__ dout, RowMap m, double* __restrict__ sums, float* __restrict__ dx,
+                        float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  extern __shared__ float bn_row[];
+  const int C = m.C, FC = m.F * m.C;
+  const int c = threadIdx.x % C, fl = threadIdx.x / C, fstep = blockDim.x / C;
+  const float mu = mean[c], rs = rstd[c], g = gamma[c], be = beta[c];
+  float m1 = 0.f, m2 = 0.f;
+  if (APPLY) {
+    m1 = (float)(sums[c] / ((double)R * m.F));
+    m2 = (float)(sums[C + c] / ((double)R * m.F));
+  }
+  float s1 = 0.f, s2 = 0.f;
+  for (int r = blockIdx.x; r < R; r += gridDim.x) {
+    const TG* drow = dout + rnn_row(m, r);
+    for (int j = threadIdx.x; j < FC; j += blockDim.x) bn_row[j] = ldf(drow + j);
+    __syncthreads();
+    const float* xr = x + (long)r * FC;
+    for (int f = fl; f < m.F; f += fstep) {
+      const float xh = (xr[f * C + c] - mu) * rs;
+      const float bn = fmaf(xh, g, be);
+      float d = bn_row[feat_slot(m, f, c)];
+      if (clip && !(bn > 0.f && bn < cap)) d = 0.f;
+      if (APPLY) {
+        dx[(long)r * FC + f * C + c] = g * rs * (d - m1 - xh * m2);
+      } else {
+        s1 += d;
+        s2 = fmaf(d, xh, s2);
+      }
+    }
+    __syncthreads();
+  }
+  if (!APPLY) {
+    __shared__ float sh1[256], sh2[256];
+    sh1[threadIdx.x] = s1;
+    sh2[threadIdx.x] = s2;
+    __syncthreads();
+    if (threadIdx.x < C) {
+      double a = 0, b = 0;
+      for (int i = threadIdx.x; i < blockDim.x; i += C) { a += sh1[i]; b += sh2[i]; }
+      atomicAdd(sums + c, a);
+      atomicAdd(sums + C + c, b);
+    }
+  } else if (blockIdx.x == 0 && threadIdx.x < C) {
+    if (dbeta) dbeta[threadIdx.x] = (float)sums[threadIdx.x];
+    if (dgamma) dgamma[threadIdx.x] = (float)sums[C + threadIdx.x];
+  }
+}
+
 // ------------------------------------------------------------------ element-wise helpers
 template <typename TI, typename TO>
 __global__ void __launch_bounds__(256) cast_kernel(const TI* __restrict__ in, TO* __restrict__ out, long n) {
@@ -580,6 +670,16 @@ static bool act_contiguous(const ActMap& m, int B) {
   return m.sc == 1 && m.sf == m.C && m.st == (long)m.F * m.C && m.sb == (long)m.T * m.F * m.C;
 }
 static bool vec_channels(int C) { return C % 4 == 0 && 256 % (C / 4) == 0; }
+// activation side = recurrent layout [T,B,F*C] with feat = c*F+f (cf) or f*C+c ?
+static bool act_rnn_rows(const ActMap& m, int B, RowMap* rm) {
+  const long feat = (long)m.F * m.C;
+  if (256 % m.C != 0 || feat * 4 > 40 * 1024 || m.sb != feat || m.st != (long)B * feat) return false;
+  if (m.sf == 1 && m.sc == m.F) rm->cf = 1;
+  else if (m.sc == 1 && m.sf == m.C) rm->cf = 0;
+  else return false;
+  rm->B = B; rm->T = m.T; rm->F = m.F; rm->C = m.C;
+  return true;
+}
 
 extern "C" int ds2_bn_stats(const float* x, long R, int C, float eps, double* sums_scratch, float* mean, float* rstd, void* stream) {
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
@@ -612,6 +712,19 @@ extern "C" int ds2_bn_clip_fwd(const float* x, int B, int T, int F, int C, const
     else
       bn_clip_fwd_vec_kernel<__nv_bfloat16><<<ew_grid(R * C / 4), threads, 0, cs>>>(x, R, C, mean, rstd, gamma, beta, cap, clip, static_cast<__nv_bfloat16*>(out));
     DS2_LAUNCH_CHECK("bn_clip_fwd_vec_kernel");
+    count_launch();
+    return DS2_OK;
+  }
+  RowMap rm;
+  if (R < 2147483647L / C && act_rnn_rows(m, B, &rm)) {
+    const int rows = (int)((long)B * T);
+    const int grid = rows < num_sms() * 8 ? rows : num_sms() * 8;
+    const size_t sm = (size_t)F * C * sizeof(float);
+    if (out_dtype == DS2_F32)
+      bn_clip_fwd_rows_kernel<float><<<grid, 256, sm, cs>>>(x, rows, mean, rstd, gamma, beta, cap, clip, static_cast<float*>(out), rm);
+    else
+      bn_clip_fwd_rows_kernel<__nv_bfloat16><<<grid, 256, sm, cs>>>(x, rows, mean, rstd, gamma, beta, cap, clip, static_cast<__nv_bfloat16*>(out), rm);
+    DS2_LAUNCH_CHECK("bn_clip_fwd_rows_kernel");
     count_launch();
     return DS2_OK;
   }
@@ -651,6 +764,26 @@ extern "C" int ds2_bn_clip_bwd(const float* x, int B, int T, int F, int C, const
       bn_clip_bwd_apply_vec_kernel<__nv_bfloat16><<<ew_grid(R * C / 4), threads, 0, cs>>>(x, R, C, mean, rstd, gamma, beta, cap, clip, d, sums_scratch, dx, dgamma, dbeta);
     }
     DS2_LAUNCH_CHECK("bn_clip_bwd_apply_vec_kernel");
+    count_launch(2);
+    return DS2_OK;
+  }
+  RowMap rm;
+  if (R < 2147483647L / C && act_rnn_rows(m, B, &rm)) {
+    const int rows = (int)((long)B * T);
+    const int g2 = rows < num_sms() * 8 ? rows : num_sms() * 8;
+    const size_t sm = (size_t)F * C * sizeof(float);
+    if (dout_dtype == DS2_F32) {
+      const float* d = static_cast<const float*>(dout);
+      bn_clip_bwd_rows_kernel<float, false><<<g2, 256, sm, cs>>>(x, rows, mean, rstd, gamma, beta, cap, clip, d, rm, sums_scratch, dx, dgamma, dbeta);
+      DS2_LAUNCH_CHECK("bn_clip_bwd_rows_kernel<reduce>");
+      bn_clip_bwd_rows_kernel<float, true><<<g2, 256, sm, cs>>>(x, rows, mean, rstd, gamma, beta, cap, clip, d, rm, sums_scratch, dx, dgamma, dbeta);
+    } else {
+      const __nv_bfloat16* d = static_cast<const __nv_bfloat16*>(dout);
+      bn_clip_bwd_rows_kernel<__nv_bfloat16, false><<<g2, 256, sm, cs>>>(x, rows, mean, rstd, gamma, beta, cap, clip, d, rm, sums_scratch, dx, dgamma, dbeta);
+      DS2_LAUNCH_CHECK("bn_clip_bwd_rows_kernel<reduce>");
+      bn_clip_bwd_rows_kernel<__nv_bfloat16, true><<<g2, 256, sm, cs>>>(x, rows, mean, rstd, gamma, beta, cap, clip, d, rm, sums_scratch, dx, dgamma, dbeta);
+    }
+    DS2_LAUNCH_CHECK("bn_clip_bwd_rows_kernel<apply>");
     count_launch(2);
     return DS2_OK;
   }

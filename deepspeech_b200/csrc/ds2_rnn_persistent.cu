@@ -252,6 +252,8 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
         if ((int)rank * p.ksl + uc * 8 < H) goff[m] = ub * (int)p.out_row_pitch + uc * 8;
       }
     }
+    if ((p.exp & 16) && (inst & 1)) { __nanosleep(900); __nanosleep(900); }
+    if ((p.exp & 32) && d == 1) __nanosleep(900);
     uint32_t ph = 0;
     for (int step = 0; step < T; ++step) {
       const int t = BWD ? (rev ? step : T - 1 - step) : (rev ? T - 1 - step : step);
