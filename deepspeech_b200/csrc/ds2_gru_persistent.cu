@@ -16,7 +16,8 @@
 
 namespace ds2 {
 
-static constexpr int GKS = 4;               // cluster size = K split
+// cluster size = K split: 4 when the CTA's K slices of U fit its 512 TMEM columns, else 8 (H = 1760: the forward keeps
+// 3 gates x 256 of 1760 columns, the backward 704 of 5280; a CTA then finishes 16 units instead of 32)
 static constexpr int GBP = 16;              // utterances per instance (MMA N)
 static constexpr int GINST_THREADS = 160;   // per instance: 1 control warp + 4 loader/epilogue warps
 static constexpr int GMAX_NI = 2;
@@ -37,6 +38,7 @@ struct GruParams {
   int T, B, H, ND, reverse_mask;
   int NC, NI, tiles_m, ksl, nbox;   // batch chunks, instances per chunk, M tiles per direction, K-slice length
                                     // (multiple of 64), boxes per slice
+  int z_base;                       // first (chunk, direction) pair of this launch: pair z = chunk * ND + d
   float scale;
   int fenced;                   // see RnnPersistParams::fenced (ds2_rnn_persistent.cu)
 };
@@ -111,21 +113,22 @@ struct GruSmem {
   uint32_t a_off, b_off, slab_off, bar_off, total;
 };
 static constexpr int GBARS_PER_INST = 3;   // b_ready, mma_done, slab_full
-__host__ __device__ inline GruSmem gru_smem_layout(int nbox, int NI, int NG) {
+__host__ __device__ inline GruSmem gru_smem_layout(int nbox, int NI, int NG) {   // the slab size does not depend on the K split
   GruSmem s;
   s.a_off = 0;                                              // GSTAGE_BOX x [128 x 64] bf16 staging of U
   s.b_off = s.a_off + GSTAGE_BOX * 16384;                         // NI x nbox x [16 x 64] bf16
   s.slab_off = s.b_off + NI * nbox * (GBP * 128);           // NI x KS x [32 x NG*16] fp32
-  s.bar_off = s.slab_off + NI * GKS * 32 * NG * GBP * 4;
+  s.bar_off = s.slab_off + NI * 128 * NG * GBP * 4;
   s.total = s.bar_off + 8 * (2 + NI * GBARS_PER_INST) + 16;
   return s;
 }
 
 // NG accumulator / A-operand groups: 3 gates (forward) or 1 (backward)
-template <bool BWD>
+template <bool BWD, int KSZ>
 __global__ void __launch_bounds__(GINST_THREADS * GMAX_NI, 1)
 gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
   constexpr int NG = BWD ? 1 : 3;
+  constexpr int UPC = 128 / KSZ;            // hidden units this CTA finishes per tile
   // 16-byte units of the moving operand per loader thread (= nbox): the forward's three resident gate slices
   // cap nbox at 4 (TMEM columns), the backward's single slice of the 3H-long contraction at GMAX_NBOX
   constexpr int GMAX_UNITS = BWD ? GMAX_NBOX : 4;
@@ -145,19 +148,20 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
   uint64_t* mma_bar = b_ready + 1;
   uint64_t* slab_bar = b_ready + 2;
   uint8_t* sB = smem + L.b_off + inst * nbox * (GBP * 128);
-  float* slab = reinterpret_cast<float*>(smem + L.slab_off) + inst * GKS * 32 * NG * GBP;
+  float* slab = reinterpret_cast<float*>(smem + L.slab_off) + inst * 128 * NG * GBP;
   // shared-space addresses used inside the step loop, computed once
   const uint32_t b_ready_a = keep_reg(smem_u32(b_ready)), mma_bar_a = b_ready_a + 8, slab_bar_a = b_ready_a + 16;
   const uint32_t sB_addr = keep_reg(smem_u32(sB)), slab_local = keep_reg(smem_u32(slab));
 
   const uint32_t rank = g_cluster_ctarank();
-  const int mt = blockIdx.y, chunk = blockIdx.z / p.ND, d = blockIdx.z % p.ND;
+  const int zz = p.z_base + blockIdx.z;
+  const int mt = blockIdx.y, chunk = zz / p.ND, d = zz % p.ND;
   const int m0 = mt * 128;
   const int rev = (p.reverse_mask >> d) & 1;
   const int T = p.T, H = p.H, ND = p.ND, Bn = p.B;
   const int KT = BWD ? 3 * H : H;                           // length of the contraction
-  unsigned int* ctr = p.ctr + ((chunk * p.ND + d) * NI + inst) * 32;
-  const unsigned int ctas_per_dir = GKS * p.tiles_m;
+  unsigned int* ctr = p.ctr + (blockIdx.z * NI + inst) * 32;
+  const unsigned int ctas_per_dir = KSZ * p.tiles_m;
   const int acols = NG * nbox * 32;                         // TMEM columns holding U
 
   if (threadIdx.x == 0) {
@@ -241,8 +245,8 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
     const int bl = et % GBP;
     const int jg = et / GBP;                     // 0..7
     const int b = chunk * GCHUNK + inst * GBP + bl;
-    const int j = m0 + 32 * (int)rank + 4 * jg;  // first of 4 consecutive hidden units
-    const bool jvalid = j < H;
+    const int j = m0 + UPC * (int)rank + 4 * jg; // first of 4 consecutive hidden units
+    const bool jvalid = jg < UPC / 4 && j < H;
     const int len_b = p.lens[b];
     const uint32_t slab_bar_local = slab_bar_a;
     // moving operand: forward h_{t-1} (rows of hs[d]), backward dgh_{t+1} (rows of dgh, direction offset d*3H)
@@ -304,7 +308,7 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) acc[g][i] = 0.f;
       if (step > 0) {
-        if (et == 0) mbar_arrive_expect_tx(slab_bar_a, GKS * 32 * NG * GBP * 4);
+        if (et == 0) mbar_arrive_expect_tx(slab_bar_a, 128 * NG * GBP * 4);
         if (et == 0) {
           const unsigned int need = ctas_per_dir * (unsigned int)step;
           if (p.fenced) {
@@ -347,26 +351,28 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
         }
         mbar_wait(mma_bar_a, ph, 40);
         tc_fence_after();
-        // partial sums of this CTA's K slice -> the cluster CTA that finishes those 32 units (all gates)
+        // partial sums of this CTA's K slice -> the cluster CTA that finishes those units (all gates)
 #pragma unroll
         for (int g = 0; g < NG; ++g) {
           uint32_t r[16];
           g_tmem_ld_32x16(d_tmem + g * GBP + (static_cast<uint32_t>(q * 32) << 16), r);
           tmem_ld_wait();
-          const uint32_t off = (((rank * 32 + lane) * NG + g) * GBP) * 4;
-          const uint32_t dst = g_map_to_rank(slab_local, (uint32_t)q) + off;
-          const uint32_t rbar = g_map_to_rank(slab_bar_local, (uint32_t)q);
+          const uint32_t row = q * 32 + lane, to = row / UPC;       // tile row -> finishing CTA
+          const uint32_t off = (((rank * UPC + row % UPC) * NG + g) * GBP) * 4;
+          const uint32_t dst = g_map_to_rank(slab_local, to) + off;
+          const uint32_t rbar = g_map_to_rank(slab_bar_local, to);
 #pragma unroll
           for (int c = 0; c < 4; ++c) g_st_async_v4(dst + c * 16, rbar, r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
         }
         tc_fence_before();
         mbar_wait(slab_bar_a, ph, 50);
 #pragma unroll
-        for (int s = 0; s < GKS; ++s)
+        for (int s = 0; s < KSZ; ++s)
 #pragma unroll
           for (int g = 0; g < NG; ++g)
 #pragma unroll
-            for (int i = 0; i < 4; ++i) acc[g][i] += lds_f32(slab_local + (((s * 32 + 4 * jg + i) * NG + g) * GBP + bl) * 4);
+            for (int i = 0; i < 4; ++i)
+              acc[g][i] += jg < UPC / 4 ? lds_f32(slab_local + (((s * UPC + 4 * jg + i) * NG + g) * GBP + bl) * 4) : 0.f;
         ph ^= 1;
       }
       if (jvalid) {
@@ -442,35 +448,43 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
 
 // ------------------------------------------------------------------ host side
 static constexpr size_t GWS_CTR_BYTES = 2048;
-static int gru_geometry(bool bwd, int B, int H, int ND, int* tiles_m, int* ksl, int* nbox, int* ni, int* nc, size_t* smem) {
+struct GruGeom {
+  int ks;              // cluster size (K split): 4 or 8
+  int tiles_m, ksl, nbox, ni, nc;
+  int zper;            // (chunk, direction) pairs one launch can hold: all of its CTAs must be resident at once
+  size_t smem;
+};
+static int gru_geometry(bool bwd, int B, int H, int ND, GruGeom* g) {
   // whole 16-utterance instances; more than one chunk of 32 only in whole chunks
   if (B < GBP || B % GBP != 0 || (B > GCHUNK && B % GCHUNK != 0) || H % 8 != 0 || H < 8 || (ND != 1 && ND != 2)) return 0;
   const int NG = bwd ? 1 : 3;
   const int KT = bwd ? 3 * H : H;
   const int tm = (H + 127) / 128;
-  const int slice = (KT + GKS - 1) / GKS;
-  const int l = ((slice + 63) / 64) * 64;
-  const int nb = l / 64;
-  if (nb > (bwd ? GMAX_NBOX : 4)) return 0;
   const int n_chunks = B <= GCHUNK ? 1 : B / GCHUNK;
   const int n_inst = B <= GCHUNK ? B / GBP : GMAX_NI;
-  if (NG * nb * 32 + n_inst * NG * GBP > 512) return 0;      // TMEM columns: resident U + accumulators
-  const size_t bytes = gru_smem_layout(nb, n_inst, NG).total + 1024;
-  if (bytes > 225 * 1024) return 0;
-  // every CTA must be resident at once (they wait on each other): one CTA per SM, 148 SMs
-  if (GKS * tm * ND * n_chunks > 144 || n_chunks * ND * n_inst * 32 * 4 > (int)GWS_CTR_BYTES) return 0;
-  if (tiles_m) *tiles_m = tm;
-  if (ksl) *ksl = l;
-  if (nbox) *nbox = nb;
-  if (ni) *ni = n_inst;
-  if (nc) *nc = n_chunks;
-  if (smem) *smem = bytes;
-  return 1;
+  for (int ks = 4; ks <= 8; ks *= 2) {
+    const int slice = (KT + ks - 1) / ks;
+    const int l = ((slice + 63) / 64) * 64;
+    const int nb = l / 64;
+    if (nb > (bwd ? GMAX_NBOX : 4)) continue;
+    if (NG * nb * 32 + n_inst * NG * GBP > 512) continue;      // TMEM columns: resident U + accumulators
+    const size_t bytes = gru_smem_layout(nb, n_inst, NG).total + 1024;
+    if (bytes > 225 * 1024) continue;
+    // every CTA of a launch must be resident at once (they wait on each other): one CTA per SM, 148 SMs
+    int zper = 144 / (ks * tm);
+    if (zper < 1) continue;
+    if (zper > ND * n_chunks) zper = ND * n_chunks;
+    if (zper * n_inst * 32 * 4 > (int)GWS_CTR_BYTES) zper = (int)GWS_CTR_BYTES / (n_inst * 32 * 4);
+    if (g) {
+      g->ks = ks; g->tiles_m = tm; g->ksl = l; g->nbox = nb; g->ni = n_inst; g->nc = n_chunks; g->zper = zper; g->smem = bytes;
+    }
+    return 1;
+  }
+  return 0;
 }
 
 int gru_persist_supported(int B, int H, int ND) {
-  return gru_geometry(false, B, H, ND, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr) &&
-         gru_geometry(true, B, H, ND, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+  return gru_geometry(false, B, H, ND, nullptr) && gru_geometry(true, B, H, ND, nullptr);
 }
 
 size_t gru_persist_workspace_bytes(int T, int B, int H, int ND) {
@@ -478,47 +492,58 @@ size_t gru_persist_workspace_bytes(int T, int B, int H, int ND) {
   return GWS_CTR_BYTES + (size_t)ND * 3 * H * H * 2;          // counters + U^T (bf16) for the backward
 }
 
-template <bool BWD>
-static int gru_launch(const CUtensorMap& ta, GruParams& p, size_t smem, cudaStream_t st) {
-  auto kern = gru_persist_kernel<BWD>;
-  static bool attr_done[2] = {false, false};
-  if (!attr_done[BWD]) {
+template <bool BWD, int KSZ>
+static int gru_launch_ks(const CUtensorMap& ta, GruParams& p, const GruGeom& g, cudaStream_t st) {
+  auto kern = gru_persist_kernel<BWD, KSZ>;
+  static bool attr_done = false;
+  if (!attr_done) {
     DS2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
-    attr_done[BWD] = true;
+    attr_done = true;
   }
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(GKS, p.tiles_m, p.ND * p.NC);
-  cfg.blockDim = dim3(GINST_THREADS * p.NI);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = st;
-  cudaLaunchAttribute attrs[2];
-  attrs[0].id = cudaLaunchAttributeClusterDimension;
-  attrs[0].val.clusterDim.x = GKS;
-  attrs[0].val.clusterDim.y = 1;
-  attrs[0].val.clusterDim.z = 1;
-  attrs[1].id = cudaLaunchAttributeCooperative;
-  attrs[1].val.cooperative = 1;
-  cfg.attrs = attrs;
-  cfg.numAttrs = getenv("DS2_RNN_NO_COOP") ? 1 : 2;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, p);
-  if (e != cudaSuccess && cfg.numAttrs == 2) {
-    (void)cudaGetLastError();
-    cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, kern, ta, p);
+  // one launch per group of (chunk, direction) pairs that fits the device; groups run one after the other
+  const int total = p.ND * p.NC;
+  for (int z0 = 0; z0 < total; z0 += g.zper) {
+    DS2_CUDA(cudaMemsetAsync(p.ctr, 0, GWS_CTR_BYTES, st));
+    p.z_base = z0;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(KSZ, p.tiles_m, total - z0 < g.zper ? total - z0 : g.zper);
+    cfg.blockDim = dim3(GINST_THREADS * p.NI);
+    cfg.dynamicSmemBytes = g.smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attrs[2];
+    attrs[0].id = cudaLaunchAttributeClusterDimension;
+    attrs[0].val.clusterDim.x = KSZ;
+    attrs[0].val.clusterDim.y = 1;
+    attrs[0].val.clusterDim.z = 1;
+    attrs[1].id = cudaLaunchAttributeCooperative;
+    attrs[1].val.cooperative = 1;
+    cfg.attrs = attrs;
+    cfg.numAttrs = getenv("DS2_RNN_NO_COOP") ? 1 : 2;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, p);
+    if (e != cudaSuccess && cfg.numAttrs == 2) {
+      (void)cudaGetLastError();
+      cfg.numAttrs = 1;
+      e = cudaLaunchKernelEx(&cfg, kern, ta, p);
+    }
+    if (e != cudaSuccess) return cuda_fail(e, BWD ? "gru_persist_kernel<bwd>" : "gru_persist_kernel<fwd>");
+    count_launch();
   }
-  if (e != cudaSuccess) return cuda_fail(e, BWD ? "gru_persist_kernel<bwd>" : "gru_persist_kernel<fwd>");
-  count_launch();
   return DS2_OK;
+}
+
+template <bool BWD>
+static int gru_launch(const CUtensorMap& ta, GruParams& p, const GruGeom& g, cudaStream_t st) {
+  p.tiles_m = g.tiles_m; p.ksl = g.ksl; p.nbox = g.nbox; p.NI = g.ni; p.NC = g.nc;
+  return g.ks == 4 ? gru_launch_ks<BWD, 4>(ta, p, g, st) : gru_launch_ks<BWD, 8>(ta, p, g, st);
 }
 
 int gru_fwd_persist(const float* wx, float scale, const void* u, const float* bw, const float* bu, const int* lens, void* hs,
                     void* gates, int T, int B, int H, int ND, int reverse_mask, void* ws, size_t ws_bytes, cudaStream_t st) {
   GruParams p = {};
-  size_t smem;
-  DS2_REQUIRE(gru_geometry(false, B, H, ND, &p.tiles_m, &p.ksl, &p.nbox, &p.NI, &p.NC, &smem), DS2_ERR_UNSUPPORTED,
+  GruGeom geo;
+  DS2_REQUIRE(gru_geometry(false, B, H, ND, &geo), DS2_ERR_UNSUPPORTED,
               "ds2_gru_fwd: persistent kernel does not take B=%d H=%d ND=%d", B, H, ND);
   DS2_REQUIRE(ws && ws_bytes >= GWS_CTR_BYTES, DS2_ERR_WORKSPACE, "ds2_gru_fwd: workspace of %zu bytes required", GWS_CTR_BYTES);
-  DS2_CUDA(cudaMemsetAsync(ws, 0, GWS_CTR_BYTES, st));
   CUtensorMap ta;
   int rc = make_tmap_2d_bf16(&ta, u, H, (uint64_t)ND * 3 * H, H, 64, 128);
   if (rc) return rc;
@@ -528,18 +553,17 @@ int gru_fwd_persist(const float* wx, float scale, const void* u, const float* bw
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = scale;
   p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
   if (!p.fenced) DS2_CUDA(cudaMemsetAsync(hs, DS2_FILL_BYTE, (size_t)ND * T * B * H * 2, st));
-  return gru_launch<false>(ta, p, smem, st);
+  return gru_launch<false>(ta, p, geo, st);
 }
 
 int gru_bwd_persist(const float* dout, const void* u, const int* lens, const void* hs, const void* gates, void* dgi, void* dgh,
                     int T, int B, int H, int ND, int reverse_mask, void* ws, size_t ws_bytes, cudaStream_t st) {
   GruParams p = {};
-  size_t smem;
-  DS2_REQUIRE(gru_geometry(true, B, H, ND, &p.tiles_m, &p.ksl, &p.nbox, &p.NI, &p.NC, &smem), DS2_ERR_UNSUPPORTED,
+  GruGeom geo;
+  DS2_REQUIRE(gru_geometry(true, B, H, ND, &geo), DS2_ERR_UNSUPPORTED,
               "ds2_gru_bwd: persistent kernel does not take B=%d H=%d ND=%d", B, H, ND);
   const size_t need = gru_persist_workspace_bytes(T, B, H, ND);
   DS2_REQUIRE(ws && ws_bytes >= need, DS2_ERR_WORKSPACE, "ds2_gru_bwd: workspace of %zu bytes required", need);
-  DS2_CUDA(cudaMemsetAsync(ws, 0, GWS_CTR_BYTES, st));
   // U^T per direction: ut[d][i][g*H + j] = U[d][g*H + j][i]
   __nv_bfloat16* ut = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + GWS_CTR_BYTES);
   int rc;
@@ -559,7 +583,7 @@ int gru_bwd_persist(const float* dout, const void* u, const int* lens, const voi
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = 1.f;
   p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
   if (!p.fenced) DS2_CUDA(cudaMemsetAsync(dgh, DS2_FILL_BYTE, (size_t)T * B * ND * 3 * H * 2, st));
-  return gru_launch<true>(ta, p, smem, st);
+  return gru_launch<true>(ta, p, geo, st);
 }
 
 }  // namespace ds2

@@ -587,7 +587,8 @@ def rec_stack_supported(cell: str, B: int, H: int, ND: int) -> bool:
 def _rec_ctas(cell: str, B: int, H: int, ND: int) -> int:
     """CTAs (= SMs) a persistent recurrence launch occupies: 4-CTA clusters x 128-unit tiles x directions x chunks."""
     chunks = max(1, B // 32) if cell == "gru" else 1
-    return 4 * ((H + 127) // 128) * ND * chunks
+    ks = 8 if (cell == "gru" and H > 1024) else 4          # the GRU's 8-CTA K split for wide layers
+    return ks * ((H + 127) // 128) * ND * chunks
 
 
 class _RecStackFn(torch.autograd.Function):

@@ -123,7 +123,8 @@ int ds2_gru_bwd(const float* dout, const void* u, const int* lens, const void* h
                 float* dhz_scratch, int dtype, int T, int B, int H, int ND, int reverse_mask, void* stream);
 /* Persistent tcgen05 form of the same GRU (one launch per layer and pass, U resident in TMEM): u, hs, gates, dgi, dgh
  * are bf16, wx/dout/bw/bu fp32, same layouts as above.  ds2_gru_persistent_supported says whether (B,H,ND) fits
- * (B in {16,32}, H%8==0, 3 gates x H/4 columns of U + accumulators within 512 TMEM columns: H <= 1024 at B=32);
+ * (B = 16 or a multiple of 32, H%8==0; H <= 1024 runs both directions in one launch, wider layers use an 8-CTA K split
+ * and one launch per direction);
  * workspace = ds2_gru_workspace_bytes (step counters + U^T for the backward), the caller owns it. */
 int ds2_gru_persistent_supported(int B, int H, int ND);
 size_t ds2_gru_workspace_bytes(int T, int B, int H, int ND);

@@ -458,7 +458,8 @@ def test_birnn_layer_bf16_persistent_vs_oracle(T, B, I, H, ragged):
 
 
 @pytest.mark.parametrize("T,B,I,H,ragged", [(5, 32, 64, 64, False), (9, 32, 128, 256, True), (7, 16, 72, 200, True),
-                                             (4, 32, 256, 800, False), (20, 32, 64, 1024, True), (6, 64, 64, 328, True)])
+                                             (4, 32, 256, 800, False), (20, 32, 64, 1024, True), (6, 64, 64, 328, True),
+                                             (4, 32, 128, 1760, True), (3, 64, 64, 1096, True)])
 def test_bigru_layer_bf16_persistent_vs_oracle(T, B, I, H, ragged):
     """Persistent tcgen05 GRU (bf16 operands, fp32 accumulation and gate math) against the fp64 oracle on the SAME
     bf16-rounded weights: outputs <= 1e-2 of the output scale; the GRU has no hard mask, so gradients are compared
