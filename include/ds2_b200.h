@@ -200,6 +200,18 @@ int ds2_cast(const void* in, int in_dtype, void* out, int out_dtype, long n, voi
 int ds2_colsum(const void* x, int dtype, long R, int N, long ld, float* out, int accumulate, void* stream);
 int ds2_transpose(const void* in, int in_dtype, long R, long C, long ldi, void* out, int out_dtype, long ldo, void* stream);
 
+/* ---- optimizer step (the step right after the hot path) -----------------------
+ * tf.train.AdamOptimizer(lr).apply_gradients + tf.train.ExponentialMovingAverage(decay, global_step).apply
+ * (src/deepSpeech_train.py:430, :457-465) for ALL tensors in one launch.  `table` is a device array of n_tensors rows
+ * of 7 int64: {w, g, m, v, shadow (0 = none) device pointers (fp32), numel, index of the tensor's first chunk}, chunks
+ * of ds2_adam_ema_chunk() elements numbered consecutively over the tensors (n_chunks in total).  lr is the decayed
+ * learning rate of this step (tf.train.exponential_decay, staircase, :231-250), step = 1 for the first update,
+ * ema_decay = min(decay, (1+n)/(10+n)) as TF computes it; the shadow follows the UPDATED weight; g is scaled by
+ * grad_scale first. */
+int ds2_adam_ema_chunk(void);
+int ds2_adam_ema_step(const void* table, int n_tensors, int n_chunks, float lr, float beta1, float beta2, float eps, long step,
+                      float ema_decay, float grad_scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -406,3 +406,34 @@ def dummy_batch(rng: np.random.Generator, batch_size: int, bucket: int):
                 vals.append(int(label[c]))
     return feats, np.asarray(idx, dtype=np.int64).reshape(-1, 2), np.asarray(vals, dtype=np.int32), \
         np.asarray([batch_size, L], dtype=np.int64), np.full(batch_size, T, dtype=np.int32)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Optimizer step.  TF-internal semantics restated from memory (parity unpinned, like the rest):
+# tf.train.exponential_decay(staircase=True) at src/deepSpeech_train.py:231-250, tf.train.AdamOptimizer defaults
+# (beta1 0.9, beta2 0.999, epsilon 1e-8) at :430 / :457-458, tf.train.ExponentialMovingAverage(decay, num_updates) at
+# :461-462.  The reference groups the Adam update and the averaging without a control dependency (:465), so their
+# order is undefined there; the build fixes it as "update, then average" with num_updates = updates done so far
+# (the order of the CIFAR-10 multi-GPU tutorial this file derives from).
+def decayed_learning_rate(initial_lr, global_step, decay_steps, decay_factor):
+    """tf.train.exponential_decay(..., staircase=True): lr * factor ** floor(step / decay_steps)."""
+    return float(initial_lr) * float(decay_factor) ** (int(global_step) // int(decay_steps))
+
+
+def ema_decay(decay, num_updates):
+    """tf.train.ExponentialMovingAverage: min(decay, (1 + n) / (10 + n))."""
+    return min(float(decay), (1.0 + num_updates) / (10.0 + num_updates))
+
+
+def adam_ema_step_np(w, g, m, v, shadow, step, lr, decay, beta1=0.9, beta2=0.999, eps=1e-8, grad_scale=1.0):
+    """One update of one tensor in float64; step = 1 for the first update.  Returns (w, m, v, shadow)."""
+    w, g, m, v = (np.asarray(a, np.float64) for a in (w, g, m, v))
+    g = g * grad_scale
+    m = beta1 * m + (1.0 - beta1) * g
+    v = beta2 * v + (1.0 - beta2) * g * g
+    lr_t = lr * np.sqrt(1.0 - beta2 ** step) / (1.0 - beta1 ** step)
+    w = w - lr_t * m / (np.sqrt(v) + eps)
+    if shadow is not None:
+        shadow = np.asarray(shadow, np.float64)
+        shadow = shadow - (1.0 - ema_decay(decay, step)) * (shadow - w)
+    return w, m, v, shadow
