@@ -40,7 +40,7 @@ struct GruParams {
                                     // (multiple of 64), boxes per slice
   int z_base;                       // first (chunk, direction) pair of this launch: pair z = chunk * ND + d
   float scale;
-  int fenced;                   // see RnnPersistParams::fenced (ds2_rnn_persistent.cu)
+  int fenced, slab16;           // see RnnPersistParams (ds2_rnn_persistent.cu)
 };
 
 __device__ __forceinline__ uint32_t g_cluster_ctarank() {
@@ -308,7 +308,7 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) acc[g][i] = 0.f;
       if (step > 0) {
-        if (et == 0) mbar_arrive_expect_tx(slab_bar_a, 128 * NG * GBP * 4);
+        if (et == 0) mbar_arrive_expect_tx(slab_bar_a, p.slab16 ? 128 * NG * GBP * 2 : 128 * NG * GBP * 4);
         if (et == 0) {
           const unsigned int need = ctas_per_dir * (unsigned int)step;
           if (p.fenced) {
@@ -361,8 +361,20 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
           const uint32_t off = (((rank * UPC + row % UPC) * NG + g) * GBP) * 4;
           const uint32_t dst = g_map_to_rank(slab_local, to) + off;
           const uint32_t rbar = g_map_to_rank(slab_bar_local, to);
+          if (p.slab16) {
+            uint32_t h[8];
 #pragma unroll
-          for (int c = 0; c < 4; ++c) g_st_async_v4(dst + c * 16, rbar, r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
+            for (int c = 0; c < 8; ++c) {
+              __nv_bfloat162 t2 = __floats2bfloat162_rn(__uint_as_float(r[2 * c]), __uint_as_float(r[2 * c + 1]));
+              h[c] = *reinterpret_cast<uint32_t*>(&t2);
+            }
+            const uint32_t dst2 = g_map_to_rank(slab_local, to) + off / 2;
+            g_st_async_v4(dst2, rbar, h[0], h[1], h[2], h[3]);
+            g_st_async_v4(dst2 + 16, rbar, h[4], h[5], h[6], h[7]);
+          } else {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) g_st_async_v4(dst + c * 16, rbar, r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
+          }
         }
         tc_fence_before();
         mbar_wait(slab_bar_a, ph, 50);
@@ -371,8 +383,18 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
 #pragma unroll
           for (int g = 0; g < NG; ++g)
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-              acc[g][i] += jg < UPC / 4 ? lds_f32(slab_local + (((s * UPC + 4 * jg + i) * NG + g) * GBP + bl) * 4) : 0.f;
+            for (int i = 0; i < 4; ++i) {
+              if (jg < UPC / 4) {
+                const uint32_t e = ((s * UPC + 4 * jg + i) * NG + g) * GBP + bl;
+                if (p.slab16) {
+                  unsigned short hv;
+                  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(hv) : "r"(slab_local + e * 2) : "memory");
+                  acc[g][i] += __uint_as_float((uint32_t)hv << 16);
+                } else {
+                  acc[g][i] += lds_f32(slab_local + e * 4);
+                }
+              }
+            }
         ph ^= 1;
       }
       if (jvalid) {
@@ -552,6 +574,7 @@ int gru_fwd_persist(const float* wx, float scale, const void* u, const float* bw
   p.ctr = static_cast<unsigned int*>(ws);
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = scale;
   p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
+  p.slab16 = getenv("DS2_RNN_SLAB_F32") ? 0 : 1;
   if (!p.fenced) DS2_CUDA(cudaMemsetAsync(hs, DS2_FILL_BYTE, (size_t)ND * T * B * H * 2, st));
   return gru_launch<false>(ta, p, geo, st);
 }
@@ -582,6 +605,7 @@ int gru_bwd_persist(const float* dout, const void* u, const int* lens, const voi
   p.ctr = static_cast<unsigned int*>(ws);
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = 1.f;
   p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
+  p.slab16 = getenv("DS2_RNN_SLAB_F32") ? 0 : 1;
   if (!p.fenced) DS2_CUDA(cudaMemsetAsync(dgh, DS2_FILL_BYTE, (size_t)T * B * ND * 3 * H * 2, st));
   return gru_launch<true>(ta, p, geo, st);
 }

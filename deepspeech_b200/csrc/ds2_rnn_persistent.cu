@@ -51,6 +51,7 @@ struct RnnPersistParams {
   int tiles_m, ksl, nbox;  // M tiles per direction, K-slice length (multiple of 64), boxes per slice
   float scale, cap;
   int exp;                 // timing experiments (DS2_RNN_EXP, results are NOT valid when set)
+  int slab16;              // 1: partial sums cross the cluster as bf16 (default), 0: fp32 (DS2_RNN_SLAB_F32=1)
   int fenced;              // 1: release/acquire step counters (DS2_RNN_FENCED=1); 0: relaxed counters + self-validating
                            // rows (see common.cuh, `out` must have been filled with DS2_FILL_BYTE)
 };
@@ -270,7 +271,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
       }
       float acc[4] = {0.f, 0.f, 0.f, 0.f};
       if (step > 0) {
-        if (et == 0) mbar_arrive_expect_tx(slab_bar_a, KS * 32 * BP * 4);           // arm this step's slab barrier
+        if (et == 0) mbar_arrive_expect_tx(slab_bar_a, p.slab16 ? KS * 32 * BP * 2 : KS * 32 * BP * 4);   // arm this step's slab barrier
         // ---- loader: poll h_{t-1}[inst's utterances][this CTA's K slice] until written, stage into smem
         if (pr) p.prof[step * 16 + 8] = dev_clock();
         {
@@ -333,8 +334,35 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
           const uint32_t off = ((rank * 32 + lane) * BP) * 4;
           const uint32_t dst = map_to_rank(slab_local, (uint32_t)q) + off;
           const uint32_t rbar = map_to_rank(slab_bar_local, (uint32_t)q);
+          if (p.exp & 128) {
+            // experiment: the warp parks its 32 rows (2 KB) in local smem and ONE bulk copy carries them to the finisher
+            const uint32_t stg = smem_u32(sA) + (inst * 4 + (w_in - 1)) * 2048;
 #pragma unroll
-          for (int c = 0; c < 4; ++c) st_async_v4(dst + c * 16, rbar, r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
+            for (int c = 0; c < 4; ++c) sts_v4(stg + lane * 64 + c * 16, make_uint4(r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]));
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+              const uint32_t dblk = map_to_rank(slab_local, (uint32_t)q) + rank * 32 * BP * 4;
+              asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                           ::"r"(dblk), "r"(stg), "r"(2048), "r"(rbar) : "memory");
+            }
+          } else if (p.slab16) {
+            // The exchange is bound by the DSMEM store queue (4 st.async per thread: 690 clk to issue, 3.76 us/step);
+            // as bf16 it is 2 per thread (110 clk, 3.26 us/step).  The rounding adds ~10 % to the error the bf16
+            // storage of h makes anyway (tools/rnn_err.py: rms 1.65e-3 -> 1.83e-3 of the output scale).
+            uint32_t h[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              __nv_bfloat162 t2 = __floats2bfloat162_rn(__uint_as_float(r[2 * c]), __uint_as_float(r[2 * c + 1]));
+              h[c] = *reinterpret_cast<uint32_t*>(&t2);
+            }
+            const uint32_t dst2 = map_to_rank(slab_local, (uint32_t)q) + off / 2;
+            st_async_v4(dst2, rbar, h[0], h[1], h[2], h[3]);
+            st_async_v4(dst2 + 16, rbar, h[4], h[5], h[6], h[7]);
+          } else {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) st_async_v4(dst + c * 16, rbar, r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
+          }
         }
         if (pr) p.prof[step * 16 + 12] = dev_clock();
         // ---- epilogue part 2: wait for the KS slabs of this step, reduce
@@ -343,7 +371,17 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
 #pragma unroll
         for (int s = 0; s < KS; ++s) {
           const uint32_t sp = slab_local + ((s * 32 + 4 * jg) * BP + bl) * 4;
-          acc[0] += lds_f32(sp); acc[1] += lds_f32(sp + BP * 4); acc[2] += lds_f32(sp + 2 * BP * 4); acc[3] += lds_f32(sp + 3 * BP * 4);
+          if (p.slab16) {
+            const uint32_t sp2 = slab_local + ((s * 32 + 4 * jg) * BP + bl) * 2;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              unsigned short hv;
+              asm volatile("ld.shared.u16 %0, [%1];" : "=h"(hv) : "r"(sp2 + i * BP * 2) : "memory");
+              acc[i] += __uint_as_float((uint32_t)hv << 16);
+            }
+          } else {
+            acc[0] += lds_f32(sp); acc[1] += lds_f32(sp + BP * 4); acc[2] += lds_f32(sp + 2 * BP * 4); acc[3] += lds_f32(sp + 3 * BP * 4);
+          }
         }
         ph ^= 1;
       }
@@ -476,6 +514,7 @@ static int persist_common(RnnPersistParams& p, size_t* smem, int T, int B, int H
   p.ctr = static_cast<unsigned int*>(ws);
   p.exp = getenv("DS2_RNN_EXP") ? atoi(getenv("DS2_RNN_EXP")) : 0;
   p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
+  p.slab16 = (getenv("DS2_RNN_SLAB_F32") || (p.exp & 128)) ? 0 : 1;
   p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(static_cast<char*>(ws) + WS_CTR_BYTES) : nullptr;
   return DS2_OK;
 }
