@@ -78,6 +78,11 @@ __device__ __forceinline__ uint4 ld_relaxed_v4(const void* p) {
   asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ uint4 ld_cg_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
   unsigned int v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -296,7 +301,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
 #pragma unroll
           for (int m = 0; m < MAX_UNITS; ++m) {
             v[m] = make_uint4(0u, 0u, 0u, 0u);
-            if (goff[m] >= 0 && !(p.exp & 4)) v[m] = ld_relaxed_v4(rows + goff[m]);
+            if (goff[m] >= 0 && !(p.exp & 4)) v[m] = (p.exp & 256) ? ld_cg_v4(rows + goff[m]) : ld_relaxed_v4(rows + goff[m]);
           }
           if (pr) p.prof[step * 16 + 9] = dev_clock();
           if (!p.fenced && !(p.exp & 6)) {
