@@ -119,6 +119,96 @@ def test_recurrence_train_sh_shape_properties():
     assert torch.equal(hs_a[1], hs_b[0].flip(0)) and torch.equal(hs_a[0], hs_b[1].flip(0))
 
 
+def test_recurrence_long_utterance_stress():
+    """BASELINE config 4(ii): 1500 recurrent steps (60 s utterances) at B=32, H=1760 through the persistent kernel:
+    bit-identical on a second run (the fence-free exchange must not depend on timing) and consistent with the
+    fp32 per-step kernels on the same bf16-rounded weights."""
+    from deepspeech_b200 import ops
+    from deepspeech_b200._lib import DS2_BF16, DS2_F32, check, lib
+    T, B, H = 1500, 32, 1760
+    g = torch.Generator(device="cuda").manual_seed(9)
+    wx = torch.randn((T, B, 2 * H), device="cuda", generator=g) * 0.7
+    U = (torch.randn((2, H, H), device="cuda", generator=g) * (0.6 / H ** 0.5)).to(torch.bfloat16)
+    bias = torch.randn((2, H), device="cuda", generator=g) * 0.1
+    lens = torch.full((B,), T, dtype=torch.int32, device="cuda")
+    p, st = ops._p, ops._stream
+    wsb = lib.ds2_rnn_workspace_bytes(T, B, H, 2, DS2_BF16)
+    ws = torch.empty(wsb, dtype=torch.uint8, device="cuda")
+    outs = []
+    for _ in range(2):
+        hs = torch.empty((2, T, B, H), dtype=torch.bfloat16, device="cuda")
+        check(lib.ds2_rnn_relu_fwd(p(wx), 1.0, p(U), p(bias), p(lens), p(hs), DS2_BF16, T, B, H, 2, 2, 20.0, p(ws), wsb, st()), "fwd")
+        outs.append(hs)
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0], outs[1])
+    h = outs[0].float()
+    assert torch.isfinite(h).all() and h.min().item() >= 0.0 and h.max().item() <= 20.0
+    hs32 = torch.empty((2, T, B, H), dtype=torch.float32, device="cuda")
+    check(lib.ds2_rnn_relu_fwd(p(wx), 1.0, p(U.float()), p(bias), p(lens), p(hs32), DS2_F32, T, B, H, 2, 2, 20.0, None, 0, st()), "fwd32")
+    torch.cuda.synchronize()
+    assert torch.nn.functional.cosine_similarity(h.flatten(), hs32.flatten(), dim=0).item() > 0.9999
+    assert (h[:, -1] - hs32[:, -1]).abs().max().item() < 5e-2 * hs32.abs().max().item()
+
+
+def test_gru_config3_shape_properties():
+    """BASELINE config 3 shape (bi-GRU H=800, B=32, T2=366): persistent bf16 kernels against the fp32 per-step GRU
+    kernels on the same bf16-rounded weights, forward and backward, plus time-reversal symmetry of the two directions."""
+    from deepspeech_b200 import ops
+    from deepspeech_b200._lib import DS2_F32, check, lib
+    T, B, H = 366, 32, 800
+    assert lib.ds2_gru_persistent_supported(B, H, 2) == 1
+    g = torch.Generator(device="cuda").manual_seed(11)
+    wx = torch.randn((T, B, 6 * H), device="cuda", generator=g) * 0.7
+    U = (torch.randn((2, 3 * H, H), device="cuda", generator=g) * (0.8 / H ** 0.5)).to(torch.bfloat16)
+    bw = torch.randn((2, 3 * H), device="cuda", generator=g) * 0.1
+    bu = torch.randn((2, 3 * H), device="cuda", generator=g) * 0.1
+    lens_h = np.random.default_rng(2).integers(T // 3, T + 1, size=B).astype(np.int32)
+    lens_h[0] = T
+    lens = torch.from_numpy(lens_h).cuda()
+    p, st = ops._p, ops._stream
+    wsb = lib.ds2_gru_workspace_bytes(T, B, H, 2)
+    ws = torch.empty(wsb, dtype=torch.uint8, device="cuda")
+    hs = torch.empty((2, T, B, H), dtype=torch.bfloat16, device="cuda")
+    gates = torch.empty((2, T, B, 4 * H), dtype=torch.bfloat16, device="cuda")
+    check(lib.ds2_gru_persistent_fwd(p(wx), 1.0, p(U), p(bw), p(bu), p(lens), p(hs), p(gates), T, B, H, 2, 2, p(ws), wsb, st()), "fwd")
+    hs32 = torch.empty((2, T, B, H), dtype=torch.float32, device="cuda")
+    gates32 = torch.empty((2, T, B, 4 * H), dtype=torch.float32, device="cuda")
+    check(lib.ds2_gru_fwd(p(wx), 1.0, p(U.float()), p(bw), p(bu), p(lens), p(hs32), p(gates32), DS2_F32, T, B, H, 2, 2, st()), "fwd32")
+    torch.cuda.synchronize()
+    h = hs.float()
+    assert torch.isfinite(h).all() and h.abs().max().item() <= 1.0
+    for b in (0, 5, 31):
+        if lens_h[b] < T:
+            assert h[:, lens_h[b]:, b].abs().max().item() == 0.0
+    assert (h - hs32).abs().max().item() < 3e-2
+    assert torch.nn.functional.cosine_similarity(h.flatten(), hs32.flatten(), dim=0).item() > 0.9999
+    # backward on the SAME stored activations: bf16 kernel vs fp32 per-step kernels
+    dout = torch.randn((T, B, H), device="cuda", generator=g)
+    dgi = torch.empty((T, B, 6 * H), dtype=torch.bfloat16, device="cuda")
+    dgh = torch.empty((T, B, 6 * H), dtype=torch.bfloat16, device="cuda")
+    check(lib.ds2_gru_persistent_bwd(p(dout), p(U), p(lens), p(hs), p(gates), p(dgi), p(dgh), T, B, H, 2, 2, p(ws), wsb, st()), "bwd")
+    dgi32 = torch.empty((T, B, 6 * H), dtype=torch.float32, device="cuda")
+    dgh32 = torch.empty((T, B, 6 * H), dtype=torch.float32, device="cuda")
+    dhz = torch.zeros((2, B, H), dtype=torch.float32, device="cuda")
+    check(lib.ds2_gru_bwd(p(dout), p(U.float()), p(lens), p(hs.float()), p(gates.float()), p(dgi32), p(dgh32), p(dhz), DS2_F32, T, B, H,
+                          2, 2, st()), "bwd32")
+    torch.cuda.synchronize()
+    for a, r in ((dgi, dgi32), (dgh, dgh32)):
+        assert torch.nn.functional.cosine_similarity(a.float().flatten(), r.flatten(), dim=0).item() > 0.999
+        assert (a.float() - r).abs().max().item() < 3e-2 * r.abs().max().item()
+    # time-reversal symmetry of the two directions (full lengths)
+    full = torch.full((B,), T, dtype=torch.int32, device="cuda")
+    wx_f = torch.cat([wx[:, :, 3 * H:], wx[:, :, :3 * H]], 2).flip(0).contiguous()
+    sw = lambda t: torch.stack([t[1], t[0]], 0).contiguous()
+    hs_a, hs_b = torch.empty_like(hs), torch.empty_like(hs)
+    check(lib.ds2_gru_persistent_fwd(p(wx), 1.0, p(U), p(bw), p(bu), p(full), p(hs_a), p(gates), T, B, H, 2, 2, p(ws), wsb, st()), "a")
+    U_f, bw_f, bu_f = sw(U), sw(bw), sw(bu)                  # keep them alive: the library only borrows the pointers
+    check(lib.ds2_gru_persistent_fwd(p(wx_f), 1.0, p(U_f), p(bw_f), p(bu_f), p(full), p(hs_b), p(gates), T, B, H, 2, 2, p(ws), wsb,
+                                     st()), "b")
+    torch.cuda.synchronize()
+    assert torch.equal(hs_a[1], hs_b[0].flip(0)) and torch.equal(hs_a[0], hs_b[1].flip(0))
+
+
 def test_full_train_sh_step_is_finite_and_native():
     from deepspeech_b200 import _lib, deepSpeech_NCHW as ds
     from deepspeech_b200.deepSpeech_dummy import DummyData
