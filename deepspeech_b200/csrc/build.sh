@@ -6,7 +6,7 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xcompiler -Wall --use_fast_math -Xptxas -v"
 mkdir -p build
 PIDS=()
-for f in ds2_api ds2_ctc ds2_generic ds2_rnn_generic ds2_gemm ds2_rnn_persistent ds2_gru_persistent ds2_conv_gemm ds2_conv_window ds2_optim; do
+for f in ds2_api ds2_ctc ds2_generic ds2_rnn_generic ds2_gemm ds2_rnn_persistent ds2_gru_persistent ds2_conv_gemm ds2_conv_window ds2_optim ds2_decode; do
   if [ ! -f build/$f.o ] || [ $f.cu -nt build/$f.o ] || [ common.cuh -nt build/$f.o ] || [ ../../include/ds2_b200.h -nt build/$f.o ]; then
     ( $NVCC $FLAGS -c $f.cu -o build/$f.o > build/$f.log 2>&1 || { cat build/$f.log; exit 1; } ) &
     PIDS+=($!)

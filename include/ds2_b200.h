@@ -212,6 +212,17 @@ int ds2_adam_ema_chunk(void);
 int ds2_adam_ema_step(const void* table, int n_tensors, int n_chunks, float lr, float beta1, float beta2, float eps, long step,
                       float ema_decay, float grad_scale, void* stream);
 
+/* ---- evaluation-side consumers of the logits ----------------------------------
+ * ds2_ctc_greedy_decode: tf.nn.ctc_greedy_decoder(log_softmax(logits), seq_lens) as used at
+ *   src/deepSpeech_test.py:209-213: per-frame argmax over K <= 32 classes (lowest index on ties), runs collapsed,
+ *   blank = K-1 removed.  logits f32 [T,B,K]; decoded int32 [B,T] (row b holds decoded_lens[b] class ids).
+ * ds2_edit_distance: Levenshtein distance of n pairs of int32 sequences (rows of a [n,lda] / b [n,ldb] with lengths
+ *   a_lens / b_lens <= maxlen <= 4000): the numerator of the character error rate, src/deepSpeech_test.py:126-130. */
+int ds2_ctc_greedy_decode(const float* logits, int T, int B, int K, const int* seq_lens, int* decoded, int* decoded_lens,
+                          void* stream);
+int ds2_edit_distance(const int* a, int lda, const int* a_lens, const int* b, int ldb, const int* b_lens, int n, int maxlen, int* out,
+                      void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -437,3 +437,43 @@ def adam_ema_step_np(w, g, m, v, shadow, step, lr, decay, beta1=0.9, beta2=0.999
         shadow = np.asarray(shadow, np.float64)
         shadow = shadow - (1.0 - ema_decay(decay, step)) * (shadow - w)
     return w, m, v, shadow
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Evaluation side: greedy CTC decoding and character error rate, src/deepSpeech_test.py:112-136,
+# :209-213.  tf.nn.ctc_greedy_decoder (TF-internal, from memory): per-frame argmax (first maximum), merge_repeated=True
+# collapses runs, the blank (K-1) is dropped; Levenshtein.distance is the unit-cost edit distance.
+ALPHABET = "ABCDEFGHIJKLMNOPQRSTUVWXYZ' "      # src/deepSpeech_test.py:28
+
+
+def ctc_greedy_decode_np(logits, seq_lens):
+    """logits [T,B,K] -> list of B lists of class ids."""
+    logits = np.asarray(logits)
+    T, B, K = logits.shape
+    out = []
+    for b in range(B):
+        prev, seq = -1, []
+        for t in range(min(int(seq_lens[b]), T)):
+            c = int(np.argmax(logits[t, b]))
+            if c != prev and c != K - 1:
+                seq.append(c)
+            prev = c
+        out.append(seq)
+    return out
+
+
+def edit_distance_py(a, b):
+    """Levenshtein distance (unit costs) of two sequences."""
+    la, lb = len(a), len(b)
+    row = list(range(lb + 1))
+    for i in range(1, la + 1):
+        prev_diag, row[0] = row[0], i
+        for j in range(1, lb + 1):
+            cur = min(row[j] + 1, row[j - 1] + 1, prev_diag + (a[i - 1] != b[j - 1]))
+            prev_diag, row[j] = row[j], cur
+    return row[lb]
+
+
+def char_error_rates(label_seqs, pred_seqs):
+    """distance(label, pred) / len(label) per utterance, src/deepSpeech_test.py:129-130."""
+    return [edit_distance_py(l, p) / len(l) for l, p in zip(label_seqs, pred_seqs)]
