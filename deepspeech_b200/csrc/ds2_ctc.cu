@@ -183,8 +183,8 @@ int ctc_launch(const float* logits, int T, int B, int K, const int* labels, int 
               workspace_bytes, need);
   DS2_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, DS2_ERR_BAD_ARG, "ds2_ctc: workspace must be 256-byte aligned");
   const int Smax = 2 * Lmax + 1;
-  // states per thread: 2 gives every thread two independent log-sum-exp chains (the loop is latency bound)
-  // and halves the number of warps at the per-step barrier
+  // states per thread: 1 measured fastest (one thread per lattice state keeps the per-step chain shortest; 2 and 4
+  // halve / quarter the warps at the barrier but lengthen the serial work of a step); DS2_CTC_NS overrides for tuning
   int ns_pref = 1;
   if (const char* e = getenv("DS2_CTC_NS")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) ns_pref = v; }
   int threads = (((Smax + ns_pref - 1) / ns_pref + 31) / 32) * 32;

@@ -171,9 +171,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           const bool full = nbase + 32 <= p.N;
           if (p.splits > 1) {
             float* crow = static_cast<float*>(p.C) + (long)row * p.ldc + nbase;
+            if (full && ((reinterpret_cast<uintptr_t>(crow) & 15) == 0)) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (nbase + j < p.N) atomicAdd(crow + j, v[j]);
+              for (int j = 0; j < 32; j += 4)      // one 16-byte reduction instead of four scalar ones
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(crow + j), "f"(v[j]), "f"(v[j + 1]), "f"(v[j + 2]),
+                             "f"(v[j + 3]) : "memory");
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (nbase + j < p.N) atomicAdd(crow + j, v[j]);
+            }
           } else if (p.c_bf16) {
             __nv_bfloat16* crow = static_cast<__nv_bfloat16*>(p.C) + (long)row * p.ldc + nbase;
             if (p.beta != 0.f) {
@@ -398,9 +405,16 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           const bool full = nbase + 32 <= p.N;
           if (p.splits > 1) {
             float* crow = static_cast<float*>(p.C) + (long)row * p.ldc + nbase;
+            if (full && ((reinterpret_cast<uintptr_t>(crow) & 15) == 0)) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (nbase + j < p.N) atomicAdd(crow + j, v[j]);
+              for (int j = 0; j < 32; j += 4)      // one 16-byte reduction instead of four scalar ones
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(crow + j), "f"(v[j]), "f"(v[j + 1]), "f"(v[j + 2]),
+                             "f"(v[j + 3]) : "memory");
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (nbase + j < p.N) atomicAdd(crow + j, v[j]);
+            }
           } else if (p.c_bf16) {
             __nv_bfloat16* crow = static_cast<__nv_bfloat16*>(p.C) + (long)row * p.ldc + nbase;
             if (p.beta != 0.f) {
@@ -573,19 +587,24 @@ extern "C" int ds2_gemm_bf16(const void* A, long lda, int a_mn_major, const void
 extern "C" int ds2_gemm_bf16_splitk(const void* A, long lda, int a_mn_major, const void* B, long ldb, int b_mn_major, float* C,
                                     long ldc, int M, int N, int K, float alpha, const float* bias, int splits, void* stream) {
   if (splits <= 0) {
-    // auto: split K only when the output has too few tiles to occupy half the SMs (the red.add epilogue and the
-    // zero-fill cost more than a partially filled last wave: measured on dW [3520x2400] / dU [1760x1760]);
-    // then use as many splits as fit the SMs, each keeping at least 8 K-blocks.
+    // auto: the split count that minimises tile waves per unit of K, ceil(tiles*s / units) / s, a "unit" being what runs
+    // one tile at a time (an SM, or a CTA pair for the 256x256 tiles).  dU [1760x1760] has 49 pair tiles for 74 pairs
+    // (one wave at 66 %); three K splits make it two full waves of a third of K each.  A split keeps >= 8 K-blocks and
+    // pays for the red.add epilogue and the zero fill: taken only for a gain of DS2_GEMM_SPLIT_GAIN percent (default 10).
     const int bn = (N <= 32) ? 32 : (N <= 128 ? 128 : 256);
-    const int tiles = ((M + ds2::BM - 1) / ds2::BM) * ((N + bn - 1) / bn);
-    const int sms = ds2::num_sms();
+    const bool pair = bn == 256 && M > 128 && getenv("DS2_GEMM_NO_PAIR") == nullptr;
+    const int tiles = pair ? ((M + 255) / 256) * ((N + 255) / 256) : ((M + ds2::BM - 1) / ds2::BM) * ((N + bn - 1) / bn);
+    const int units = pair ? ds2::num_sms() / 2 : ds2::num_sms();
     const int num_kb = (K + ds2::BK - 1) / ds2::BK;
+    static const double gain = getenv("DS2_GEMM_SPLIT_GAIN") ? atof(getenv("DS2_GEMM_SPLIT_GAIN")) / 100.0 : 0.10;
     splits = 1;
-    if (tiles * 2 <= sms) {
-      splits = sms / tiles;
-      if (splits > 32) splits = 32;
-      if (splits > num_kb / 8) splits = num_kb / 8;
-      if (splits < 1) splits = 1;
+    double best = (double)((tiles + units - 1) / units);
+    for (int sp = 2; sp <= 32 && num_kb / sp >= 8; ++sp) {
+      const double cost = (double)(((long)tiles * sp + units - 1) / units) / sp;
+      if (cost < best * (1.0 - gain)) {
+        best = cost;
+        splits = sp;
+      }
     }
   }
   return ds2::gemm_bf16_launch(A, lda, a_mn_major, B, ldb, b_mn_major, C, DS2_F32, ldc, M, N, K, alpha, 0.f, bias, splits,
