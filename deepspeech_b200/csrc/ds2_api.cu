@@ -49,7 +49,7 @@ int rnn_relu_bwd_generic(const float* dout, const float* u, const int* lens, con
                          int ND, int reverse_mask, float cap, cudaStream_t st);
 int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, int T, int B,
                          int H, int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st);
-int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, const void* hs, void* dz, int T, int B, int H, int ND,
+int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, const void* hs, void* dz, float* dbias, int T, int B, int H, int ND,
                          int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st);
 size_t rnn_persist_workspace_bytes(int T, int B, int H, int ND);
 int rnn_persist_supported(int B, int H, int ND);
@@ -84,19 +84,22 @@ extern "C" int ds2_rnn_relu_fwd(const float* wx, float scale, const void* u, con
   return rnn_relu_fwd_persist(wx, scale, u, bias, lens, hs, T, B, H, ND, reverse_mask, cap, workspace, workspace_bytes, st);
 }
 
-extern "C" int ds2_rnn_relu_bwd(const float* dout, const void* u, const int* lens, const void* hs, void* dz, int dtype, int T,
-                                int B, int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes,
-                                void* stream) {
+extern "C" int ds2_rnn_relu_bwd(const float* dout, const void* u, const int* lens, const void* hs, void* dz, float* dbias,
+                                int dtype, int T, int B, int H, int ND, int reverse_mask, float cap, void* workspace,
+                                size_t workspace_bytes, void* stream) {
   int rc = rnn_check(dout, u, hs, dz, T, B, H, ND, dtype);
   if (rc) return rc;
   DS2_REQUIRE(lens, DS2_ERR_BAD_ARG, "ds2_rnn_relu_bwd: lens is null");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (dtype == DS2_F32)
-    return rnn_relu_bwd_generic(dout, static_cast<const float*>(u), lens, static_cast<const float*>(hs), static_cast<float*>(dz),
-                                T, B, H, ND, reverse_mask, cap, st);
+  if (dtype == DS2_F32) {
+    rc = rnn_relu_bwd_generic(dout, static_cast<const float*>(u), lens, static_cast<const float*>(hs), static_cast<float*>(dz),
+                              T, B, H, ND, reverse_mask, cap, st);
+    if (rc || !dbias) return rc;
+    return ds2_colsum(dz, DS2_F32, (long)T * B, ND * H, (long)ND * H, dbias, 0, stream);
+  }
   DS2_REQUIRE(rnn_persist_supported(B, H, ND), DS2_ERR_UNSUPPORTED,
               "ds2_rnn_relu_bwd: persistent bf16 kernel does not take B=%d H=%d ND=%d (use DS2_F32)", B, H, ND);
-  return rnn_relu_bwd_persist(dout, u, lens, hs, dz, T, B, H, ND, reverse_mask, cap, workspace, workspace_bytes, st);
+  return rnn_relu_bwd_persist(dout, u, lens, hs, dz, dbias, T, B, H, ND, reverse_mask, cap, workspace, workspace_bytes, st);
 }
 
 extern "C" size_t ds2_rnn_workspace_bytes(int T, int B, int H, int ND, int dtype) {

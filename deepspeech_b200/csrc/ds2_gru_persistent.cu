@@ -34,6 +34,8 @@ struct GruParams {
   __nv_bfloat16* gates;         // [ND,T,B,4H]  fwd: out ; bwd: in   (r | z | n | U_n h + bu_n)
   __nv_bfloat16* dgi;           // bwd out [T,B,ND*3H]
   __nv_bfloat16* dgh;           // bwd out [T,B,ND*3H] (and moving operand)
+  float* dbw;                   // bwd, optional: [ND,3H] receives sum_{t,b} dgi (zero-filled by the host side)
+  float* dbu;                   // bwd, optional: [ND,3H] receives sum_{t,b} dgh
   unsigned int* ctr;            // [NC][ND][NI] step counters, 32 uints apart
   int T, B, H, ND, reverse_mask;
   int NC, NI, tiles_m, ksl, nbox;   // batch chunks, instances per chunk, M tiles per direction, K-slice length
@@ -280,6 +282,7 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
     }
     // forward: h_{t-1} of this thread's (b, units); backward: dh_{t+1} * z_{t+1}, the direct path of dh
     float carry[4] = {0.f, 0.f, 0.f, 0.f};
+    float sdr[4] = {0.f, 0.f, 0.f, 0.f}, sdz[4] = {0.f, 0.f, 0.f, 0.f}, sdn[4] = {0.f, 0.f, 0.f, 0.f}, sdnr[4] = {0.f, 0.f, 0.f, 0.f};
     uint32_t ph = 0;
     for (int step = 0; step < T; ++step) {
       const int t = BWD ? (rev ? step : T - 1 - step) : (rev ? T - 1 - step : step);
@@ -441,6 +444,7 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
             dr[i] = dn[i] * gh4[i] * r4[i] * (1.f - r4[i]);
             dnr[i] = dn[i] * r4[i];
             carry[i] = dh * z4[i];
+            sdr[i] += dr[i]; sdz[i] += dz[i]; sdn[i] += dn[i]; sdnr[i] += dnr[i];
           }
           __nv_bfloat16* gip = p.dgi + ((size_t)t * Bn + b) * ND * 3 * H + (size_t)d * 3 * H + j;
           __nv_bfloat16* ghp = p.dgh + ((size_t)t * Bn + b) * ND * 3 * H + (size_t)d * 3 * H + j;
@@ -456,6 +460,29 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
       if (et == 0) {
         if (p.fenced) g_red_release_add(ctr, 1u);
         else red_relaxed_gpu_add(ctr, 1u);
+      }
+    }
+    if (BWD && p.dbw != nullptr) {
+      // bias gradients: sum over the instance's 16 utterances (16 consecutive lanes share a unit quad), one red per unit
+      // dbw = sum (dr, dz, dn), dbu = sum (dr, dz, dn*r)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+          sdr[i] += __shfl_xor_sync(0xffffffffu, sdr[i], o);
+          sdz[i] += __shfl_xor_sync(0xffffffffu, sdz[i], o);
+          sdn[i] += __shfl_xor_sync(0xffffffffu, sdn[i], o);
+          sdnr[i] += __shfl_xor_sync(0xffffffffu, sdnr[i], o);
+        }
+      }
+      if (bl == 0 && jvalid) {
+        float* w = p.dbw + (size_t)d * 3 * H + j;
+        float* u = p.dbu + (size_t)d * 3 * H + j;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          atomicAdd(w + i, sdr[i]); atomicAdd(w + H + i, sdz[i]); atomicAdd(w + 2 * (size_t)H + i, sdn[i]);
+          atomicAdd(u + i, sdr[i]); atomicAdd(u + H + i, sdz[i]); atomicAdd(u + 2 * (size_t)H + i, sdnr[i]);
+        }
       }
     }
   }
@@ -580,7 +607,7 @@ int gru_fwd_persist(const float* wx, float scale, const void* u, const float* bw
 }
 
 int gru_bwd_persist(const float* dout, const void* u, const int* lens, const void* hs, const void* gates, void* dgi, void* dgh,
-                    int T, int B, int H, int ND, int reverse_mask, void* ws, size_t ws_bytes, cudaStream_t st) {
+                    float* dbw, float* dbu, int T, int B, int H, int ND, int reverse_mask, void* ws, size_t ws_bytes, cudaStream_t st) {
   GruParams p = {};
   GruGeom geo;
   DS2_REQUIRE(gru_geometry(true, B, H, ND, &geo), DS2_ERR_UNSUPPORTED,
@@ -602,6 +629,11 @@ int gru_bwd_persist(const float* dout, const void* u, const int* lens, const voi
   p.hs = const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(hs));
   p.gates = const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(gates));
   p.dgi = static_cast<__nv_bfloat16*>(dgi); p.dgh = static_cast<__nv_bfloat16*>(dgh);
+  p.dbw = (dbw && dbu) ? dbw : nullptr; p.dbu = dbu;
+  if (p.dbw) {
+    DS2_CUDA(cudaMemsetAsync(dbw, 0, (size_t)ND * 3 * H * sizeof(float), st));
+    DS2_CUDA(cudaMemsetAsync(dbu, 0, (size_t)ND * 3 * H * sizeof(float), st));
+  }
   p.ctr = static_cast<unsigned int*>(ws);
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = 1.f;
   p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
@@ -628,10 +660,10 @@ extern "C" int ds2_gru_persistent_fwd(const float* wx, float scale, const void* 
 }
 
 extern "C" int ds2_gru_persistent_bwd(const float* dout, const void* u, const int* lens, const void* hs, const void* gates, void* dgi,
-                                      void* dgh, int T, int B, int H, int ND, int reverse_mask, void* workspace,
-                                      size_t workspace_bytes, void* stream) {
+                                      void* dgh, float* dbw, float* dbu, int T, int B, int H, int ND, int reverse_mask,
+                                      void* workspace, size_t workspace_bytes, void* stream) {
   DS2_REQUIRE(dout && u && lens && hs && gates && dgi && dgh, DS2_ERR_BAD_ARG, "ds2_gru_persistent_bwd: null pointer");
   DS2_REQUIRE(T > 0 && B > 0 && H > 0 && (ND == 1 || ND == 2), DS2_ERR_BAD_SHAPE, "ds2_gru_persistent_bwd: bad shape");
-  return gru_bwd_persist(dout, u, lens, hs, gates, dgi, dgh, T, B, H, ND, reverse_mask, workspace, workspace_bytes,
+  return gru_bwd_persist(dout, u, lens, hs, gates, dgi, dgh, dbw, dbu, T, B, H, ND, reverse_mask, workspace, workspace_bytes,
                          static_cast<cudaStream_t>(stream));
 }

@@ -41,6 +41,7 @@ struct RnnPersistParams {
   const float* bias;       // fwd: [ND,H]
   const int* lens;         // [B]
   const __nv_bfloat16* hs_in;   // bwd: hs [ND,T,B,H] (activation mask)
+  float* dbias;            // bwd, optional: [ND,H] receives sum_t,b dz (zero-filled by the host side)
   __nv_bfloat16* out;      // fwd: hs [ND,T,B,H] ; bwd: dz [T,B,ND*H]   (also the moving operand of the next step)
   unsigned int* ctr;       // [ND][NI] step counters, 32 uints apart
   long long* prof;         // optional per-step clock64 stamps of CTA (0,0,0) instance 0 (DS2_RNN_PROF=1), 16 per step
@@ -260,6 +261,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
     }
     if ((p.exp & 16) && (inst & 1)) { __nanosleep(900); __nanosleep(900); }
     if ((p.exp & 32) && d == 1) __nanosleep(900);
+    float dbs[4] = {0.f, 0.f, 0.f, 0.f};         // backward: running sum over time of this thread's dz (bias gradient)
     uint32_t ph = 0;
     for (int step = 0; step < T; ++step) {
       const int t = BWD ? (rev ? step : T - 1 - step) : (rev ? T - 1 - step : step);
@@ -406,6 +408,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
           for (int i = 0; i < 4; ++i) {
             const float h = __bfloat162float(hb[i]);
             o[i] = (live && h > 0.f && h < p.cap) ? (av[i] + acc[i]) : 0.f;
+            dbs[i] += o[i];
           }
         }
         uint2 pk;
@@ -424,6 +427,18 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
         else red_relaxed_gpu_add(ctr, 1u);
       }
       if (pr) p.prof[step * 16 + 7] = dev_clock();
+    }
+    if (BWD && p.dbias != nullptr) {
+      // bias gradient: sum over the instance's 16 utterances (16 consecutive lanes share a unit quad), one red per unit
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) dbs[i] += __shfl_xor_sync(0xffffffffu, dbs[i], o);
+      }
+      if (bl == 0 && jvalid) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) atomicAdd(p.dbias + (size_t)d * H + j + i, dbs[i]);
+      }
     }
   }
   // no CTA may exit while a peer can still write into its shared memory
@@ -542,8 +557,8 @@ int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const floa
 
 // The backward contraction is U^T dz: U is transposed per direction into the workspace first
 // (ut[d][k][j] = U[d][j][k], 2*ND*H*H bytes, one small kernel per direction), then used as the resident A operand.
-int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, const void* hs, void* dz, int T, int B, int H, int ND,
-                         int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
+int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, const void* hs, void* dz, float* dbias, int T, int B, int H,
+                         int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
   RnnPersistParams p = {};
   size_t smem;
   int rc = persist_common(p, &smem, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_bwd", st);
@@ -557,6 +572,8 @@ int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, cons
   rc = make_tmap_2d_bf16(&ta, ut, H, (uint64_t)ND * H, H, 64, 128);
   if (rc) return rc;
   p.add_in = dout; p.bias = nullptr; p.lens = lens; p.hs_in = static_cast<const __nv_bfloat16*>(hs);
+  p.dbias = dbias;
+  if (dbias) DS2_CUDA(cudaMemsetAsync(dbias, 0, (size_t)ND * H * sizeof(float), st));
   p.out = static_cast<__nv_bfloat16*>(dz);
   p.out_row_pitch = (long)ND * H; p.out_dir_stride = H;
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = 1.f; p.cap = cap;

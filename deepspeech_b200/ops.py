@@ -445,9 +445,9 @@ class _BiRNNLayerFn(torch.autograd.Function):
         dz = torch.empty((T * B, ND * H), dtype=cdt, device=dev)
         wsb = lib.ds2_rnn_workspace_bytes(T, B, H, ND, _dt(hs))
         ws = _workspace(wsb, dev, "rnn") if wsb else None
-        check(lib.ds2_rnn_relu_bwd(_p(dout), _p(Ug), _p(lens), _p(hs), _p(dz), _dt(hs), T, B, H, ND, reverse_mask,
+        db = torch.empty((ND, H), dtype=torch.float32, device=dev)
+        check(lib.ds2_rnn_relu_bwd(_p(dout), _p(Ug), _p(lens), _p(hs), _p(dz), _p(db), _dt(hs), T, B, H, ND, reverse_mask,
                                    RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_bwd")
-        db = colsum(dz, T * B, ND * H, ND * H).view(ND, H)
         # dW = scale * dz^T x ; dx = scale * dz W   (both directions in one GEMM each)
         dW = torch.empty((ND * H, I), dtype=torch.float32, device=dev)
         gemm_wgrad(dz, xg.view(T * B, I), ND * H, I, T * B, ND * H, I, dW, alpha=SBN_SCALE)    # [ND*H, I]
@@ -525,14 +525,17 @@ class _BiGRULayerFn(torch.autograd.Function):
         if cdt == torch.bfloat16:
             wsb = lib.ds2_gru_workspace_bytes(T, B, H, ND)
             ws = _workspace(wsb, dev, "gru")
-            check(lib.ds2_gru_persistent_bwd(_p(dout), _p(Ug), _p(lens), _p(hs), _p(gates), _p(dgi), _p(dgh), T, B, H, ND,
-                                             reverse_mask, _p(ws), wsb, _stream()), "ds2_gru_persistent_bwd")
+            dbw = torch.empty((ND, 3 * H), dtype=torch.float32, device=dev)
+            dbu = torch.empty((ND, 3 * H), dtype=torch.float32, device=dev)
+            check(lib.ds2_gru_persistent_bwd(_p(dout), _p(Ug), _p(lens), _p(hs), _p(gates), _p(dgi), _p(dgh), _p(dbw), _p(dbu), T, B,
+                                             H, ND, reverse_mask, _p(ws), wsb, _stream()), "ds2_gru_persistent_bwd")
         else:
             dhz = torch.zeros((ND, B, H), dtype=torch.float32, device=dev)
             check(lib.ds2_gru_bwd(_p(dout), _p(Ug), _p(lens), _p(hs), _p(gates), _p(dgi), _p(dgh), _p(dhz), DS2_F32, T, B, H,
                                   ND, reverse_mask, _stream()), "ds2_gru_bwd")
-        dbw = colsum(dgi, T * B, G, G).view(ND, 3 * H)
-        dbu = colsum(dgh, T * B, G, G).view(ND, 3 * H)
+        if cdt != torch.bfloat16:
+            dbw = colsum(dgi, T * B, G, G).view(ND, 3 * H)
+            dbu = colsum(dgh, T * B, G, G).view(ND, 3 * H)
         dW = torch.empty((G, I), dtype=torch.float32, device=dev)
         gemm_wgrad(dgi, xg.view(T * B, I), G, I, T * B, G, I, dW, alpha=SBN_SCALE)
         dx = None
@@ -563,6 +566,8 @@ def bigru_layer(x, Wcat, U, bw, bu, lens, reverse_mask: int, want_bf16: bool, ou
 # ------------------------------------------------------------------------------------ whole recurrent stack
 _aux_streams = {}
 OVERLAP_WGRAD = True          # weight-gradient GEMMs on a side stream next to the following layer's recurrence
+import os as _os
+FUSED_BIAS_GRAD = _os.environ.get("DS2_NO_FUSED_DB") is None   # bias gradients accumulated inside the backward recurrence
 STACK_TRACE = None            # set to a list to collect (tag, layer, start_event, end_event) of the stack backward
 
 
@@ -669,6 +674,8 @@ class _RecStackFn(torch.autograd.Function):
             #      scattered over the SMs, could keep some clusters from being placed
             dz = torch.empty((T * B, G), dtype=torch.bfloat16, device=dev)
             dgh = torch.empty((T * B, G), dtype=torch.bfloat16, device=dev) if gru else dz
+            db = torch.empty((ND, G // ND), dtype=torch.float32, device=dev)           # bias gradients come out of the kernel
+            dbu = torch.empty((ND, G // ND), dtype=torch.float32, device=dev) if gru else None
             keep += [dz, dgh, d_cur]
             if overlap:
                 rec.wait_stream(main)
@@ -681,12 +688,13 @@ class _RecStackFn(torch.autograd.Function):
                 if gru:
                     wsb = lib.ds2_gru_workspace_bytes(T, B, H, ND)
                     ws = _workspace(wsb, dev, "gru")
-                    check(lib.ds2_gru_persistent_bwd(_p(d_cur), _p(Ug), _p(lens), _p(hs), _p(gates), _p(dz), _p(dgh), T, B, H,
-                                                     ND, reverse_mask, _p(ws), wsb, _stream()), "ds2_gru_persistent_bwd")
+                    check(lib.ds2_gru_persistent_bwd(_p(d_cur), _p(Ug), _p(lens), _p(hs), _p(gates), _p(dz), _p(dgh), _p(db if FUSED_BIAS_GRAD else None),
+                                                     _p(dbu if FUSED_BIAS_GRAD else None), T,
+                                                     B, H, ND, reverse_mask, _p(ws), wsb, _stream()), "ds2_gru_persistent_bwd")
                 else:
                     wsb = lib.ds2_rnn_workspace_bytes(T, B, H, ND, DS2_BF16)
                     ws = _workspace(wsb, dev, "rnn")
-                    check(lib.ds2_rnn_relu_bwd(_p(d_cur), _p(Ug), _p(lens), _p(hs), _p(dz), DS2_BF16, T, B, H, ND,
+                    check(lib.ds2_rnn_relu_bwd(_p(d_cur), _p(Ug), _p(lens), _p(hs), _p(dz), _p(db if FUSED_BIAS_GRAD else None), DS2_BF16, T, B, H, ND,
                                                reverse_mask, RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_bwd")
                 if STACK_TRACE is not None:
                     ev1 = torch.cuda.Event(enable_timing=True)
@@ -721,10 +729,12 @@ class _RecStackFn(torch.autograd.Function):
                                    dU[d])
                     else:
                         dU[d].zero_()
-                db = colsum(dz, T * B, G, G).view(ND, GH)
+                if not FUSED_BIAS_GRAD:
+                    db = colsum(dz, T * B, G, G).view(ND, GH)
+                    dbu = colsum(dgh, T * B, G, G).view(ND, GH) if gru else None
                 outs = [dW, dU, db]
                 if gru:
-                    outs.append(colsum(dgh, T * B, G, G).view(ND, GH))
+                    outs.append(dbu)
                 if STACK_TRACE is not None:
                     ev3 = torch.cuda.Event(enable_timing=True)
                     ev3.record()

@@ -105,12 +105,13 @@ int ds2_gemm_generic(const void* A, int a_dtype, long sam, long sak, const void*
  * kernels, u/hs fp32; DS2_BF16 = persistent tcgen05 kernel, u/hs bf16 (see
  * ds2_rnn_relu_persistent_supported).
  * Backward: dout [T,B,H] f32 is the gradient w.r.t. sum_d hs[d]; dz [T,B,ND*H] (f32|bf16) receives
- * the gradient w.r.t. the pre-activation, from which the caller forms dW, dU, db, dx by GEMM. */
+ * the gradient w.r.t. the pre-activation, from which the caller forms dW, dU, dx by GEMM; dbias [ND,H] f32 (may be
+ * NULL) receives the bias gradient sum_{t,b} dz, accumulated inside the persistent kernel. */
 int ds2_rnn_relu_fwd(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, int dtype,
                      int T, int B, int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes,
                      void* stream);
-int ds2_rnn_relu_bwd(const float* dout, const void* u, const int* lens, const void* hs, void* dz, int dtype, int T, int B,
-                     int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes, void* stream);
+int ds2_rnn_relu_bwd(const float* dout, const void* u, const int* lens, const void* hs, void* dz, float* dbias, int dtype, int T,
+                     int B, int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes, void* stream);
 size_t ds2_rnn_workspace_bytes(int T, int B, int H, int ND, int dtype);
 int ds2_rnn_relu_persistent_supported(int B, int H, int ND);
 
@@ -125,15 +126,16 @@ int ds2_gru_bwd(const float* dout, const void* u, const int* lens, const void* h
  * are bf16, wx/dout/bw/bu fp32, same layouts as above.  ds2_gru_persistent_supported says whether (B,H,ND) fits
  * (B = 16 or a multiple of 32, H%8==0; H <= 1024 runs both directions in one launch, wider layers use an 8-CTA K split
  * and one launch per direction);
- * workspace = ds2_gru_workspace_bytes (step counters + U^T for the backward), the caller owns it. */
+ * workspace = ds2_gru_workspace_bytes (step counters + U^T for the backward), the caller owns it.  dbw / dbu [ND,3H] f32
+ * (both or neither, may be NULL) receive the bias gradients sum_{t,b} dgi and sum_{t,b} dgh. */
 int ds2_gru_persistent_supported(int B, int H, int ND);
 size_t ds2_gru_workspace_bytes(int T, int B, int H, int ND);
 int ds2_gru_persistent_fwd(const float* wx, float scale, const void* u, const float* bw, const float* bu, const int* lens,
                            void* hs, void* gates, int T, int B, int H, int ND, int reverse_mask, void* workspace,
                            size_t workspace_bytes, void* stream);
 int ds2_gru_persistent_bwd(const float* dout, const void* u, const int* lens, const void* hs, const void* gates, void* dgi,
-                           void* dgh, int T, int B, int H, int ND, int reverse_mask, void* workspace, size_t workspace_bytes,
-                           void* stream);
+                           void* dgh, float* dbw, float* dbu, int T, int B, int H, int ND, int reverse_mask, void* workspace,
+                           size_t workspace_bytes, void* stream);
 
 /* ---- conv front-end -------------------------------------------------------------------------
  * tf.nn.conv2d + bias_add at src/deepSpeech_NCHW.py:120-127,:142-151 (src/deepSpeech.py:120-126,

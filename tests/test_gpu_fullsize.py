@@ -186,13 +186,20 @@ def test_gru_config3_shape_properties():
     dout = torch.randn((T, B, H), device="cuda", generator=g)
     dgi = torch.empty((T, B, 6 * H), dtype=torch.bfloat16, device="cuda")
     dgh = torch.empty((T, B, 6 * H), dtype=torch.bfloat16, device="cuda")
-    check(lib.ds2_gru_persistent_bwd(p(dout), p(U), p(lens), p(hs), p(gates), p(dgi), p(dgh), T, B, H, 2, 2, p(ws), wsb, st()), "bwd")
+    dbw = torch.empty((2, 3 * H), device="cuda")
+    dbu = torch.empty((2, 3 * H), device="cuda")
+    check(lib.ds2_gru_persistent_bwd(p(dout), p(U), p(lens), p(hs), p(gates), p(dgi), p(dgh), p(dbw), p(dbu), T, B, H, 2, 2, p(ws), wsb,
+                                     st()), "bwd")
     dgi32 = torch.empty((T, B, 6 * H), dtype=torch.float32, device="cuda")
     dgh32 = torch.empty((T, B, 6 * H), dtype=torch.float32, device="cuda")
     dhz = torch.zeros((2, B, H), dtype=torch.float32, device="cuda")
     check(lib.ds2_gru_bwd(p(dout), p(U.float()), p(lens), p(hs.float()), p(gates.float()), p(dgi32), p(dgh32), p(dhz), DS2_F32, T, B, H,
                           2, 2, st()), "bwd32")
     torch.cuda.synchronize()
+    # the bias gradients accumulated inside the kernel = column sums of the fp32 per-step result
+    for got, ref in ((dbw, dgi32), (dbu, dgh32)):
+        want = ref.view(T * B, 2, 3 * H).sum(0)
+        assert (got - want).abs().max().item() < 2e-2 * want.abs().max().item()
     for a, r in ((dgi, dgi32), (dgh, dgh32)):
         assert torch.nn.functional.cosine_similarity(a.float().flatten(), r.flatten(), dim=0).item() > 0.999
         assert (a.float() - r).abs().max().item() < 3e-2 * r.abs().max().item()

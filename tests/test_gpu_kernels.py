@@ -449,10 +449,10 @@ def test_birnn_layer_bf16_persistent_vs_oracle(T, B, I, H, ragged):
     check(lib.ds2_rnn_relu_fwd(p(wx), ops.SBN_SCALE, p(Ub), p(Bv.detach()), p(lens_d), p(hs), DS2_BF16, T, B, H, 2, 2, 20.0, p(ws), wsb, st()), "fwd")
     dout = torch.tensor(rng.standard_normal((T, B, H)), dtype=torch.float32, device=dev)
     dz_b = torch.empty((T, B, 2 * H), dtype=torch.bfloat16, device=dev)
-    check(lib.ds2_rnn_relu_bwd(p(dout), p(Ub), p(lens_d), p(hs), p(dz_b), DS2_BF16, T, B, H, 2, 2, 20.0, p(ws), wsb, st()), "bwd")
+    check(lib.ds2_rnn_relu_bwd(p(dout), p(Ub), p(lens_d), p(hs), p(dz_b), None, DS2_BF16, T, B, H, 2, 2, 20.0, p(ws), wsb, st()), "bwd")
     hs32, U32 = hs.float(), Ub.float()
     dz_f = torch.empty((T, B, 2 * H), dtype=torch.float32, device=dev)
-    check(lib.ds2_rnn_relu_bwd(p(dout), p(U32), p(lens_d), p(hs32), p(dz_f), DS2_F32, T, B, H, 2, 2, 20.0, None, 0, st()), "bwd32")
+    check(lib.ds2_rnn_relu_bwd(p(dout), p(U32), p(lens_d), p(hs32), p(dz_f), None, DS2_F32, T, B, H, 2, 2, 20.0, None, 0, st()), "bwd32")
     torch.cuda.synchronize()
     assert relerr(dz_b.float().cpu().numpy(), dz_f.cpu().numpy()) < 2e-2
 
