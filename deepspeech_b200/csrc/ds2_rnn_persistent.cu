@@ -306,6 +306,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
             if (goff[m] >= 0 && !(p.exp & 4)) v[m] = (p.exp & 256) ? ld_cg_v4(rows + goff[m]) : ld_relaxed_v4(rows + goff[m]);
           }
           if (pr) p.prof[step * 16 + 9] = dev_clock();
+          int n_retry = 0;
           if (!p.fenced && !(p.exp & 6)) {
             // the counter was published without a fence: a row may still show the host's fill; reload until it landed
 #pragma unroll
@@ -315,6 +316,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
                 do {
                   v[m] = ld_relaxed_v4(rows + goff[m]);
                   g.check(22);
+                  ++n_retry;
                 } while (unit_stale(v[m]));
               }
             }
@@ -322,7 +324,7 @@ rnn_persist_kernel(const __grid_constant__ CUtensorMap tm_a, RnnPersistParams p)
 #pragma unroll
           for (int m = 0; m < MAX_UNITS; ++m)
             if (soff[m] >= 0) sts_v4(sB_addr + soff[m], v[m]);
-          if (pr) p.prof[step * 16 + 13] = dev_clock();
+          if (pr) { p.prof[step * 16 + 13] = dev_clock(); p.prof[step * 16 + 2] = n_retry; }
           fence_proxy_async();       // generic-proxy smem writes -> visible to the tensor core (async proxy)
           if (pr) p.prof[step * 16 + 14] = dev_clock();
           mbar_arrive(b_ready_a);

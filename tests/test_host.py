@@ -42,6 +42,16 @@ def test_c_abi_argument_validation_without_gpu():
     assert rc == 1
     with pytest.raises(RuntimeError):
         _lib.check(4, "x")
+    # shape queries and host-only state of the newer entry points (no kernel is launched)
+    assert lib.ds2_rnn_relu_persistent_supported(32, 1760, 2) == 1 and lib.ds2_rnn_relu_persistent_supported(33, 1760, 2) == 0
+    assert lib.ds2_gru_persistent_supported(32, 800, 2) == 1 and lib.ds2_gru_persistent_supported(64, 1760, 2) == 1
+    assert lib.ds2_gru_persistent_supported(48, 800, 2) == 0            # more than one chunk only in whole chunks of 32
+    assert lib.ds2_conv_window_supported(32, 32, 79, 10, 5, 1) == 1 and lib.ds2_conv_window_supported(1, 32, 161, 20, 5, 2) == 0
+    assert lib.ds2_set_sm_limit(36) == 0 and lib.ds2_set_sm_limit(0) == 36 and lib.ds2_set_sm_limit(0) == 0
+    assert lib.ds2_adam_ema_chunk() > 0
+    assert lib.ds2_adam_ema_step(None, 1, 1, 1e-3, 0.9, 0.999, 1e-8, 1, 0.99, 1.0, None) == 1
+    assert lib.ds2_ctc_greedy_decode(None, 4, 1, 29, None, None, None, None) == 1
+    assert lib.ds2_conv_window_fwd(None, None, None, None, 1, 20, 20, 3, 3, 1, None) == 1
 
 
 def test_no_cpu_fallback():

@@ -47,3 +47,5 @@ for name, a, b in seq:
 g = (nxt[:, 8] - s[:, 7]).astype(np.float64)
 print("%-46s mean %8.1f cyc" % ("published -> next step's poll start", g.mean()))
 print("sum %.0f cycles per step" % (tot + g.mean()))
+r = s[:, 2].astype(np.float64)
+print("reloads of not-yet-visible rows by the stamping thread: mean %.2f per step, steps with any: %.0f %%" % (r.mean(), 100.0 * (r > 0).mean()))
