@@ -39,6 +39,25 @@ class GradAllReducer(object):
         self._seen = 0
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
         self.launched = 0
+        # The recurrent stack is one autograd node: its gradients reach the hooks only when the whole stack has been
+        # back-propagated.  It offers them layer by layer instead (ops.STACK_GRAD_HOOK); they are all-reduced right
+        # there; when autograd later installs its own copy as .grad, finish() overwrites that copy with the reduced
+        # tensor.  This relies on .grad being a fresh tensor of this backward pass, i.e. on gradients having been reset
+        # with zero_grad(set_to_none=True): accumulating into an older .grad would add the not-yet-reduced values.
+        self._early = {}            # id(parameter) -> (work handle, reduced tensor)
+        if self.world > 1:
+            from . import ops
+            ops.STACK_GRAD_HOOK = self._on_stack_layer
+
+    def _on_stack_layer(self, layer, tensors, params):
+        for t, p in zip(tensors, params):
+            if t is None:
+                continue
+            if p.grad is not None:
+                raise RuntimeError("GradAllReducer: reset gradients with zero_grad(set_to_none=True) before backward")
+            w = dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            self._early[id(p)] = (w, t)
+            self.launched += 1
 
     def _flush(self):
         if not self._bucket:
@@ -57,6 +76,10 @@ class GradAllReducer(object):
         if self.world == 1:
             return
         self._seen += 1
+        e = self._early.pop(id(p), None)
+        if e is not None:                       # already on its way (offered by the recurrent stack's backward)
+            self._pending.append((e[0], e[1], [p]))
+            return
         nbytes = p.grad.numel() * p.grad.element_size()
         if nbytes >= self.bucket_bytes:
             self._flush()
@@ -73,6 +96,9 @@ class GradAllReducer(object):
         if self.world == 1:
             return
         self._flush()
+        if self._early:
+            raise RuntimeError("GradAllReducer: %d gradients were all-reduced early for parameters this reducer does not own"
+                               % len(self._early))
         inv = 1.0 / self.world
         for w, flat, ps in self._pending:
             w.wait()
@@ -80,7 +106,8 @@ class GradAllReducer(object):
                 off = 0
                 for p in ps:
                     n = p.grad.numel()
-                    p.grad.copy_(flat[off:off + n].view_as(p.grad))
+                    if p.grad.data_ptr() != flat.data_ptr() or n != flat.numel():
+                        p.grad.copy_(flat[off:off + n].view_as(p.grad))
                     off += n
             for p in ps:
                 _scale_(p.grad, inv)
@@ -90,6 +117,9 @@ class GradAllReducer(object):
     def remove(self):
         for h in self._hooks:
             h.remove()
+        from . import ops
+        if ops.STACK_GRAD_HOOK == self._on_stack_layer:
+            ops.STACK_GRAD_HOOK = None
 
 
 def _scale_(t: torch.Tensor, s: float):

@@ -568,6 +568,8 @@ _aux_streams = {}
 OVERLAP_WGRAD = True          # weight-gradient GEMMs on a side stream next to the following layer's recurrence
 import os as _os
 FUSED_BIAS_GRAD = _os.environ.get("DS2_NO_FUSED_DB") is None   # bias gradients accumulated inside the backward recurrence
+STACK_GRAD_HOOK = None        # callable(layer, [gradient tensors], [their parameters]) run as soon as a layer's weight gradients are enqueued
+                              # (data-parallel reducers start their all-reduce here, see dp.GradAllReducer)
 STACK_TRACE = None            # set to a list to collect (tag, layer, start_event, end_event) of the stack backward
 
 
@@ -641,6 +643,7 @@ class _RecStackFn(torch.autograd.Function):
             cur = add2(hs[0], hs[1], odt) if ND == 2 else cast(hs[0], odt)
         ctx.save_for_backward(lens, *saved)
         ctx.meta = (T, B, gru, reverse_mask, L, metas, x.dtype)
+        ctx.param_objs = params                     # identities only: handed to STACK_GRAD_HOOK with their gradients
         return cur
 
     @staticmethod
@@ -735,6 +738,9 @@ class _RecStackFn(torch.autograd.Function):
                 outs = [dW, dU, db]
                 if gru:
                     outs.append(dbu)
+                if STACK_GRAD_HOOK is not None:
+                    # on the stream that produced them: the reducer orders itself after it
+                    STACK_GRAD_HOOK(l, outs, ctx.param_objs[l * npl:(l + 1) * npl])
                 if STACK_TRACE is not None:
                     ev3 = torch.cuda.Event(enable_timing=True)
                     ev3.record()

@@ -137,6 +137,80 @@ def _dp_worker(rank, world, port, q):
     dist.destroy_process_group()
 
 
+class _EarlyLinear(torch.autograd.Function):
+    """Stands in for the recurrent stack's autograd node: offers its weight gradient to ops.STACK_GRAD_HOOK from inside
+    backward, as deepspeech_b200.ops._RecStackFn does layer by layer."""
+
+    @staticmethod
+    def forward(ctx, x, W):
+        ctx.save_for_backward(x, W)
+        ctx.param_objs = (W,)
+        return x @ W.t()
+
+    @staticmethod
+    def backward(ctx, go):
+        from deepspeech_b200 import ops
+        x, W = ctx.saved_tensors
+        gW = go.t() @ x
+        if ops.STACK_GRAD_HOOK is not None:
+            ops.STACK_GRAD_HOOK(0, [gW], ctx.param_objs)
+        return go @ W, gW
+
+
+def _dp_early_worker(rank, world, port, q):
+    import torch.distributed as dist
+    from deepspeech_b200 import ops
+    from deepspeech_b200.dp import GradAllReducer, shard_batch
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    torch.manual_seed(0)
+    W1 = torch.nn.Parameter(torch.randn(8, 6, dtype=torch.float64))
+    lin2 = torch.nn.Linear(8, 3).double()
+    X = torch.randn(8, 6, dtype=torch.float64)
+    Y = torch.randn(8, 3, dtype=torch.float64)
+    params = [W1] + list(lin2.parameters())
+    fwd = lambda x: lin2(torch.relu(_EarlyLinear.apply(x, W1)))
+    red = GradAllReducer(params, bucket_bytes=200)
+    assert ops.STACK_GRAD_HOOK is not None
+    sl = shard_batch(8, rank, world)
+    errs = []
+    for it in range(2):                                      # twice: the reducer must be reusable step after step
+        for p in params:
+            p.grad = None
+        ((fwd(X[sl]) - Y[sl]) ** 2).mean().backward()
+        red.finish()
+        g_dp = torch.cat([p.grad.reshape(-1) for p in params])
+        for p in params:
+            p.grad = None
+        hook, ops.STACK_GRAD_HOOK = ops.STACK_GRAD_HOOK, None
+        ((fwd(X) - Y) ** 2).mean().backward()                # single-process global-batch gradient
+        ops.STACK_GRAD_HOOK = hook
+        g_ref = torch.cat([p.grad.reshape(-1) for p in params])
+        errs.append(float((g_dp - g_ref).abs().max()))
+    # gradients that were not reset: refused instead of silently double counting
+    refused = False
+    try:
+        ((fwd(X[sl]) - Y[sl]) ** 2).mean().backward()
+    except RuntimeError:
+        refused = True
+    red.remove()
+    q.put((rank, max(errs), refused and ops.STACK_GRAD_HOOK is None))
+    dist.destroy_process_group()
+
+
+def test_dp_early_allreduce_from_stack_hook_world2_gloo():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_dp_early_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(err < 1e-12 and ok for _, err, ok in res), res
+
+
 def test_dp_allreduce_world2_gloo():
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
