@@ -347,8 +347,8 @@ def extras(args, dev, model, ops, _lib, B, T2, H, L, peak_tf, peak_hbm, peak_src
                            else "recurrent forward kernel (T=%d steps, B=%d, H=%d, 2 directions)" % (T2, B, H),
                            "bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
                            # dram__bytes_read+write of one launch from the committed ncu --set full capture
-                           # (profiles/r1_rnn_persist_ncu.txt, same shape); algorithmic bytes 259.7 MB
-                           "traffic": None if dom_gemm else 238.6e6, "peak_source": peak_src,
+                           # (profiles/r1_rnn_persist_ncu_v6.txt, same shape); algorithmic bytes 259.7 MB
+                           "traffic": None if dom_gemm else 238.0e6, "peak_source": peak_src,
                            "note": "latency-bound T-step dependency chain (4 chains x 366 steps); see profiles/r1_rnn_stage_cycles_v5.txt"}
     total_flops, rnn_flops, _ = step_flops(B, args.frames, H, L, 32, args.cell)
     out["rnn_tflops_in_step"] = {"note": "all RNN-stack GEMM FLOPs (fwd+bwd) / whole step time (lower bound)",
