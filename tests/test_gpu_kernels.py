@@ -201,7 +201,8 @@ def test_conv_gemm_route_vs_fp64():
         assert abs(np.linalg.norm(got.grad.cpu().numpy()) / np.linalg.norm(ref.grad.numpy()) - 1) < 3e-2, name
 
 
-@pytest.mark.parametrize("B,Ti,Fi,KT,KF,st", [(2, 31, 79, 10, 5, 2), (1, 12, 9, 3, 2, 1), (3, 22, 128, 4, 7, 3), (2, 741, 79, 10, 5, 2)])
+@pytest.mark.parametrize("B,Ti,Fi,KT,KF,st", [(2, 31, 79, 10, 5, 2), (1, 12, 9, 3, 2, 1), (3, 22, 128, 4, 7, 3), (2, 741, 79, 10, 5, 2),
+                                              (1, 25, 40, 5, 3, 2), (2, 18, 30, 3, 4, 1), (1, 10, 16, 2, 1, 1), (1, 9, 8, 8, 8, 4)])
 def test_conv_window_kernels_vs_fp64(B, Ti, Fi, KT, KF, st):
     """Implicit-GEMM conv (forward, data gradient, weight gradient through the strided TMA window view) against an fp64
     convolution of the SAME bf16-rounded operands: only fp32 accumulation order differs (<= 1e-4 of the scale)."""
