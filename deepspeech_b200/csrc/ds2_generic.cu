@@ -451,7 +451,20 @@ bn_clip_fwd_rows_kernel(const float* __restrict__ x, int R, const float* __restr
     }
     __syncthreads();
     TO* orow = out + rnn_row(m, r);
-    for (int j = threadIdx.x; j < FC; j += blockDim.x) stf(orow + j, bn_row[j]);
+    if (sizeof(TO) == 2 && (FC & 7) == 0) {
+      // bf16 output: 8 values = one 16-byte store (rows are 16-byte aligned when FC % 8 == 0)
+      for (int j = threadIdx.x * 8; j < FC; j += blockDim.x * 8) {
+        const float4 a = *reinterpret_cast<const float4*>(bn_row + j), b = *reinterpret_cast<const float4*>(bn_row + j + 4);
+        __nv_bfloat162 p0 = __floats2bfloat162_rn(a.x, a.y), p1 = __floats2bfloat162_rn(a.z, a.w);
+        __nv_bfloat162 p2 = __floats2bfloat162_rn(b.x, b.y), p3 = __floats2bfloat162_rn(b.z, b.w);
+        uint4 pk;
+        pk.x = *reinterpret_cast<uint32_t*>(&p0); pk.y = *reinterpret_cast<uint32_t*>(&p1);
+        pk.z = *reinterpret_cast<uint32_t*>(&p2); pk.w = *reinterpret_cast<uint32_t*>(&p3);
+        *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(orow) + j) = pk;
+      }
+    } else {
+      for (int j = threadIdx.x; j < FC; j += blockDim.x) stf(orow + j, bn_row[j]);
+    }
     __syncthreads();
   }
 }
@@ -474,7 +487,19 @@ bn_clip_bwd_rows_kernel(const float* __restrict__ x, int R, const float* __restr
   float s1 = 0.f, s2 = 0.f;
   for (int r = blockIdx.x; r < R; r += gridDim.x) {
     const TG* drow = dout + rnn_row(m, r);
-    for (int j = threadIdx.x; j < FC; j += blockDim.x) bn_row[j] = ldf(drow + j);
+    if (sizeof(TG) == 2 && (FC & 7) == 0) {
+      for (int j = threadIdx.x * 8; j < FC; j += blockDim.x * 8) {
+        const uint4 pk = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(drow) + j);
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&pk);
+        *reinterpret_cast<float4*>(bn_row + j) = make_float4(__low2float(h[0]), __high2float(h[0]), __low2float(h[1]), __high2float(h[1]));
+        *reinterpret_cast<float4*>(bn_row + j + 4) = make_float4(__low2float(h[2]), __high2float(h[2]), __low2float(h[3]), __high2float(h[3]));
+      }
+    } else if (sizeof(TG) == 4 && (FC & 3) == 0) {
+      for (int j = threadIdx.x * 4; j < FC; j += blockDim.x * 4)
+        *reinterpret_cast<float4*>(bn_row + j) = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(drow) + j);
+    } else {
+      for (int j = threadIdx.x; j < FC; j += blockDim.x) bn_row[j] = ldf(drow + j);
+    }
     __syncthreads();
     const float* xr = x + (long)r * FC;
     for (int f = fl; f < m.F; f += fstep) {
