@@ -406,6 +406,10 @@ def extras(args, dev, model, ops, _lib, B, T2, H, L, peak_tf, peak_hbm, peak_src
                                "sample": "dummy bucket T=100 frames x B=%d (%.0f audio-s/step), 1 warm-up + 2 timed steps, fp32 torch-CPU "
                                          "port of the same step (reference TF path unavailable on this box)" % (B, B * 1.0),
                                "ms_per_step": ms}
+        if threads > 8:
+            # the reference's own setting: OMP_NUM_THREADS=8 / intra_op=8 (src/setenvs.py:22-23, src/deepSpeech_train.py:518-523)
+            val8, ms8, _ = cb.time_steps(B, 0, 2, 1, 8, H, L)
+            out["cpu_baseline"]["at_8_threads"] = {"value": val8, "ms_per_step": ms8}
     return out
 
 
