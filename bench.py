@@ -165,13 +165,18 @@ def main():
     reducer = GradAllReducer(model.parameters()) if world > 1 else None
     bucket = utt_lengths.index(T) if T in utt_lengths else None
     data = DummyData(B, seed=1234 + rank)
-    if bucket is None:                                       # non-bucket length (e.g. T2=1500 stress): reuse bucket-14 labels
-        raise SystemExit("--frames must be one of the dummy buckets %s" % utt_lengths)
+    stress_rng = np.random.default_rng(4321 + rank)          # non-bucket length (BASELINE config 4(ii): T2 = 1500 recurrent steps
+    if bucket is None and T < utt_lengths[-1]:               # = 6034 frames): standard-normal features, bucket-14 labels
+        raise SystemExit("--frames must be one of the dummy buckets %s or longer than the longest" % utt_lengths)
 
     pinned = [torch.empty((B, T, 161), dtype=torch.float32).pin_memory() for _ in range(2)]
     feats_dev = torch.empty((B, T, 161), dtype=torch.float32, device=dev)
 
     def host_batch(slot):
+        if bucket is None:
+            _, idx, vals, shape, _ = data.inputs(len(utt_lengths) - 1)
+            pinned[slot].copy_(torch.from_numpy(stress_rng.standard_normal((B, T, 161), dtype=np.float32)))
+            return (idx, vals, shape), np.full(B, T, dtype=np.int32)
         feats, idx, vals, shape, lens = data.inputs(bucket)
         pinned[slot].copy_(torch.from_numpy(feats))
         return (idx, vals, shape), lens
