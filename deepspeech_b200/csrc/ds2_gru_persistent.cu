@@ -37,12 +37,14 @@ struct GruParams {
   float* dbw;                   // bwd, optional: [ND,3H] receives sum_{t,b} dgi (zero-filled by the host side)
   float* dbu;                   // bwd, optional: [ND,3H] receives sum_{t,b} dgh
   unsigned int* ctr;            // [NC][ND][NI] step counters, 32 uints apart
+  long long* prof;              // optional (DS2_RNN_PROF=1): 8 clock stamps per step of CTA (0,0,0), instance 0, first loader thread
   int T, B, H, ND, reverse_mask;
   int NC, NI, tiles_m, ksl, nbox;   // batch chunks, instances per chunk, M tiles per direction, K-slice length
                                     // (multiple of 64), boxes per slice
   int z_base;                       // first (chunk, direction) pair of this launch: pair z = chunk * ND + d
   float scale;
   int fenced, slab16;           // see RnnPersistParams (ds2_rnn_persistent.cu)
+  int bulk;                     // forward: a warp parks its bf16 partial sums in smem and sends them with one bulk copy
 };
 
 __device__ __forceinline__ uint32_t g_cluster_ctarank() {
@@ -283,8 +285,10 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
     // forward: h_{t-1} of this thread's (b, units); backward: dh_{t+1} * z_{t+1}, the direct path of dh
     float carry[4] = {0.f, 0.f, 0.f, 0.f};
     float sdr[4] = {0.f, 0.f, 0.f, 0.f}, sdz[4] = {0.f, 0.f, 0.f, 0.f}, sdn[4] = {0.f, 0.f, 0.f, 0.f}, sdnr[4] = {0.f, 0.f, 0.f, 0.f};
+    const bool pr = p.prof != nullptr && blockIdx.x + blockIdx.y + blockIdx.z == 0 && inst == 0 && et == 0;
     uint32_t ph = 0;
     for (int step = 0; step < T; ++step) {
+      if (pr && step < 1024) p.prof[step * 8 + 0] = dev_clock();
       const int t = BWD ? (rev ? step : T - 1 - step) : (rev ? T - 1 - step : step);
       const int tsrc = BWD ? (rev ? t - 1 : t + 1) : (rev ? t + 1 : t - 1);      // producer of the moving operand
       const int tprev = rev ? t + 1 : t - 1;                                     // previous step in FORWARD order
@@ -293,6 +297,7 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
       float4 gi[3];
       float4 dout4 = make_float4(0.f, 0.f, 0.f, 0.f);
       uint2 g4[4];
+      uint2 hp2 = make_uint2(0u, 0u);             // backward: h of the previous step in forward order (zero before the first)
       if (jvalid) {
         if (!BWD) {
           const float* src = p.add_in + ((size_t)t * Bn + b) * ND * 3 * H + (size_t)d * 3 * H + j;
@@ -303,6 +308,7 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
           const __nv_bfloat16* gp = p.gates + (((size_t)d * T + t) * Bn + b) * 4 * H + j;
 #pragma unroll
           for (int g = 0; g < 4; ++g) g4[g] = *reinterpret_cast<const uint2*>(gp + (size_t)g * H);
+          if (has_prev) hp2 = *reinterpret_cast<const uint2*>(p.hs + (((size_t)d * T + tprev) * Bn + b) * H + j);
         }
       }
       float acc[NG][4];
@@ -325,6 +331,7 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
           }
         }
         asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
+        if (pr && step < 1024) p.prof[step * 8 + 1] = dev_clock();
         {
           const __nv_bfloat16* rows = src_dir + ((size_t)tsrc * Bn + chunk * GCHUNK + inst * GBP) * src_pitch;
           uint4 v[GMAX_UNITS];
@@ -352,9 +359,45 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
           fence_proxy_async();
           mbar_arrive(b_ready_a);
         }
+        if (pr && step < 1024) p.prof[step * 8 + 2] = dev_clock();
         mbar_wait(mma_bar_a, ph, 40);
         tc_fence_after();
+        if (pr && step < 1024) p.prof[step * 8 + 3] = dev_clock();
         // partial sums of this CTA's K slice -> the cluster CTA that finishes those units (all gates)
+        if (!BWD && p.slab16 && p.bulk) {
+          // Three gates are 6 st.async per thread: the DSMEM store queue backs up into the LSU (1700 clk to issue, and the
+          // epilogue's own loads and stores queue behind it).  Instead the warp writes its 32 rows x 3 gates x 16 bf16
+          // (3 KB, already in the slab's layout) to local shared memory and one thread sends them with a bulk copy per
+          // finishing CTA, completing on that CTA's slab barrier like the st.async did.  The staging area is the U staging
+          // buffer, free after set-up; a step's copy has been consumed before any CTA can reach the next step.
+          const uint32_t stg = smem_u32(sA) + (inst * 4 + (w_in - 1)) * (32 * NG * GBP * 2);
+#pragma unroll
+          for (int g = 0; g < NG; ++g) {
+            uint32_t r[16];
+            g_tmem_ld_32x16(d_tmem + g * GBP + (static_cast<uint32_t>(q * 32) << 16), r);
+            tmem_ld_wait();
+            uint32_t h[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              __nv_bfloat162 t2 = __floats2bfloat162_rn(__uint_as_float(r[2 * c]), __uint_as_float(r[2 * c + 1]));
+              h[c] = *reinterpret_cast<uint32_t*>(&t2);
+            }
+            sts_v4(stg + (lane * NG + g) * (GBP * 2), make_uint4(h[0], h[1], h[2], h[3]));
+            sts_v4(stg + (lane * NG + g) * (GBP * 2) + 16, make_uint4(h[4], h[5], h[6], h[7]));
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+#pragma unroll
+            for (int hh = 0; hh < 32 / UPC; ++hh) {
+              const uint32_t to = (q * 32 + hh * UPC) / UPC;
+              const uint32_t dstb = g_map_to_rank(slab_local, to) + rank * (UPC * NG * GBP * 2);
+              const uint32_t rbar = g_map_to_rank(slab_bar_local, to);
+              asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                           ::"r"(dstb), "r"(stg + hh * (UPC * NG * GBP * 2)), "r"(UPC * NG * GBP * 2), "r"(rbar) : "memory");
+            }
+          }
+        } else
 #pragma unroll
         for (int g = 0; g < NG; ++g) {
           uint32_t r[16];
@@ -380,7 +423,9 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
           }
         }
         tc_fence_before();
+        if (pr && step < 1024) p.prof[step * 8 + 4] = dev_clock();
         mbar_wait(slab_bar_a, ph, 50);
+        if (pr && step < 1024) p.prof[step * 8 + 5] = dev_clock();
 #pragma unroll
         for (int s = 0; s < KSZ; ++s)
 #pragma unroll
@@ -409,8 +454,8 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
         if (!BWD) {
 #pragma unroll
           for (int i = 0; i < 4; ++i) hp[i] = carry[i];
-        } else if (has_prev) {
-          g_unpack4(*reinterpret_cast<const uint2*>(p.hs + (((size_t)d * T + tprev) * Bn + b) * H + j), hp);
+        } else {
+          g_unpack4(hp2, hp);                     // fetched with the other inputs at the top of the step
         }
         if (!BWD) {
           float ho[4], ro[4], zo[4], no[4], go[4];
@@ -456,11 +501,13 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
           *reinterpret_cast<uint2*>(ghp + (size_t)2 * H) = g_pack4(dnr);
         }
       }
+      if (pr && step < 1024) p.prof[step * 8 + 6] = dev_clock();
       asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
       if (et == 0) {
         if (p.fenced) g_red_release_add(ctr, 1u);
         else red_relaxed_gpu_add(ctr, 1u);
       }
+      if (pr && step < 1024) p.prof[step * 8 + 7] = dev_clock();
     }
     if (BWD && p.dbw != nullptr) {
       // bias gradients: sum over the instance's 16 utterances (16 consecutive lanes share a unit quad), one red per unit
@@ -497,6 +544,7 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
 
 // ------------------------------------------------------------------ host side
 static constexpr size_t GWS_CTR_BYTES = 2048;
+static constexpr size_t GWS_PROF_BYTES = 65536;     // 1024 steps x 8 stamps
 struct GruGeom {
   int ks;              // cluster size (K split): 4 or 8
   int tiles_m, ksl, nbox, ni, nc;
@@ -538,7 +586,7 @@ int gru_persist_supported(int B, int H, int ND) {
 
 size_t gru_persist_workspace_bytes(int T, int B, int H, int ND) {
   (void)T; (void)B;
-  return GWS_CTR_BYTES + (size_t)ND * 3 * H * H * 2;          // counters + U^T (bf16) for the backward
+  return GWS_CTR_BYTES + GWS_PROF_BYTES + (size_t)ND * 3 * H * H * 2;          // counters + stamps + U^T (bf16) for the backward
 }
 
 template <bool BWD, int KSZ>
@@ -592,7 +640,9 @@ int gru_fwd_persist(const float* wx, float scale, const void* u, const float* bw
   GruGeom geo;
   DS2_REQUIRE(gru_geometry(false, B, H, ND, &geo), DS2_ERR_UNSUPPORTED,
               "ds2_gru_fwd: persistent kernel does not take B=%d H=%d ND=%d", B, H, ND);
-  DS2_REQUIRE(ws && ws_bytes >= GWS_CTR_BYTES, DS2_ERR_WORKSPACE, "ds2_gru_fwd: workspace of %zu bytes required", GWS_CTR_BYTES);
+  DS2_REQUIRE(ws && ws_bytes >= GWS_CTR_BYTES + GWS_PROF_BYTES, DS2_ERR_WORKSPACE, "ds2_gru_fwd: workspace of %zu bytes required",
+              GWS_CTR_BYTES + GWS_PROF_BYTES);
+  p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(static_cast<char*>(ws) + GWS_CTR_BYTES) : nullptr;
   CUtensorMap ta;
   int rc = make_tmap_2d_bf16(&ta, u, H, (uint64_t)ND * 3 * H, H, 64, 128);
   if (rc) return rc;
@@ -602,6 +652,7 @@ int gru_fwd_persist(const float* wx, float scale, const void* u, const float* bw
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = scale;
   p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
   p.slab16 = getenv("DS2_RNN_SLAB_F32") ? 0 : 1;
+  p.bulk = getenv("DS2_GRU_NO_BULK") ? 0 : 1;
   if (!p.fenced) DS2_CUDA(cudaMemsetAsync(hs, DS2_FILL_BYTE, (size_t)ND * T * B * H * 2, st));
   return gru_launch<false>(ta, p, geo, st);
 }
@@ -615,7 +666,8 @@ int gru_bwd_persist(const float* dout, const void* u, const int* lens, const voi
   const size_t need = gru_persist_workspace_bytes(T, B, H, ND);
   DS2_REQUIRE(ws && ws_bytes >= need, DS2_ERR_WORKSPACE, "ds2_gru_bwd: workspace of %zu bytes required", need);
   // U^T per direction: ut[d][i][g*H + j] = U[d][g*H + j][i]
-  __nv_bfloat16* ut = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + GWS_CTR_BYTES);
+  __nv_bfloat16* ut = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + GWS_CTR_BYTES + GWS_PROF_BYTES);
+  p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(static_cast<char*>(ws) + GWS_CTR_BYTES) : nullptr;
   int rc;
   for (int d = 0; d < ND; ++d) {
     rc = ds2_transpose(static_cast<const __nv_bfloat16*>(u) + (size_t)d * 3 * H * H, DS2_BF16, 3L * H, H, H,
@@ -638,6 +690,7 @@ int gru_bwd_persist(const float* dout, const void* u, const int* lens, const voi
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = 1.f;
   p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
   p.slab16 = getenv("DS2_RNN_SLAB_F32") ? 0 : 1;
+  p.bulk = getenv("DS2_GRU_NO_BULK") ? 0 : 1;
   if (!p.fenced) DS2_CUDA(cudaMemsetAsync(dgh, DS2_FILL_BYTE, (size_t)T * B * ND * 3 * H * 2, st));
   return gru_launch<true>(ta, p, geo, st);
 }
