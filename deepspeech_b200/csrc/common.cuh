@@ -33,6 +33,9 @@ int cuda_fail(cudaError_t e, const char* what);
 
 int num_sms();              // SM count of the current device, capped by ds2_set_sm_limit
 int set_sm_limit(int n);
+// true the first time it is called with `flags` on the current device (kernel attributes such as the dynamic
+// shared-memory limit are per device: a process that drives several GPUs must set them on each)
+bool first_use_on_device(unsigned long long* flags);
 void count_launch(int n = 1);
 
 // ------------------------------------------------------------------ small device helpers

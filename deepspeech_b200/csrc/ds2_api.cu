@@ -3,6 +3,8 @@
 
 #include <atomic>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace ds2 {
@@ -34,6 +36,16 @@ int num_sms() {
     v = n[dev];
   }
   return (g_sm_limit > 0 && g_sm_limit < v) ? g_sm_limit : v;
+}
+bool first_use_on_device(unsigned long long* flags) {
+  static std::mutex mu;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;     // unknown device: set the attributes again
+  std::lock_guard<std::mutex> lock(mu);
+  const unsigned long long bit = 1ull << dev;
+  if (*flags & bit) return false;
+  *flags |= bit;
+  return true;
 }
 int set_sm_limit(int n) {
   const int prev = g_sm_limit;

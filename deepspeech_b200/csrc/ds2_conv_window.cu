@@ -435,11 +435,10 @@ extern "C" int ds2_conv_window_pad_cast(const float* dy, void* out, long R, int 
 }
 
 static int window_attr() {
-  static bool done = false;
-  if (!done) {
+  static unsigned long long done_devs = 0;
+  if (first_use_on_device(&done_devs)) {
     DS2_CUDA(cudaFuncSetAttribute(conv_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CW_SMEM));
     DS2_CUDA(cudaFuncSetAttribute(conv_window_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CWG_SMEM));
-    done = true;
   }
   return DS2_OK;
 }

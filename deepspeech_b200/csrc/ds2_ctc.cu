@@ -193,13 +193,12 @@ int ctc_launch(const float* logits, int T, int B, int K, const int* labels, int 
   const size_t smem = ctc_smem_layout(T, Lmax, K, ws.Sp).bytes;
   DS2_REQUIRE(Smax <= 1024 * CTC_NSMAX, DS2_ERR_BAD_SHAPE, "ds2_ctc: Lmax=%d exceeds the supported label length %d", Lmax, (1024 * CTC_NSMAX - 1) / 2);
   DS2_REQUIRE(smem <= 200 * 1024, DS2_ERR_BAD_SHAPE, "ds2_ctc: T=%d / Lmax=%d need %zu bytes of shared memory (> 200 KB)", T, Lmax, smem);
-  static bool attr_done = false;
-  if (!attr_done) {
+  static unsigned long long attr_done_devs = 0;
+  if (first_use_on_device(&attr_done_devs)) {
     DS2_CUDA(cudaFuncSetAttribute(ctc_chain_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     DS2_CUDA(cudaFuncSetAttribute(ctc_chain_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     DS2_CUDA(cudaFuncSetAttribute(ctc_chain_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     DS2_CUDA(cudaFuncSetAttribute(ctc_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-    attr_done = true;
   }
   const int ns = (Smax + threads - 1) / threads;
   if (ns <= 1) ctc_chain_kernel<1><<<dim3(B, 2), threads, smem, st>>>(logits, T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws);

@@ -524,13 +524,12 @@ int gemm_bf16_launch(const void* A, long lda, int a_mn, const void* B, long ldb,
   if (!b_mn) rc = make_tmap_2d_bf16(&tb, B, K, N, ldb, BK, pair ? 128 : bn);
   else rc = make_tmap_2d_bf16(&tb, B, N, K, ldb, 64, BK);
   if (rc) return rc;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static unsigned long long attr_done_devs = 0;
+  if (first_use_on_device(&attr_done_devs)) {
     DS2_CUDA(cudaFuncSetAttribute(gemm_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G2_SMEM));
     DS2_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<32>::SMEM));
     DS2_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<128>::SMEM));
     DS2_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<256>::SMEM));
-    attr_done = true;
   }
   GemmParams p;
   p.C = C; p.ldc = ldc; p.M = M; p.N = N; p.K = K; p.alpha = alpha; p.beta = beta; p.bias = bias;

@@ -592,10 +592,9 @@ size_t gru_persist_workspace_bytes(int T, int B, int H, int ND) {
 template <bool BWD, int KSZ>
 static int gru_launch_ks(const CUtensorMap& ta, GruParams& p, const GruGeom& g, cudaStream_t st) {
   auto kern = gru_persist_kernel<BWD, KSZ>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static unsigned long long attr_done_devs = 0;
+  if (first_use_on_device(&attr_done_devs)) {
     DS2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
-    attr_done = true;
   }
   // one launch per group of (chunk, direction) pairs that fits the device; groups run one after the other
   const int total = p.ND * p.NC;

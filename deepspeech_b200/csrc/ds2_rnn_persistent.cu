@@ -489,10 +489,9 @@ size_t rnn_persist_workspace_bytes(int T, int B, int H, int ND) {
 template <bool BWD, int NIMAX>
 static int persist_launch_n(const CUtensorMap& ta, RnnPersistParams& p, size_t smem, cudaStream_t st) {
   auto kern = rnn_persist_kernel<BWD, NIMAX>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static unsigned long long attr_done_devs = 0;
+  if (first_use_on_device(&attr_done_devs)) {
     DS2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
-    attr_done = true;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(KS, p.tiles_m, p.ND);
