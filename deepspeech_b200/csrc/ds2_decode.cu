@@ -98,3 +98,66 @@ extern "C" int ds2_edit_distance(const int* a, int lda, const int* a_lens, const
   count_launch();
   return DS2_OK;
 }
+
+// ------------------------------------------------------------------ label pre-processing on the device
+// tf.nn.ctc_loss's handling of the SparseTensor labels built at src/deepSpeech_train.py:437 (values produced by the
+// host double loop of src/deepSpeech_dummy.py:89-98): per batch row, in index order, collapse adjacent repeats when
+// asked, stop at the first label >= num_classes-1; a valid label after such a terminator is an error (status 1).
+// indices [n,2] int64 sorted row-major (the SparseTensor convention), values [n] int32.
+namespace ds2 {
+__global__ void ctc_labels_from_sparse_kernel(const long long* __restrict__ indices, const int* __restrict__ values, int n, int B, int Lcap,
+                                              int num_classes, int collapse, int* __restrict__ labels, int* __restrict__ label_lens,
+                                              int* __restrict__ repeats, int* __restrict__ status) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  int lo = 0, hi = n;                      // first entry of row b
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (indices[2 * (long long)mid] < b) lo = mid + 1; else hi = mid;
+  }
+  int len = 0, rep = 0, st = 0;
+  long long prev_col = -1;
+  int prev_v = -1, last = -1;
+  bool have_prev = false, finished = false;
+  for (int i = lo; i < n && indices[2 * (long long)i] == b; ++i) {
+    const long long col = indices[2 * (long long)i + 1];
+    if (col < prev_col) st |= 2;           // not sorted within the row
+    prev_col = col;
+    const int v = values[i];
+    if (!have_prev || !collapse || v != prev_v) {
+      if (v >= num_classes - 1 || v < 0) {
+        finished = true;
+      } else if (finished) {
+        st |= 1;
+      } else if (len < Lcap) {
+        labels[(long long)b * Lcap + len] = v;
+        if (len > 0 && v == last) ++rep;
+        last = v;
+        ++len;
+      } else {
+        st |= 4;                           // more labels than the dense shape allows
+      }
+    }
+    prev_v = v;
+    have_prev = true;
+  }
+  for (int j = len; j < Lcap; ++j) labels[(long long)b * Lcap + j] = 0;
+  label_lens[b] = len;
+  repeats[b] = rep;
+  status[b] = st;
+}
+}  // namespace ds2
+
+extern "C" int ds2_ctc_labels_from_sparse(const long long* indices, const int* values, int n, int B, int Lcap, int num_classes,
+                                          int collapse_repeated, int* labels, int* label_lens, int* repeats, int* status,
+                                          void* stream) {
+  DS2_REQUIRE(labels && label_lens && repeats && status && (n == 0 || (indices && values)), DS2_ERR_BAD_ARG,
+              "ds2_ctc_labels_from_sparse: null pointer");
+  DS2_REQUIRE(n >= 0 && B > 0 && Lcap > 0 && num_classes >= 2, DS2_ERR_BAD_SHAPE, "ds2_ctc_labels_from_sparse: bad shape");
+  ctc_labels_from_sparse_kernel<<<(B + 63) / 64, 64, 0, static_cast<cudaStream_t>(stream)>>>(indices, values, n, B, Lcap, num_classes,
+                                                                                             collapse_repeated, labels, label_lens,
+                                                                                             repeats, status);
+  DS2_LAUNCH_CHECK("ctc_labels_from_sparse_kernel");
+  count_launch();
+  return DS2_OK;
+}

@@ -858,6 +858,25 @@ def ctc_prepare_labels(indices, values, dense_shape, num_classes: int, preproces
     return lab, lens, reps
 
 
+def ctc_prepare_labels_device(indices: torch.Tensor, values: torch.Tensor, dense_shape, num_classes: int,
+                              preprocess_collapse_repeated: bool):
+    """Device form of ctc_prepare_labels: indices int64 [n,2] (row-major sorted) and values int32 [n]
+    are CUDA tensors, nothing is copied to the host.  -> (labels [B,Lcap] int32, label_lens [B], repeats [B], status [B])
+    CUDA tensors, Lcap = dense_shape[1]; status != 0 marks the rows for which tf.nn.ctc_loss would raise."""
+    _need_cuda(indices, values)
+    Bn, Lcap = int(dense_shape[0]), max(1, int(dense_shape[1]))
+    idx = indices.contiguous().to(torch.int64)
+    val = values.contiguous().to(torch.int32)
+    dev = idx.device
+    labels = torch.empty((Bn, Lcap), dtype=torch.int32, device=dev)
+    lens = torch.empty((Bn,), dtype=torch.int32, device=dev)
+    reps = torch.empty((Bn,), dtype=torch.int32, device=dev)
+    status = torch.empty((Bn,), dtype=torch.int32, device=dev)
+    check(lib.ds2_ctc_labels_from_sparse(_p(idx), _p(val), int(val.numel()), Bn, Lcap, num_classes, int(preprocess_collapse_repeated),
+                                         _p(labels), _p(lens), _p(reps), _p(status), _stream()), "ds2_ctc_labels_from_sparse")
+    return labels, lens, reps, status
+
+
 class _CTCFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, logits, labels_dev, label_lens_dev, seq_lens_dev, Lmax):

@@ -225,6 +225,16 @@ int ds2_ctc_greedy_decode(const float* logits, int T, int B, int K, const int* s
 int ds2_edit_distance(const int* a, int lda, const int* a_lens, const int* b, int ldb, const int* b_lens, int n, int maxlen, int* out,
                       void* stream);
 
+/* ---- label pre-processing on the device ------------------------------------------
+ * What tf.nn.ctc_loss does with the SparseTensor labels of src/deepSpeech_train.py:437 before the lattice: per batch
+ * row, in index order, collapse adjacent repeats when asked, stop at the first label >= num_classes-1.  indices [n,2]
+ * int64 sorted row-major, values [n] int32 (both on the device); labels [B,Lcap] (zero padded), label_lens, repeats
+ * (adjacent equal labels that remain: the lattice needs that many extra frames) and status [B] come back: bit 0 = a
+ * valid label follows a terminator (TF raises), bit 1 = columns not sorted, bit 2 = more than Lcap labels.
+ * The host form with the reference's exceptions is deepspeech_b200.ops.ctc_prepare_labels. */
+int ds2_ctc_labels_from_sparse(const long long* indices, const int* values, int n, int B, int Lcap, int num_classes,
+                               int collapse_repeated, int* labels, int* label_lens, int* repeats, int* status, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

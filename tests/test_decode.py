@@ -53,3 +53,38 @@ def test_greedy_decode_and_cer_kernels_vs_oracle():
     assert list(d) == [O.edit_distance_py(p, q) for p, q in zip(a, bq)]
     with pytest.raises(RuntimeError):
         decode.ctc_greedy_decoder(torch.zeros(3, 2, 29), [3, 3])
+
+
+@pytest.mark.gpu
+def test_label_transform_on_the_device_matches_the_host_form():
+    """ds2_ctc_labels_from_sparse against ops.ctc_prepare_labels (itself checked against the oracle in test_host.py)."""
+    from deepspeech_b200 import ops
+    rng = np.random.default_rng(6)
+    B, L, K = 7, 23, 29
+    dense = rng.integers(0, 28, size=(B, L))
+    dense[rng.random((B, L)) < 0.35] = 0                       # zeros are dropped by the sparse conversion (dummy.py:89-98)
+    for b in range(B):
+        for j in range(1, L):
+            if rng.random() < 0.3:
+                dense[b, j] = dense[b, j - 1]                      # adjacent repeats: collapsed when asked
+    dense[2, 9:] = 0
+    dense[2, 9] = 28                                              # a terminator with nothing valid after it
+    dense[5] = 0                                                  # an empty row
+    idx = np.argwhere(dense != 0).astype(np.int64)
+    vals = dense[dense != 0].astype(np.int32)
+    for collapse in (True, False):
+        lab_h, len_h, rep_h = ops.ctc_prepare_labels(idx, vals, dense.shape, K, collapse)
+        lab_d, len_d, rep_d, st = ops.ctc_prepare_labels_device(torch.tensor(idx, device="cuda"), torch.tensor(vals, device="cuda"),
+                                                                dense.shape, K, collapse)
+        assert st.cpu().numpy().tolist() == [0] * B
+        assert len_d.cpu().numpy().tolist() == len_h.tolist() and rep_d.cpu().numpy().tolist() == rep_h.tolist()
+        ld = lab_d.cpu().numpy()
+        for b in range(B):
+            assert ld[b, :len_h[b]].tolist() == lab_h[b, :len_h[b]].tolist() and not ld[b, len_h[b]:].any()
+    # a valid label after a terminator: the host form raises, the device form flags the row
+    bad_idx = np.asarray([[0, 0], [0, 1], [1, 0]], np.int64)
+    bad_vals = np.asarray([28, 3, 5], np.int32)
+    with pytest.raises(ValueError):
+        ops.ctc_prepare_labels(bad_idx, bad_vals, (2, 2), K, True)
+    _, _, _, st = ops.ctc_prepare_labels_device(torch.tensor(bad_idx, device="cuda"), torch.tensor(bad_vals, device="cuda"), (2, 2), K, True)
+    assert st.cpu().numpy().tolist() == [1, 0]
