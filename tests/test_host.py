@@ -137,6 +137,14 @@ def _dp_worker(rank, world, port, q):
     dist.destroy_process_group()
 
 
+def _free_port():
+    """A TCP port nobody listens on right now (asked from the kernel), for the gloo rendezvous of the two workers."""
+    import socket
+    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as sk:
+        sk.bind(("127.0.0.1", 0))
+        return sk.getsockname()[1]
+
+
 class _EarlyLinear(torch.autograd.Function):
     """Stands in for the recurrent stack's autograd node: offers its weight gradient to ops.STACK_GRAD_HOOK from inside
     backward, as deepspeech_b200.ops._RecStackFn does layer by layer."""
@@ -201,7 +209,7 @@ def test_dp_early_allreduce_from_stack_hook_world2_gloo():
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 31500 + os.getpid() % 2000
+    port = _free_port()
     procs = [ctx.Process(target=_dp_early_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
@@ -215,7 +223,7 @@ def test_dp_allreduce_world2_gloo():
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29500 + os.getpid() % 2000
+    port = _free_port()
     procs = [ctx.Process(target=_dp_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
