@@ -796,14 +796,21 @@ class _LinearFn(torch.autograd.Function):
         R, K = x2d.shape
         N = W.shape[0]
         dx = None
-        if ctx.needs_input_grad[0]:
-            dx = gemm_nt(dy, W, b_mn=True)                      # [R,K] = dy[R,N] . W[N,K]
-            if x2d.dtype != torch.float32:
-                dx = cast(dx, x2d.dtype)
-        if x2d.dtype == torch.bfloat16 and R % 8 == 0 and K % 8 == 0:
-            # tensor cores: dy^T as a K-major bf16 operand (transpose+cast, N x R), x as the MN-major one, split-K over R
+        tc = x2d.dtype == torch.bfloat16 and R % 8 == 0 and K % 8 == 0
+        if tc:
+            # tensor cores: dy^T [N,R] in bf16 (one transpose + cast) serves both products
             dyT = torch.empty((N, R), dtype=torch.bfloat16, device=dy.device)
             check(lib.ds2_transpose(_p(dy), DS2_F32, R, N, N, _p(dyT), DS2_BF16, R, _stream()), "ds2_transpose")
+        if ctx.needs_input_grad[0]:
+            if tc:
+                # dx[R,K] = dy . W: dy^T is the MN-major A operand, W [N,K] the MN-major B operand, contraction over N classes
+                dx = gemm_nt(dyT, cast(W, torch.bfloat16), a_mn=True, b_mn=True, M=R, N=K, K=N, out_dtype=torch.bfloat16)
+            else:
+                dx = gemm_nt(dy, W, b_mn=True)                  # [R,K] = dy[R,N] . W[N,K]
+                if x2d.dtype != torch.float32:
+                    dx = cast(dx, x2d.dtype)
+        if tc:
+            # dW[N,K] = dy^T x: dy^T K-major, x the MN-major operand, split-K over the R rows
             dW = torch.empty((N, K), dtype=torch.float32, device=dy.device)
             check(lib.ds2_gemm_bf16_splitk(_p(dyT), R, 0, _p(x2d), K, 1, _p(dW), K, N, K, R, 1.0, None, 0, _stream()),
                   "ds2_gemm_bf16_splitk")
