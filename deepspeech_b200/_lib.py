@@ -27,6 +27,7 @@ _SIGS = {
     "ds2_last_error": (c_char_p, []),
     "ds2_version": (I, []),
     "ds2_launch_count": (c_longlong, []),
+    "ds2_debug_reload_env": (None, []),
     "ds2_ctc_workspace_bytes": (SZ, [I, I, I, I]),
     "ds2_ctc_loss_fwd_bwd": (I, [P, I, I, I, P, I, P, P, P, P, P, P, SZ, P]),
     "ds2_ctc_noalloc_max_bytes": (SZ, []),

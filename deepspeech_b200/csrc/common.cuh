@@ -31,6 +31,26 @@ int cuda_fail(cudaError_t e, const char* what);
     }                                                              \
   } while (0)
 
+// Environment switches (debugging / A-B runs), read ONCE per process (ds2_debug_reload_env re-reads them).
+struct EnvSwitches {
+  int rnn_no_coop;      // DS2_RNN_NO_COOP: never use the cooperative launch attribute
+  int rnn_exp;          // DS2_RNN_EXP: timing experiments (results invalid for some bits)
+  int rnn_fenced;       // DS2_RNN_FENCED: release/acquire step counters instead of self-validating rows
+  int rnn_slab_f32;     // DS2_RNN_SLAB_F32: fp32 partial sums across the cluster
+  int rnn_prof;         // DS2_RNN_PROF: in-kernel stage stamps
+  int rnn_v1;           // DS2_RNN_V1: round-1 exchange protocol of the ReLU recurrence (A/B runs)
+  int gru_no_bulk;      // DS2_GRU_NO_BULK
+  int gemm_no_pair;     // DS2_GEMM_NO_PAIR
+  int ctc_ns;           // DS2_CTC_NS
+  int ctc_v1;           // DS2_CTC_V1: round-1 CTC kernels (A/B runs)
+  int profiler;         // a profiler / injection library is attached to this process (ncu, nsys, compute-sanitizer)
+};
+const EnvSwitches& env();
+void reload_env();
+// Cooperative launches guarantee co-residency of the persistent grids but cannot be replayed by profilers:
+// used unless DS2_RNN_NO_COOP is set or a profiler is attached.
+bool use_cooperative_launch();
+
 int num_sms();              // SM count of the current device, capped by ds2_set_sm_limit
 int set_sm_limit(int n);
 // true the first time it is called with `flags` on the current device (kernel attributes such as the dynamic
@@ -79,12 +99,16 @@ __device__ __forceinline__ long long dev_clock() {
   return 0;
 #endif
 }
+// Only the first few waiters report (one line each, with the tag of the wait they were stuck in); the others trap
+// silently - a timed-out grid has thousands of stuck threads and their lines would bury the first, informative one.
+static __device__ unsigned int g_spin_reports = 0;
 struct SpinGuard {
   long long t0;
   __device__ __forceinline__ SpinGuard() : t0(dev_clock()) {}
   __device__ __forceinline__ void check(int tag) {
     if (dev_clock() - t0 > DS2_SPIN_LIMIT_CYCLES) {
-      printf("ds2: device spin timeout tag=%d block=(%d,%d) thread=%d\n", tag, blockIdx.x, blockIdx.y, threadIdx.x);
+      if (atomicAdd(&g_spin_reports, 1u) < 4u)
+        printf("ds2: device spin timeout tag=%d block=(%d,%d,%d) thread=%d\n", tag, blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x);
       __trap();
     }
   }

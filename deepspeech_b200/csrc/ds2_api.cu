@@ -1,5 +1,6 @@
 // Error plumbing, device queries and the recurrent-layer dispatch of the C ABI.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <atomic>
 
@@ -54,6 +55,41 @@ int set_sm_limit(int n) {
 }
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
+static EnvSwitches g_env;
+static std::once_flag g_env_once;
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  if (!v) return dflt;
+  if (!*v) return 1;
+  return atoi(v);
+}
+static int env_flag(const char* name) { return getenv(name) ? 1 : 0; }
+void reload_env() {
+  EnvSwitches e = {};
+  e.rnn_no_coop = env_flag("DS2_RNN_NO_COOP");
+  e.rnn_exp = env_int("DS2_RNN_EXP", 0);
+  e.rnn_fenced = env_flag("DS2_RNN_FENCED");
+  e.rnn_slab_f32 = env_flag("DS2_RNN_SLAB_F32");
+  e.rnn_prof = env_flag("DS2_RNN_PROF");
+  e.rnn_v1 = env_flag("DS2_RNN_V1");
+  e.gru_no_bulk = env_flag("DS2_GRU_NO_BULK");
+  e.gemm_no_pair = env_flag("DS2_GEMM_NO_PAIR");
+  e.ctc_ns = env_int("DS2_CTC_NS", 0);
+  e.ctc_v1 = env_flag("DS2_CTC_V1");
+  // Nsight Compute / Systems and compute-sanitizer inject a library into the target process and announce it in the
+  // environment (observed under ncu 2025.2: NV_COMPUTE_PROFILER_PERFWORKS_DIR, NV_NSIGHT_INJECTION_*,
+  // NV_TPS_LAUNCH_TOKEN; CUDA_INJECTION64_PATH is the documented generic hook)
+  e.profiler = (getenv("NV_COMPUTE_PROFILER_PERFWORKS_DIR") || getenv("CUDA_INJECTION64_PATH") || getenv("NV_TPS_LAUNCH_TOKEN") ||
+                getenv("NV_NSIGHT_INJECTION_PORT_BASE") || getenv("NSYS_PROFILING_SESSION_ID") || getenv("NV_SANITIZER_INJECTION_PORT_BASE"))
+                   ? 1 : 0;
+  g_env = e;
+}
+const EnvSwitches& env() {
+  std::call_once(g_env_once, reload_env);
+  return g_env;
+}
+bool use_cooperative_launch() { return !env().rnn_no_coop && !env().profiler; }
+
 // implemented in ds2_rnn_generic.cu / ds2_rnn_persist.cu
 int rnn_relu_fwd_generic(const float* wx, float scale, const float* u, const float* bias, const int* lens, float* hs, int T,
                          int B, int H, int ND, int reverse_mask, float cap, cudaStream_t st);
@@ -71,7 +107,8 @@ int rnn_persist_supported(int B, int H, int ND);
 using namespace ds2;
 
 extern "C" const char* ds2_last_error(void) { return g_err; }
-extern "C" int ds2_version(void) { return 100; }
+extern "C" int ds2_version(void) { return 200; }
+extern "C" void ds2_debug_reload_env(void) { (void)env(); reload_env(); }
 extern "C" long long ds2_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 static int rnn_check(const void* a, const void* b, const void* c, const void* d, int T, int B, int H, int ND, int dtype) {

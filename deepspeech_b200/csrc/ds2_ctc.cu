@@ -186,7 +186,7 @@ int ctc_launch(const float* logits, int T, int B, int K, const int* labels, int 
   // states per thread: 1 measured fastest (one thread per lattice state keeps the per-step chain shortest; 2 and 4
   // halve / quarter the warps at the barrier but lengthen the serial work of a step); DS2_CTC_NS overrides for tuning
   int ns_pref = 1;
-  if (const char* e = getenv("DS2_CTC_NS")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) ns_pref = v; }
+  { const int v = env().ctc_ns; if (v == 1 || v == 2 || v == 4) ns_pref = v; }
   int threads = (((Smax + ns_pref - 1) / ns_pref + 31) / 32) * 32;
   if (threads < 64) threads = 64;
   if (threads > 1024) threads = 1024;

@@ -519,7 +519,7 @@ int gemm_bf16_launch(const void* A, long lda, int a_mn, const void* B, long ldb,
   if (rc) return rc;
   const int bn = (N <= 32) ? 32 : (N <= 128 ? 128 : 256);
   // wide outputs with at least two row blocks: CTA pairs on 256x256 tiles (DS2_GEMM_NO_PAIR=1: single-CTA 128x256)
-  static const bool no_pair = getenv("DS2_GEMM_NO_PAIR") != nullptr;
+  const bool no_pair = env().gemm_no_pair != 0;
   const bool pair = bn == 256 && M > 128 && !no_pair && num_sms() >= 2;
   if (!b_mn) rc = make_tmap_2d_bf16(&tb, B, K, N, ldb, BK, pair ? 128 : bn);
   else rc = make_tmap_2d_bf16(&tb, B, N, K, ldb, 64, BK);
@@ -591,7 +591,7 @@ extern "C" int ds2_gemm_bf16_splitk(const void* A, long lda, int a_mn_major, con
     // (one wave at 66 %); three K splits make it two full waves of a third of K each.  A split keeps >= 8 K-blocks and
     // pays for the red.add epilogue and the zero fill: taken only for a gain of DS2_GEMM_SPLIT_GAIN percent (default 10).
     const int bn = (N <= 32) ? 32 : (N <= 128 ? 128 : 256);
-    const bool pair = bn == 256 && M > 128 && getenv("DS2_GEMM_NO_PAIR") == nullptr;
+    const bool pair = bn == 256 && M > 128 && !ds2::env().gemm_no_pair;
     const int tiles = pair ? ((M + 255) / 256) * ((N + 255) / 256) : ((M + ds2::BM - 1) / ds2::BM) * ((N + bn - 1) / bn);
     const int units = pair ? ds2::num_sms() / 2 : ds2::num_sms();
     const int num_kb = (K + ds2::BK - 1) / ds2::BK;

@@ -614,7 +614,7 @@ static int gru_launch_ks(const CUtensorMap& ta, GruParams& p, const GruGeom& g, 
     attrs[1].id = cudaLaunchAttributeCooperative;
     attrs[1].val.cooperative = 1;
     cfg.attrs = attrs;
-    cfg.numAttrs = getenv("DS2_RNN_NO_COOP") ? 1 : 2;
+    cfg.numAttrs = use_cooperative_launch() ? 2 : 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, p);
     if (e != cudaSuccess && cfg.numAttrs == 2) {
       (void)cudaGetLastError();
@@ -641,7 +641,7 @@ int gru_fwd_persist(const float* wx, float scale, const void* u, const float* bw
               "ds2_gru_fwd: persistent kernel does not take B=%d H=%d ND=%d", B, H, ND);
   DS2_REQUIRE(ws && ws_bytes >= GWS_CTR_BYTES + GWS_PROF_BYTES, DS2_ERR_WORKSPACE, "ds2_gru_fwd: workspace of %zu bytes required",
               GWS_CTR_BYTES + GWS_PROF_BYTES);
-  p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(static_cast<char*>(ws) + GWS_CTR_BYTES) : nullptr;
+  p.prof = env().rnn_prof ? reinterpret_cast<long long*>(static_cast<char*>(ws) + GWS_CTR_BYTES) : nullptr;
   CUtensorMap ta;
   int rc = make_tmap_2d_bf16(&ta, u, H, (uint64_t)ND * 3 * H, H, 64, 128);
   if (rc) return rc;
@@ -649,9 +649,9 @@ int gru_fwd_persist(const float* wx, float scale, const void* u, const float* bw
   p.gates = static_cast<__nv_bfloat16*>(gates); p.dgi = nullptr; p.dgh = nullptr;
   p.ctr = static_cast<unsigned int*>(ws);
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = scale;
-  p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
-  p.slab16 = getenv("DS2_RNN_SLAB_F32") ? 0 : 1;
-  p.bulk = getenv("DS2_GRU_NO_BULK") ? 0 : 1;
+  p.fenced = env().rnn_fenced;
+  p.slab16 = env().rnn_slab_f32 ? 0 : 1;
+  p.bulk = env().gru_no_bulk ? 0 : 1;
   if (!p.fenced) DS2_CUDA(cudaMemsetAsync(hs, DS2_FILL_BYTE, (size_t)ND * T * B * H * 2, st));
   return gru_launch<false>(ta, p, geo, st);
 }
@@ -666,7 +666,7 @@ int gru_bwd_persist(const float* dout, const void* u, const int* lens, const voi
   DS2_REQUIRE(ws && ws_bytes >= need, DS2_ERR_WORKSPACE, "ds2_gru_bwd: workspace of %zu bytes required", need);
   // U^T per direction: ut[d][i][g*H + j] = U[d][g*H + j][i]
   __nv_bfloat16* ut = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + GWS_CTR_BYTES + GWS_PROF_BYTES);
-  p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(static_cast<char*>(ws) + GWS_CTR_BYTES) : nullptr;
+  p.prof = env().rnn_prof ? reinterpret_cast<long long*>(static_cast<char*>(ws) + GWS_CTR_BYTES) : nullptr;
   int rc;
   for (int d = 0; d < ND; ++d) {
     rc = ds2_transpose(static_cast<const __nv_bfloat16*>(u) + (size_t)d * 3 * H * H, DS2_BF16, 3L * H, H, H,
@@ -687,9 +687,9 @@ int gru_bwd_persist(const float* dout, const void* u, const int* lens, const voi
   }
   p.ctr = static_cast<unsigned int*>(ws);
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = 1.f;
-  p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
-  p.slab16 = getenv("DS2_RNN_SLAB_F32") ? 0 : 1;
-  p.bulk = getenv("DS2_GRU_NO_BULK") ? 0 : 1;
+  p.fenced = env().rnn_fenced;
+  p.slab16 = env().rnn_slab_f32 ? 0 : 1;
+  p.bulk = env().gru_no_bulk ? 0 : 1;
   if (!p.fenced) DS2_CUDA(cudaMemsetAsync(dgh, DS2_FILL_BYTE, (size_t)T * B * ND * 3 * H * 2, st));
   return gru_launch<true>(ta, p, geo, st);
 }

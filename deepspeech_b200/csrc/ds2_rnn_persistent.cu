@@ -506,7 +506,7 @@ static int persist_launch_n(const CUtensorMap& ta, RnnPersistParams& p, size_t s
   attrs[1].id = cudaLaunchAttributeCooperative;       // all CTAs co-resident (they wait on each other's data)
   attrs[1].val.cooperative = 1;
   cfg.attrs = attrs;
-  cfg.numAttrs = getenv("DS2_RNN_NO_COOP") ? 1 : 2;   // profilers cannot replay cooperative launches
+  cfg.numAttrs = use_cooperative_launch() ? 2 : 1;   // profilers cannot replay cooperative launches
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, p);
   if (e != cudaSuccess && cfg.numAttrs == 2) {
     // some driver versions reject cooperative + cluster launches: the grid (<= 128 CTAs, 1 per SM)
@@ -533,10 +533,10 @@ static int persist_common(RnnPersistParams& p, size_t* smem, int T, int B, int H
   DS2_REQUIRE(ws && ws_bytes >= need, DS2_ERR_WORKSPACE, "%s: workspace of %zu bytes required", who, need);
   DS2_CUDA(cudaMemsetAsync(ws, 0, WS_CTR_BYTES, st));
   p.ctr = static_cast<unsigned int*>(ws);
-  p.exp = getenv("DS2_RNN_EXP") ? atoi(getenv("DS2_RNN_EXP")) : 0;
-  p.fenced = getenv("DS2_RNN_FENCED") ? 1 : 0;
-  p.slab16 = (getenv("DS2_RNN_SLAB_F32") || (p.exp & 128)) ? 0 : 1;
-  p.prof = getenv("DS2_RNN_PROF") ? reinterpret_cast<long long*>(static_cast<char*>(ws) + WS_CTR_BYTES) : nullptr;
+  p.exp = env().rnn_exp;
+  p.fenced = env().rnn_fenced;
+  p.slab16 = (env().rnn_slab_f32 || (p.exp & 128)) ? 0 : 1;
+  p.prof = env().rnn_prof ? reinterpret_cast<long long*>(static_cast<char*>(ws) + WS_CTR_BYTES) : nullptr;
   return DS2_OK;
 }
 

@@ -35,6 +35,9 @@ enum {
 
 const char* ds2_last_error(void);
 int ds2_version(void);
+/* Re-reads the DS2_* debugging switches from the environment (they are otherwise read once per process).  No
+ * counterpart in the reference; used by the tests that flip a switch inside one process. */
+void ds2_debug_reload_env(void);
 /* number of kernels this library has launched in this process (bench.py's gpu_launches) */
 long long ds2_launch_count(void);
 /* Caps the number of CTAs that grid-sized (persistent / grid-stride) kernels launched afterwards from THIS host

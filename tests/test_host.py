@@ -23,7 +23,7 @@ def test_library_loads_and_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(raw, name), "library does not export %s" % name
     assert sorted(_lib.EXPORTS) == declared, set(_lib.EXPORTS) ^ set(declared)
-    assert _lib.lib.ds2_version() == 100
+    assert _lib.lib.ds2_version() == 200
 
 
 def test_c_abi_argument_validation_without_gpu():
