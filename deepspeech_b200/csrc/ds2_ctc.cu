@@ -259,7 +259,14 @@ static int ctc_noalloc_scratch(void** out) {
   return DS2_OK;
 }
 
-extern "C" size_t ds2_ctc_noalloc_max_bytes(void) { return (size_t)DS2_CTC_NOALLOC_MAX_BYTES; }
+// Also the set-up call: it looks up the array's device address on the CURRENT device (no allocation; with lazy module
+// loading this is the moment the driver backs the array with memory).  A caller whose own allocator is about to claim
+// the rest of HBM, or who is about to begin a stream capture, calls this first, once per device.
+extern "C" size_t ds2_ctc_noalloc_max_bytes(void) {
+  void* scratch = nullptr;
+  (void)ctc_noalloc_scratch(&scratch);      // a failure is reported again, with its message, by the first compute call
+  return (size_t)DS2_CTC_NOALLOC_MAX_BYTES;
+}
 
 // Same computation and same kernels as ds2_ctc_loss_fwd_bwd; only the home of the scratch differs.
 //  * The first call on each device looks up the scratch address (no allocation, but a runtime query): make that

@@ -8,7 +8,7 @@ import numpy as np
 import torch
 
 from . import ops
-from .helper_routines import glorot_uniform
+from .helper_routines import glorot_uniform, stable_seed
 
 _SCOPE_VARS = {}      # (scope-name) -> dict of Parameters; the analogue of TF's variable store
 
@@ -143,7 +143,7 @@ class CustomRNNCell2(object):
     def variables(self, scope, input_size, device="cuda"):
         sc = "%s/CustomRNNCell2" % scope if scope else "CustomRNNCell2"
         H = self._num_units
-        seed = abs(hash(sc)) % (2 ** 32)
+        seed = stable_seed(sc)
         W = _get_variable(sc, "W", (H, input_size), lambda s: glorot_uniform(np.random.default_rng(seed), s), True, device)
         U = _get_variable(sc, "U", (H, H), lambda s: glorot_uniform(np.random.default_rng(seed + 1), s), True, device)
         B = _get_variable(sc, "B", (H,), 0.0, True, device)

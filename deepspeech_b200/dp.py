@@ -46,6 +46,10 @@ class GradAllReducer(object):
         # with zero_grad(set_to_none=True): accumulating into an older .grad would add the not-yet-reduced values.
         self._early = {}            # id(parameter) -> (work handle, reduced tensor)
         if self.world > 1:
+            # replicas must start from the same weights whatever seeded them: rank 0's values go to everybody
+            with torch.no_grad():
+                for q in self.params:
+                    dist.broadcast(q.data, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
             from . import ops
             ops.STACK_GRAD_HOOK = self._on_stack_layer
 

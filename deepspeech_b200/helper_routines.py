@@ -24,6 +24,13 @@ def variance_scaling(rng: np.random.Generator, shape, factor: float = 2.0) -> np
     return (out * std).astype(np.float32)
 
 
+def stable_seed(name: str, base: int = 1234) -> int:
+    """Seed derived from a variable's scope name, identical in every process and on every data-parallel rank
+    (Python randomises str hashes per process; crc32 does not)."""
+    import zlib
+    return (zlib.crc32(name.encode("utf-8")) + int(base)) % (2 ** 32)
+
+
 def glorot_uniform(rng: np.random.Generator, shape) -> np.ndarray:
     """tf.get_variable's default initializer for the RNN W/U (src/custom_ops.py:60,66)."""
     lim = math.sqrt(6.0 / (shape[-2] + shape[-1]))
@@ -36,7 +43,7 @@ def _variable_on_cpu(name, shape, initializer=None, use_fp16=False, trainable=Tr
     if isinstance(shape, int):
         shape = [shape]
     if initializer is None:
-        val = glorot_uniform(np.random.default_rng(abs(hash(name)) % (2 ** 32)), tuple(shape)) if len(shape) >= 2 \
+        val = glorot_uniform(np.random.default_rng(stable_seed(name)), tuple(shape)) if len(shape) >= 2 \
             else np.zeros(shape, np.float32)
     elif callable(initializer):
         val = np.asarray(initializer(tuple(shape)), dtype=np.float32)
@@ -47,7 +54,7 @@ def _variable_on_cpu(name, shape, initializer=None, use_fp16=False, trainable=Tr
 
 def _variable_with_weight_decay(name, shape, wd_value, use_fp16, rng=None, device="cuda"):
     """src/helper_routines.py:49-78 (wd_value is always None at the reference's call sites)."""
-    rng = rng or np.random.default_rng(abs(hash(name)) % (2 ** 32))
+    rng = rng or np.random.default_rng(stable_seed(name))
     if wd_value is not None:
         raise NotImplementedError("weight decay is never enabled on the reference's hot path (wd_value=None)")
     return _variable_on_cpu(name, shape, lambda s: variance_scaling(rng, s), use_fp16, device=device)

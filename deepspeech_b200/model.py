@@ -122,6 +122,12 @@ class DeepSpeech2(torch.nn.Module):
             return ops.bigru_layer(x, W, U, Bv, BU, self._lens, reverse_mask, self.use_bf16, out_dtype)
         return ops.birnn_layer(x, W, U, Bv, self._lens, reverse_mask, self.use_bf16, out_dtype)
 
+    @torch.no_grad()
+    def _layer_eval(self, x, l, rnn_lens_dev):
+        """One bi-directional layer of the 'stacked' wiring on its own (the per-layer error report of the parity tests)."""
+        self._lens = rnn_lens_dev
+        return self._layer(x, l, (0, 1), 0b10, torch.bfloat16 if self.use_bf16 else torch.float32)
+
     def recurrent_stack(self, x: torch.Tensor, rnn_lens_dev: torch.Tensor) -> torch.Tensor:
         self._lens = rnn_lens_dev
         act = torch.bfloat16 if self.use_bf16 else torch.float32

@@ -838,30 +838,40 @@ def ctc_prepare_labels(indices, values, dense_shape, num_classes: int, preproces
         raise ValueError("ctc_loss: labels.indices and labels.values disagree in length")
     if idx.shape[0] and (idx[:, 0].min() < 0 or idx[:, 0].max() >= Bn):
         raise ValueError("ctc_loss: label batch index out of range")
-    seqs: List[List[int]] = [[] for _ in range(Bn)]
-    order = np.lexsort((idx[:, 1], idx[:, 0])) if idx.shape[0] else []
-    prev_b, prev_v, finished = -1, None, False
-    for i in order:
-        b, v = int(idx[i, 0]), int(vals[i])
-        if b != prev_b:
-            prev_b, prev_v, finished = b, None, False
-        if prev_v is None or not preprocess_collapse_repeated or v != prev_v:
-            if v >= num_classes - 1 or v < 0:
-                finished = True
-            else:
-                if finished:
-                    raise ValueError("ctc_loss: saw a non-null label (index >= num_classes - 1) following a null "
-                                     "label, batch: %d" % b)
-                seqs[b].append(v)
-        prev_v = v
-    Lmax = max([len(s) for s in seqs] + [1])
+    n = idx.shape[0]
+    if n == 0:
+        return np.zeros((Bn, 1), np.int32), np.zeros(Bn, np.int32), np.zeros(Bn, np.int32)
+    # whole-array form of the per-entry scan (no Python loop inside the training step)
+    order = np.lexsort((idx[:, 1], idx[:, 0]))
+    bs, vs = idx[order, 0], vals[order]
+    first = np.ones(n, bool)
+    first[1:] = bs[1:] != bs[:-1]
+    considered = first.copy()
+    if preprocess_collapse_repeated:
+        considered[1:] |= vs[1:] != vs[:-1]
+    else:
+        considered[:] = True
+    null = considered & ((vs >= num_classes - 1) | (vs < 0))
+    # number of terminators seen in this row BEFORE each entry
+    c = np.cumsum(null)
+    row_start = np.maximum.accumulate(np.where(first, np.arange(n), 0))
+    before = c - null - (c[row_start] - null[row_start])
+    emit = considered & ~null
+    bad = emit & (before > 0)
+    if bad.any():
+        raise ValueError("ctc_loss: saw a non-null label (index >= num_classes - 1) following a null "
+                         "label, batch: %d" % int(bs[np.argmax(bad)]))
+    eb, ev = bs[emit], vs[emit]
+    lens = np.bincount(eb, minlength=Bn).astype(np.int32)
+    Lmax = max(int(lens.max(initial=0)), 1)
     lab = np.zeros((Bn, Lmax), dtype=np.int32)
-    lens = np.zeros(Bn, dtype=np.int32)
+    starts = np.concatenate([[0], np.cumsum(lens)[:-1]])
+    pos = np.arange(eb.shape[0]) - starts[eb]
+    lab[eb, pos] = ev
     reps = np.zeros(Bn, dtype=np.int32)
-    for b, s in enumerate(seqs):
-        lab[b, :len(s)] = s
-        lens[b] = len(s)
-        reps[b] = sum(1 for i in range(1, len(s)) if s[i] == s[i - 1])
+    if eb.shape[0] > 1:
+        same = (eb[1:] == eb[:-1]) & (ev[1:] == ev[:-1])
+        reps = np.bincount(eb[1:][same], minlength=Bn).astype(np.int32)
     return lab, lens, reps
 
 

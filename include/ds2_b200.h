@@ -66,8 +66,10 @@ int ds2_ctc_loss_fwd_bwd(const float* logits, int T, int B, int K, const int* la
  * that loads the library until the process exits).  Limits and rules:
  *   - refused with DS2_ERR_WORKSPACE when ds2_ctc_workspace_bytes(T,B,K,Lmax) exceeds that maximum
  *     (the reference's largest dummy bucket at B=32 - T2=366, 209 labels - needs 39.4 MB and fits);
- *   - the first call on each device resolves the array's device address; make it before starting any
- *     stream capture on that device;
+ *   - ds2_ctc_noalloc_max_bytes() is also the set-up call: on the CURRENT device it resolves the array's device
+ *     address (a runtime query, no allocation; with lazy module loading it is also the moment the driver backs
+ *     the array with memory).  Call it once per device BEFORE your own allocator claims the rest of HBM and
+ *     before any stream capture; if you do not, the first compute call on the device does the same set-up;
  *   - the entry point itself calls no cudaMalloc/cudaFree or any allocating routine;
  *   - all calls share the array and it keeps the previous call's contents; each call overwrites every cell
  *     it later reads, so nothing is cleared, but calls that overlap on the GPU (two streams) race on it. */

@@ -109,13 +109,18 @@ def conv_frontend(feats: torch.Tensor, p: Dict[str, torch.Tensor], layout: str =
 
 
 # ----------------------------------------------------------------------------- recurrent cells
-def rnn_cell_step(x_t, h_prev, W, U, b, sbn: str = "as_written"):
-    """src/custom_ops.py:48-72 : h = min(relu(sbn(x W^T) + h U^T + b), 20)."""
+def rnn_cell_preact(x_t, h_prev, W, U, b, sbn: str = "as_written"):
+    """src/custom_ops.py:59-68 : the argument of the clipped ReLU, sbn(x W^T) + h U^T + b."""
     resi = x_t @ W.t()
     if sbn == "as_written":
         resi = seq_batch_norm_as_written(resi)
     resu = h_prev @ U.t()
-    return relux(resi + resu + b, RELU_CAP)
+    return resi + resu + b
+
+
+def rnn_cell_step(x_t, h_prev, W, U, b, sbn: str = "as_written"):
+    """src/custom_ops.py:48-72 : h = min(relu(sbn(x W^T) + h U^T + b), 20)."""
+    return relux(rnn_cell_preact(x_t, h_prev, W, U, b, sbn), RELU_CAP)
 
 
 def gru_cell_step(x_t, h_prev, W, U, bw, bu, sbn: str = "as_written"):
@@ -135,12 +140,14 @@ def gru_cell_step(x_t, h_prev, W, U, bw, bu, sbn: str = "as_written"):
     return (1.0 - z) * n + z * h_prev
 
 
-def rnn_direction(x, lens, cell_params, reverse: bool, cell: str = "relu_clip", sbn: str = "as_written"):
+def rnn_direction(x, lens, cell_params, reverse: bool, cell: str = "relu_clip", sbn: str = "as_written", preacts=None):
     """One direction of tf.nn.bidirectional_dynamic_rnn (src/custom_ops.py:91-93,
     src/deepSpeech.py:179-183), time-major, zero initial state (custom_ops.py:89-90).
     dynamic_rnn semantics (TF-internal): for t >= len[b] the emitted output is zero and the
     state is copied through; the backward direction runs over reverse_sequence(x, len), i.e.
-    over the valid prefix only, and its outputs are reversed back."""
+    over the valid prefix only, and its outputs are reversed back.
+    preacts (relu_clip only): a list of length T that receives the pre-activation tensor of every step (kept in
+    the autograd graph with retain_grad, so that d loss / d pre-activation can be read after backward())."""
     T, B, _ = x.shape
     H = cell_params["U"].shape[1]
     lens_t = torch.as_tensor(np.asarray(lens), dtype=torch.int64)
@@ -148,7 +155,13 @@ def rnn_direction(x, lens, cell_params, reverse: bool, cell: str = "relu_clip", 
     outs = [None] * T
     order = range(T - 1, -1, -1) if reverse else range(T)
     for t in order:
-        if cell == "relu_clip":
+        if cell == "relu_clip" and preacts is not None:
+            z = rnn_cell_preact(x[t], h, cell_params["W"], cell_params["U"], cell_params["B"], sbn)
+            if z.requires_grad:
+                z.retain_grad()
+            preacts[t] = z
+            hn = relux(z, RELU_CAP)
+        elif cell == "relu_clip":
             hn = rnn_cell_step(x[t], h, cell_params["W"], cell_params["U"], cell_params["B"], sbn)
         else:
             hn = gru_cell_step(x[t], h, cell_params["W"], cell_params["U"], cell_params["BW"],

@@ -46,19 +46,31 @@ def _both(x, lab, ll, sl, Lmax):
     loss_a, grad_a = torch.empty(B, device="cuda"), torch.empty_like(x)
     _lib.check(lib.ds2_ctc_loss_fwd_bwd(P(x), T, B, K, P(lab), Lmax, P(ll), P(sl), None, P(loss_a), P(grad_a), P(ws), n, st), "regular")
     loss_b, grad_b = torch.full((B,), float("nan"), device="cuda"), torch.full_like(x, float("nan"))
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]            # cudaMemGetInfo: what the DRIVER has left, not torch's cache
     _lib.check(lib.ds2_ctc_loss_fwd_bwd_noalloc(P(x), T, B, K, P(lab), Lmax, P(ll), P(sl), None, P(loss_b), P(grad_b), st), "noalloc")
     torch.cuda.synchronize()
+    assert torch.cuda.mem_get_info()[0] == free0, "the allocation-free entry point changed the free device memory"
     return loss_a.cpu().numpy(), grad_a.cpu().numpy(), loss_b.cpu().numpy(), grad_b.cpu().numpy()
 
 
 def test_noalloc_matches_regular_entry_point_on_two_calls_in_a_row():
     from deepspeech_b200 import _lib
+    from oracle import ds2_oracle as O
+    # the set-up call comes first, as a caller with its own arena would make it (before that arena claims HBM)
     assert _lib.lib.ds2_ctc_noalloc_max_bytes() == 64 << 20
     for (T, B, L, ragged, seed) in [(366, 32, 209, False, 1), (90, 5, 17, True, 2)]:
-        la, ga, lb, gb = _both(*_case(T, B, L, ragged, seed))
+        x, lab, ll, sl, Lmax = _case(T, B, L, ragged, seed)
+        la, ga, lb, gb = _both(x, lab, ll, sl, Lmax)
         assert np.isfinite(lb).all() and np.isfinite(gb).all()
         assert np.allclose(lb, la, rtol=1e-4, atol=1e-4)
         assert np.abs(gb - ga).max() <= 1e-3 * np.abs(ga).max()
+        # and against the fp64 oracle on the first rows (not only CUDA against CUDA)
+        nb = min(B, 3)
+        labs = [[int(v) for v in lab[b, :int(ll[b])].cpu().numpy()] for b in range(nb)]
+        lo, go = O.ctc_loss_and_grad_np(x[:, :nb].double().cpu().numpy(), labs, sl[:nb].cpu().numpy())
+        assert np.abs(lb[:nb] - lo).max() <= 1e-4 * np.abs(lo).max()
+        assert np.abs(gb[:, :nb] - go).max() <= 1e-3 * np.abs(go).max()
 
 
 def test_noalloc_refuses_problems_beyond_its_built_in_scratch():
