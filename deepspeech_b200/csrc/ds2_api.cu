@@ -97,7 +97,7 @@ int rnn_relu_bwd_generic(const float* dout, const float* u, const int* lens, con
                          int ND, int reverse_mask, float cap, cudaStream_t st);
 int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, int T, int B,
                          int H, int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st);
-int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, const void* hs, void* dz, float* dbias, int T, int B, int H, int ND,
+int rnn_relu_bwd_persist(const float* dout, const void* u, const void* ut, const int* lens, const void* hs, void* dz, float* dbias, int T, int B, int H, int ND,
                          int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st);
 size_t rnn_persist_workspace_bytes(int T, int B, int H, int ND);
 int rnn_persist_supported(int B, int H, int ND);
@@ -148,7 +148,7 @@ extern "C" int ds2_rnn_relu_bwd(const float* dout, const void* u, const int* len
   }
   DS2_REQUIRE(rnn_persist_supported(B, H, ND), DS2_ERR_UNSUPPORTED,
               "ds2_rnn_relu_bwd: persistent bf16 kernel does not take B=%d H=%d ND=%d (use DS2_F32)", B, H, ND);
-  return rnn_relu_bwd_persist(dout, u, lens, hs, dz, dbias, T, B, H, ND, reverse_mask, cap, workspace, workspace_bytes, st);
+  return rnn_relu_bwd_persist(dout, u, nullptr, lens, hs, dz, dbias, T, B, H, ND, reverse_mask, cap, workspace, workspace_bytes, st);
 }
 
 extern "C" size_t ds2_rnn_workspace_bytes(int T, int B, int H, int ND, int dtype) {

@@ -507,3 +507,167 @@ __global__ void __launch_bounds__(256) rnn2_ring_init_kernel(uint4* ring, long n
 }
 
 }  // namespace p2
+
+// ------------------------------------------------------------------ host side
+using namespace p2;
+
+// implemented in ds2_rnn_persistent.cu (round-1 protocol, kept for A/B runs)
+int rnn_relu_fwd_persist_v1(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, int T, int B,
+                            int H, int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st);
+int rnn_relu_bwd_persist_v1(const float* dout, const void* u, const int* lens, const void* hs, void* dz, float* dbias, int T, int B, int H,
+                            int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st);
+size_t rnn_persist_workspace_bytes_v1(int T, int B, int H, int ND);
+
+struct Geom {
+  int tiles_m, ksl, nbox, ni;
+  size_t smem, ring_bytes;
+};
+
+static int geometry(int B, int H, int ND, Geom* g) {
+  if (B % BP != 0 || B < BP || B / BP > MAX_NI || H % 8 != 0 || H < 8 || (ND != 1 && ND != 2)) return 0;
+  const int tm = (H + 127) / 128;
+  const int slice = (H + KS - 1) / KS;
+  const int l = ((slice + 63) / 64) * 64;
+  const int nb = l / 64;
+  if (nb > MAX_NBOX) return 0;
+  const int n_inst = B / BP;
+  if (nb * 32 + n_inst * BP > 512) return 0;   // TMEM columns: resident U + accumulators
+  const size_t bytes = smem_layout(nb, n_inst).total + 1024;
+  if (bytes > 225 * 1024) return 0;
+  if (KS * tm * ND > 128) return 0;            // must be co-resident in clusters of 4 (148 SMs, 1 CTA / SM)
+  if (g) {
+    g->tiles_m = tm; g->ksl = l; g->nbox = nb; g->ni = n_inst; g->smem = bytes;
+    g->ring_bytes = (size_t)ND * n_inst * RING * KS * nb * BOX_BYTES;
+  }
+  return 1;
+}
+
+int rnn_persist_supported(int B, int H, int ND) { return geometry(B, H, ND, nullptr); }
+
+static constexpr size_t WS_CTR_BYTES = 2048;     // round-1 layout prefix: counters, stamps, U^T
+static constexpr size_t WS_PROF_BYTES = 131072;
+
+static size_t ring_offset(int H, int ND) {
+  const size_t o = WS_CTR_BYTES + WS_PROF_BYTES + (size_t)ND * H * H * 2;
+  return (o + 1023) & ~size_t(1023);
+}
+
+size_t rnn_persist_workspace_bytes(int T, int B, int H, int ND) {
+  (void)T;
+  Geom g;
+  if (!geometry(B, H, ND, &g)) return rnn_persist_workspace_bytes_v1(T, B, H, ND);
+  return ring_offset(H, ND) + g.ring_bytes + (size_t)(NCOPY + 1) * 4096;     // + the counter copies, each in its own 4 KB block
+}
+
+template <bool BWD, int NIMAX, int NBOX>
+static int launch_nb(const CUtensorMap& ta, Params& p, size_t smem, cudaStream_t st) {
+  auto kern = rnn2_kernel<BWD, NIMAX, NBOX>;
+  static unsigned long long attr_done_devs = 0;
+  if (first_use_on_device(&attr_done_devs)) {
+    DS2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(KS, p.tiles_m, p.ND);
+  cfg.blockDim = dim3(INST_THREADS * p.NI);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attrs[2];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = KS;
+  attrs[0].val.clusterDim.y = 1;
+  attrs[0].val.clusterDim.z = 1;
+  attrs[1].id = cudaLaunchAttributeCooperative;       // all CTAs co-resident (they wait on each other's data)
+  attrs[1].val.cooperative = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs = use_cooperative_launch() ? 2 : 1;    // profilers cannot replay cooperative launches
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, p);
+  if (e != cudaSuccess && cfg.numAttrs == 2) {
+    // some driver versions reject cooperative + cluster launches: the grid (<= 128 CTAs, 1 per SM) fits the device anyway
+    (void)cudaGetLastError();
+    cfg.numAttrs = 1;
+    e = cudaLaunchKernelEx(&cfg, kern, ta, p);
+  }
+  if (e != cudaSuccess) return cuda_fail(e, BWD ? "rnn2_kernel<bwd>" : "rnn2_kernel<fwd>");
+  count_launch();
+  return DS2_OK;
+}
+
+template <bool BWD, int NIMAX>
+static int launch_ni(const CUtensorMap& ta, Params& p, size_t smem, cudaStream_t st) {
+  if (p.nbox == 7) return launch_nb<BWD, NIMAX, 7>(ta, p, smem, st);     // H = 1760 (train.sh)
+  if (p.nbox == 4) return launch_nb<BWD, NIMAX, 4>(ta, p, smem, st);     // H = 800 .. 1024
+  return launch_nb<BWD, NIMAX, 0>(ta, p, smem, st);
+}
+
+template <bool BWD>
+static int launch(const CUtensorMap& ta, Params& p, size_t smem, cudaStream_t st) {
+  return p.NI <= 2 ? launch_ni<BWD, 2>(ta, p, smem, st) : launch_ni<BWD, MAX_NI>(ta, p, smem, st);
+}
+
+static int common_setup(Params& p, Geom& g, int T, int B, int H, int ND, void* ws, size_t ws_bytes, const char* who, cudaStream_t st) {
+  DS2_REQUIRE(geometry(B, H, ND, &g), DS2_ERR_UNSUPPORTED, "%s: persistent kernel does not take B=%d H=%d ND=%d", who, B, H, ND);
+  const size_t need = rnn_persist_workspace_bytes(T, B, H, ND);
+  DS2_REQUIRE(ws && ws_bytes >= need, DS2_ERR_WORKSPACE, "%s: workspace of %zu bytes required", who, need);
+  DS2_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, DS2_ERR_BAD_ARG, "%s: workspace must be 256-byte aligned", who);
+  p.tiles_m = g.tiles_m; p.ksl = g.ksl; p.nbox = g.nbox; p.NI = g.ni;
+  p.ring = reinterpret_cast<unsigned char*>(ws) + ring_offset(H, ND);
+  p.ctr = reinterpret_cast<unsigned int*>((reinterpret_cast<uintptr_t>(p.ring) + g.ring_bytes + 4095) & ~uintptr_t(4095));
+  p.exp = env().rnn_exp;
+  p.slab16 = env().rnn_slab_f32 ? 0 : 1;
+  p.prof = env().rnn_prof ? reinterpret_cast<long long*>(static_cast<char*>(ws) + WS_CTR_BYTES) : nullptr;
+  const long n_units = (long)(g.ring_bytes / 16);
+  int blocks = (int)((n_units + 255) / 256);
+  if (blocks > 4 * num_sms()) blocks = 4 * num_sms();
+  rnn2_ring_init_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<uint4*>(p.ring), n_units, g.nbox, g.ksl, H, p.ctr, NCOPY * CTR_COPY_STRIDE);
+  DS2_LAUNCH_CHECK("rnn2_ring_init_kernel");
+  count_launch();
+  return DS2_OK;
+}
+
+int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, int T, int B,
+                         int H, int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
+  if (env().rnn_v1) return rnn_relu_fwd_persist_v1(wx, scale, u, bias, lens, hs, T, B, H, ND, reverse_mask, cap, ws, ws_bytes, st);
+  Params p = {};
+  Geom g;
+  int rc = common_setup(p, g, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_fwd", st);
+  if (rc) return rc;
+  CUtensorMap ta;
+  rc = make_tmap_2d_bf16(&ta, u, H, (uint64_t)ND * H, H, 64, 128);
+  if (rc) return rc;
+  p.add_in = wx; p.bias = bias; p.lens = lens; p.hs_in = nullptr; p.out = static_cast<__nv_bfloat16*>(hs);
+  p.out_row_pitch = H; p.out_dir_stride = (long)T * B * H;
+  p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = scale; p.cap = cap;
+  return launch<false>(ta, p, g.smem, st);
+}
+
+// The backward contraction is U^T dz: `ut_in` (bf16 [ND,H,H], ut[d][k][j] = U[d][j][k]) is the resident A operand.  When
+// the caller has no transposed copy (ut_in == nullptr) U is transposed into the workspace first.
+int rnn_relu_bwd_persist(const float* dout, const void* u, const void* ut_in, const int* lens, const void* hs, void* dz, float* dbias, int T,
+                         int B, int H, int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
+  if (env().rnn_v1) return rnn_relu_bwd_persist_v1(dout, u, lens, hs, dz, dbias, T, B, H, ND, reverse_mask, cap, ws, ws_bytes, st);
+  Params p = {};
+  Geom g;
+  int rc = common_setup(p, g, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_bwd", st);
+  if (rc) return rc;
+  const void* ut = ut_in;
+  if (!ut) {
+    __nv_bfloat16* utw = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + WS_CTR_BYTES + WS_PROF_BYTES);
+    for (int d = 0; d < ND; ++d) {
+      rc = ds2_transpose(static_cast<const __nv_bfloat16*>(u) + (size_t)d * H * H, DS2_BF16, H, H, H, utw + (size_t)d * H * H, DS2_BF16, H, st);
+      if (rc) return rc;
+    }
+    ut = utw;
+  }
+  CUtensorMap ta;
+  rc = make_tmap_2d_bf16(&ta, ut, H, (uint64_t)ND * H, H, 64, 128);
+  if (rc) return rc;
+  p.add_in = dout; p.bias = nullptr; p.lens = lens; p.hs_in = static_cast<const __nv_bfloat16*>(hs);
+  p.dbias = dbias;
+  if (dbias) DS2_CUDA(cudaMemsetAsync(dbias, 0, (size_t)ND * H * sizeof(float), st));
+  p.out = static_cast<__nv_bfloat16*>(dz);
+  p.out_row_pitch = (long)ND * H; p.out_dir_stride = H;
+  p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = 1.f; p.cap = cap;
+  return launch<true>(ta, p, g.smem, st);
+}
+
+}  // namespace ds2

@@ -475,12 +475,11 @@ static int persist_geometry(int B, int H, int ND, int* tiles_m, int* ksl, int* n
   return 1;
 }
 
-int rnn_persist_supported(int B, int H, int ND) { return persist_geometry(B, H, ND, nullptr, nullptr, nullptr, nullptr, nullptr); }
 
 static constexpr size_t WS_CTR_BYTES = 2048;     // ND x MAX_NI counters, one 128-byte line each
 static constexpr size_t WS_PROF_BYTES = 131072;
 
-size_t rnn_persist_workspace_bytes(int T, int B, int H, int ND) {
+size_t rnn_persist_workspace_bytes_v1(int T, int B, int H, int ND) {
   (void)T; (void)B;
   // optional profile stamps + room for U^T (bf16) used by the backward
   return WS_CTR_BYTES + WS_PROF_BYTES + (size_t)ND * H * H * 2;
@@ -529,7 +528,7 @@ static int persist_common(RnnPersistParams& p, size_t* smem, int T, int B, int H
                           cudaStream_t st) {
   DS2_REQUIRE(persist_geometry(B, H, ND, &p.tiles_m, &p.ksl, &p.nbox, &p.NI, smem), DS2_ERR_UNSUPPORTED,
               "%s: persistent kernel does not take B=%d H=%d ND=%d", who, B, H, ND);
-  const size_t need = rnn_persist_workspace_bytes(T, B, H, ND);
+  const size_t need = rnn_persist_workspace_bytes_v1(T, B, H, ND);
   DS2_REQUIRE(ws && ws_bytes >= need, DS2_ERR_WORKSPACE, "%s: workspace of %zu bytes required", who, need);
   DS2_CUDA(cudaMemsetAsync(ws, 0, WS_CTR_BYTES, st));
   p.ctr = static_cast<unsigned int*>(ws);
@@ -540,7 +539,7 @@ static int persist_common(RnnPersistParams& p, size_t* smem, int T, int B, int H
   return DS2_OK;
 }
 
-int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, int T, int B,
+int rnn_relu_fwd_persist_v1(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, int T, int B,
                          int H, int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
   RnnPersistParams p = {};
   size_t smem;
@@ -558,7 +557,7 @@ int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const floa
 
 // The backward contraction is U^T dz: U is transposed per direction into the workspace first
 // (ut[d][k][j] = U[d][j][k], 2*ND*H*H bytes, one small kernel per direction), then used as the resident A operand.
-int rnn_relu_bwd_persist(const float* dout, const void* u, const int* lens, const void* hs, void* dz, float* dbias, int T, int B, int H,
+int rnn_relu_bwd_persist_v1(const float* dout, const void* u, const int* lens, const void* hs, void* dz, float* dbias, int T, int B, int H,
                          int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
   RnnPersistParams p = {};
   size_t smem;

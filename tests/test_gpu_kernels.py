@@ -502,3 +502,55 @@ def test_bigru_layer_bf16_persistent_vs_oracle(T, B, I, H, ragged):
     assert relerr(U.grad.cpu().numpy(), torch.stack([lp["fw"]["U"].grad, lp["bw"]["U"].grad], 0).numpy()) < 3e-2
     assert relerr(BW.grad.cpu().numpy(), torch.stack([lp["fw"]["BW"].grad, lp["bw"]["BW"].grad], 0).numpy()) < 3e-2
     assert relerr(BU.grad.cpu().numpy(), torch.stack([lp["fw"]["BU"].grad, lp["bw"]["BU"].grad], 0).numpy()) < 3e-2
+
+
+def test_rnn_persistent_refetch_path_and_v1_agree():
+    """The round-2 exchange protocol of the persistent recurrence (ds2_rnn_persist2.cu): with DS2_RNN_EXP=1 the image
+    check reports 'stale' once every 5th step, which drives the re-fetch path; the result must be bit-identical to the
+    normal run.  The round-1 kernel (DS2_RNN_V1=1, fp32 slab exchange on both sides so that the arithmetic is the same)
+    must agree with it bit for bit as well, forward and backward."""
+    import os
+    ops = _ops()
+    from deepspeech_b200._lib import DS2_BF16, check, lib
+    T, B, H = 23, 32, 1760
+    g = torch.Generator(device="cuda").manual_seed(17)
+    wx = torch.randn((T, B, 2 * H), device="cuda", generator=g) * 0.7
+    U = (torch.randn((2, H, H), device="cuda", generator=g) * (0.6 / H ** 0.5)).to(torch.bfloat16)
+    bias = torch.randn((2, H), device="cuda", generator=g) * 0.1
+    dout = torch.randn((T, B, H), device="cuda", generator=g)
+    lens = torch.tensor([T] + list(np.random.default_rng(3).integers(1, T + 1, size=B - 1)), dtype=torch.int32, device="cuda")
+    p, st = ops._p, ops._stream
+    wsb = lib.ds2_rnn_workspace_bytes(T, B, H, 2, DS2_BF16)
+    ws = torch.empty(wsb, dtype=torch.uint8, device="cuda")
+
+    def run():
+        hs = torch.empty((2, T, B, H), dtype=torch.bfloat16, device="cuda")
+        dz = torch.empty((T, B, 2 * H), dtype=torch.bfloat16, device="cuda")
+        db = torch.empty((2, H), device="cuda")
+        check(lib.ds2_rnn_relu_fwd(p(wx), 1.0, p(U), p(bias), p(lens), p(hs), DS2_BF16, T, B, H, 2, 2, 20.0, p(ws), wsb, st()), "fwd")
+        check(lib.ds2_rnn_relu_bwd(p(dout), p(U), p(lens), p(hs), p(dz), p(db), DS2_BF16, T, B, H, 2, 2, 20.0, p(ws), wsb, st()), "bwd")
+        torch.cuda.synchronize()
+        return hs, dz, db
+
+    saved = {k: os.environ.get(k) for k in ("DS2_RNN_EXP", "DS2_RNN_V1", "DS2_RNN_SLAB_F32")}
+    try:
+        os.environ["DS2_RNN_SLAB_F32"] = "1"
+        lib.ds2_debug_reload_env()
+        base = run()
+        os.environ["DS2_RNN_EXP"] = "1"
+        lib.ds2_debug_reload_env()
+        forced = run()
+        os.environ.pop("DS2_RNN_EXP")
+        os.environ["DS2_RNN_V1"] = "1"
+        lib.ds2_debug_reload_env()
+        v1 = run()
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+        lib.ds2_debug_reload_env()
+    for a, b_, c in zip(base, forced, v1):
+        assert torch.equal(a, b_)
+        assert torch.equal(a[..., :] if a.dtype != torch.float32 else a, c) if a.dtype != torch.float32 else torch.allclose(a, c, rtol=1e-5, atol=1e-5)

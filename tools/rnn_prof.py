@@ -34,18 +34,33 @@ for it in range(3):
 print("T=%d H=%d B=%d: fwd kernel %.3f ms  (%.2f us/step)" % (T, H, B, e0.elapsed_time(e1), e0.elapsed_time(e1) * 1e3 / T))
 n = min(T, 1024)
 S = ws[2048:2048 + n * 128].view(torch.int64).cpu().numpy().reshape(-1, 16)
-s, nxt = S[2:n - 1], S[3:n]
-seq = [("acquire counter + bar.sync", 8, 15), ("load h_{t-1} slice (7 x 16 B / thread)", 15, 9), ("swizzled st.shared", 9, 13), ("fence.proxy.async.shared::cta", 13, 14), ("mbarrier.arrive", 14, 10),
-       ("loaders arrived -> control sees b_ready", 10, 0), ("MMAs + commit issued", 0, 1), ("commit -> epilogue sees accumulators", 1, 3),
-       ("tcgen05.ld", 3, 11), ("st.async partial slabs issued", 11, 12), ("all 4 slabs arrived", 12, 5),
-       ("reduce + epilogue + h_t store issued", 5, 6), ("bar.sync + red.release issued", 6, 7)]
+s, nxt = S[10:n - 1], S[11:n]
+if os.environ.get("DS2_RNN_V1"):
+    seq = [("acquire counter + bar.sync", 8, 15), ("load h_{t-1} slice (7 x 16 B / thread)", 15, 9), ("swizzled st.shared", 9, 13), ("fence.proxy.async.shared::cta", 13, 14), ("mbarrier.arrive", 14, 10),
+           ("loaders arrived -> control sees b_ready", 10, 0), ("MMAs + commit issued", 0, 1), ("commit -> epilogue sees accumulators", 1, 3),
+           ("tcgen05.ld", 3, 11), ("st.async partial slabs issued", 11, 12), ("all 4 slabs arrived", 12, 5),
+           ("reduce + epilogue + h_t store issued", 5, 6), ("bar.sync + red.release issued", 6, 7)]
+    last, first = 7, 8
+else:
+    # round-2 protocol: control thread stamps 0, 1, 4; first epilogue thread 13, 8, 9..12
+    seq = [("control: wait for the step counter", 0, 1), ("bulk copy landed (seen by the epilogue warp)", 1, 13),
+           ("image checked + arrive", 13, 8), ("accumulators + verdict seen", 8, 9),
+           ("tcgen05.ld + st.async partial slabs issued", 9, 10), ("all 4 slabs arrived", 10, 11),
+           ("reduce + epilogue + stores + counter red", 11, 12)]
+    last, first = 12, 0
 tot = 0.0
 for name, a, b in seq:
     g = (s[:, b] - s[:, a]).astype(np.float64)
     print("%-46s mean %8.1f cyc   median %8.1f   p90 %8.1f" % (name, g.mean(), np.median(g), np.percentile(g, 90)))
     tot += g.mean()
-g = (nxt[:, 8] - s[:, 7]).astype(np.float64)
-print("%-46s mean %8.1f cyc" % ("published -> next step's poll start", g.mean()))
+g = (nxt[:, first] - s[:, last]).astype(np.float64)
+print("%-46s mean %8.1f cyc" % ("published -> next step starts (negative: the control thread is already waiting)", g.mean()))
 print("sum %.0f cycles per step" % (tot + g.mean()))
-r = s[:, 2].astype(np.float64)
-print("reloads of not-yet-visible rows by the stamping thread: mean %.2f per step, steps with any: %.0f %%" % (r.mean(), 100.0 * (r > 0).mean()))
+if os.environ.get("DS2_RNN_V1"):
+    r = s[:, 2].astype(np.float64)
+    print("reloads of not-yet-visible rows by the stamping thread: mean %.2f per step, steps with any: %.0f %%" % (r.mean(), 100.0 * (r > 0).mean()))
+else:
+    g = (s[:, 4] - s[:, 1]).astype(np.float64)
+    print("control: counter seen -> copy landed, MMAs issued, commit: mean %.1f cyc;  re-fetches: %d" % (g.mean(), int(S[:, 7].sum())))
+    g = (s[:, 12] - s[:, 1]).astype(np.float64)
+    print("counter seen -> own publication: mean %.1f cyc  (the rest of the step is the wait for the other CTAs)" % g.mean())
