@@ -95,7 +95,7 @@ int rnn_relu_fwd_generic(const float* wx, float scale, const float* u, const flo
                          int B, int H, int ND, int reverse_mask, float cap, cudaStream_t st);
 int rnn_relu_bwd_generic(const float* dout, const float* u, const int* lens, const float* hs, float* dz, int T, int B, int H,
                          int ND, int reverse_mask, float cap, cudaStream_t st);
-int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, int T, int B,
+int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, float* hs32, int T, int B,
                          int H, int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st);
 int rnn_relu_bwd_persist(const float* dout, const void* u, const void* ut, const int* lens, const void* hs, void* dz, float* dbias, int T, int B, int H, int ND,
                          int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st);
@@ -130,7 +130,19 @@ extern "C" int ds2_rnn_relu_fwd(const float* wx, float scale, const void* u, con
                                 reverse_mask, cap, st);
   DS2_REQUIRE(rnn_persist_supported(B, H, ND), DS2_ERR_UNSUPPORTED,
               "ds2_rnn_relu_fwd: persistent bf16 kernel does not take B=%d H=%d ND=%d (use DS2_F32)", B, H, ND);
-  return rnn_relu_fwd_persist(wx, scale, u, bias, lens, hs, T, B, H, ND, reverse_mask, cap, workspace, workspace_bytes, st);
+  return rnn_relu_fwd_persist(wx, scale, u, bias, lens, hs, nullptr, T, B, H, ND, reverse_mask, cap, workspace, workspace_bytes, st);
+}
+
+extern "C" int ds2_rnn_relu_fwd_ex(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, float* hs_f32,
+                                   int T, int B, int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes,
+                                   void* stream) {
+  int rc = rnn_check(wx, u, bias, hs, T, B, H, ND, DS2_BF16);
+  if (rc) return rc;
+  DS2_REQUIRE(lens, DS2_ERR_BAD_ARG, "ds2_rnn_relu_fwd_ex: lens is null");
+  DS2_REQUIRE(rnn_persist_supported(B, H, ND), DS2_ERR_UNSUPPORTED,
+              "ds2_rnn_relu_fwd_ex: persistent bf16 kernel does not take B=%d H=%d ND=%d", B, H, ND);
+  return rnn_relu_fwd_persist(wx, scale, u, bias, lens, hs, hs_f32, T, B, H, ND, reverse_mask, cap, workspace, workspace_bytes,
+                              static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int ds2_rnn_relu_bwd(const float* dout, const void* u, const int* lens, const void* hs, void* dz, float* dbias,

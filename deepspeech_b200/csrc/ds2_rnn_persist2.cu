@@ -54,6 +54,7 @@ struct Params {
   const __nv_bfloat16* hs_in;   // bwd: hs [ND,T,B,H] (activation mask)
   float* dbias;            // bwd, optional: [ND,H]
   __nv_bfloat16* out;      // fwd: hs [ND,T,B,H] ; bwd: dz [T,B,ND*H]
+  float* out32;            // fwd, optional: the same hidden states before their rounding to bf16, [ND,T,B,H] fp32
   unsigned char* ring;     // [ND][NI][RING][KS][nbox*BOX_BYTES]
   unsigned int* ctr;       // NCOPY x [ND][NI] step counters, 32 uints apart, copies CTR_COPY_STRIDE apart
   long long* prof;         // optional stage stamps of CTA (0,0,0) instance 0, 16 per step
@@ -335,6 +336,7 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
     const long hm_inc = t_inc * (long)Bn * H;
     __nv_bfloat16* out_ptr = p.out + (size_t)d * p.out_dir_stride + ((size_t)t_first * Bn + b) * p.out_row_pitch + j;
     const long out_inc = t_inc * (long)Bn * p.out_row_pitch;
+    float* out32_ptr = (!BWD && p.out32) ? p.out32 + (((size_t)d * T + t_first) * Bn + b) * H + j : nullptr;
     float dbs[4] = {0.f, 0.f, 0.f, 0.f};         // backward: running sum over time of this thread's dz (bias gradient)
     uint32_t phc = 0, pho = 0, phm = 0, phs = 0, vround = 0;
     int t = t_first;
@@ -460,6 +462,10 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
         st_relaxed_b64(ring_cell + (size_t)(step % RING) * slot_stride, pk.x, pk.y);
         st_relaxed_b64(ring_cell + (size_t)((step + 2) % RING) * slot_stride, 0xFFFFFFFFu, 0xFFFFFFFFu);
         *reinterpret_cast<uint2*>(out_ptr) = pk;
+        if (!BWD && out32_ptr) {
+          *reinterpret_cast<float4*>(out32_ptr) = make_float4(o[0], o[1], o[2], o[3]);
+          out32_ptr += out_inc;            // fwd: the fp32 tensor has the pitch of the bf16 one
+        }
       }
       // publish: one relaxed increment per counter copy after the warp's stores (no fence: the image validates itself)
       __syncwarp();
@@ -624,9 +630,12 @@ static int common_setup(Params& p, Geom& g, int T, int B, int H, int ND, void* w
   return DS2_OK;
 }
 
-int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, int T, int B,
+int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, float* hs32, int T, int B,
                          int H, int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
-  if (env().rnn_v1) return rnn_relu_fwd_persist_v1(wx, scale, u, bias, lens, hs, T, B, H, ND, reverse_mask, cap, ws, ws_bytes, st);
+  if (env().rnn_v1) {
+    DS2_REQUIRE(!hs32, DS2_ERR_UNSUPPORTED, "ds2_rnn_relu_fwd_ex: the round-1 kernel (DS2_RNN_V1) has no fp32 output");
+    return rnn_relu_fwd_persist_v1(wx, scale, u, bias, lens, hs, T, B, H, ND, reverse_mask, cap, ws, ws_bytes, st);
+  }
   Params p = {};
   Geom g;
   int rc = common_setup(p, g, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_fwd", st);
@@ -635,6 +644,7 @@ int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const floa
   rc = make_tmap_2d_bf16(&ta, u, H, (uint64_t)ND * H, H, 64, 128);
   if (rc) return rc;
   p.add_in = wx; p.bias = bias; p.lens = lens; p.hs_in = nullptr; p.out = static_cast<__nv_bfloat16*>(hs);
+  p.out32 = hs32;
   p.out_row_pitch = H; p.out_dir_stride = (long)T * B * H;
   p.T = T; p.B = B; p.H = H; p.ND = ND; p.reverse_mask = reverse_mask; p.scale = scale; p.cap = cap;
   return launch<false>(ta, p, g.smem, st);

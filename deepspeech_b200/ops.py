@@ -403,6 +403,24 @@ def rnn_path_dtype(B: int, H: int, ND: int, want_bf16: bool):
     return torch.float32
 
 
+import os as _os0
+USE_FP32_LAYER_SUM = _os0.environ.get("DS2_NO_FP32_LAYER_SUM") is None and _os0.environ.get("DS2_RNN_V1") is None
+
+
+def _relu_recurrence_fwd(wx, Ug, bias, lens, hs, T, B, H, ND, reverse_mask, ws, wsb):
+    """Runs the forward recurrence into hs [ND,T,B,H] and returns the tensor the layer output fw + bw
+    (src/custom_ops.py:95) is formed from: on the bf16 path the kernel's fp32 copy of the hidden states (values before
+    their rounding to bf16: the layer output is then rounded once instead of three times), else hs itself."""
+    if hs.dtype == torch.bfloat16 and USE_FP32_LAYER_SUM:
+        hs32 = torch.empty((ND, T, B, H), dtype=torch.float32, device=hs.device)
+        check(lib.ds2_rnn_relu_fwd_ex(_p(wx), SBN_SCALE, _p(Ug), _p(bias), _p(lens), _p(hs), _p(hs32), T, B, H, ND,
+                                      reverse_mask, RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_fwd_ex")
+        return hs32
+    check(lib.ds2_rnn_relu_fwd(_p(wx), SBN_SCALE, _p(Ug), _p(bias), _p(lens), _p(hs), _dt(hs), T, B, H, ND,
+                               reverse_mask, RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_fwd")
+    return hs
+
+
 class _BiRNNLayerFn(torch.autograd.Function):
     """One (bi)directional clipped-ReLU layer over the whole sequence:
          wx = x . Wcat^T            (one batched GEMM, all timesteps, both directions)
@@ -425,12 +443,11 @@ class _BiRNNLayerFn(torch.autograd.Function):
         hs = torch.empty((ND, T, B, H), dtype=cdt, device=dev)
         wsb = lib.ds2_rnn_workspace_bytes(T, B, H, ND, _dt(hs))
         ws = _workspace(wsb, dev, "rnn") if wsb else None
-        check(lib.ds2_rnn_relu_fwd(_p(wx), SBN_SCALE, _p(Ug), _p(bias), _p(lens), _p(hs), _dt(hs), T, B, H, ND,
-                                   reverse_mask, RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_fwd")
+        src = _relu_recurrence_fwd(wx, Ug, bias, lens, hs, T, B, H, ND, reverse_mask, ws, wsb)
         if ND == 2:
-            out = add2(hs[0], hs[1], out_dtype)
+            out = add2(src[0], src[1], out_dtype)
         else:
-            out = cast(hs[0], out_dtype)
+            out = cast(src[0], out_dtype)
         ctx.save_for_backward(xg, Wg, Ug, hs, lens)
         ctx.meta = (T, B, I, H, ND, reverse_mask, x.dtype)
         return out
@@ -634,13 +651,14 @@ class _RecStackFn(torch.autograd.Function):
                 bias = params[l * npl + 2]
                 wsb = lib.ds2_rnn_workspace_bytes(T, B, H, ND, DS2_BF16)
                 ws = _workspace(wsb, dev, "rnn")
-                check(lib.ds2_rnn_relu_fwd(_p(wx), SBN_SCALE, _p(Ug), _p(bias), _p(lens), _p(hs), DS2_BF16, T, B, H, ND,
-                                           reverse_mask, RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_fwd")
+                src = _relu_recurrence_fwd(wx, Ug, bias, lens, hs, T, B, H, ND, reverse_mask, ws, wsb)
                 saved += [cur, Wg, Ug, hs]
             metas.append((I, H, ND))
             last = l == L - 1
             odt = out_dtype if last else torch.bfloat16
-            cur = add2(hs[0], hs[1], odt) if ND == 2 else cast(hs[0], odt)
+            if gru:
+                src = hs
+            cur = add2(src[0], src[1], odt) if ND == 2 else cast(src[0], odt)
         ctx.save_for_backward(lens, *saved)
         ctx.meta = (T, B, gru, reverse_mask, L, metas, x.dtype)
         ctx.param_objs = params                     # identities only: handed to STACK_GRAD_HOOK with their gradients

@@ -115,6 +115,12 @@ int ds2_gemm_generic(const void* A, int a_dtype, long sam, long sak, const void*
 int ds2_rnn_relu_fwd(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, int dtype,
                      int T, int B, int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes,
                      void* stream);
+/* ds2_rnn_relu_fwd on the bf16 tensor-core path with one more output: hs_f32 [ND,T,B,H] (may be NULL) receives the
+ * hidden states BEFORE their rounding to bf16, so that the caller can form the layer output fw + bw
+ * (src/custom_ops.py:95) from unrounded values - one rounding per layer instead of three. */
+int ds2_rnn_relu_fwd_ex(const float* wx, float scale, const void* u, const float* bias, const int* lens, void* hs, float* hs_f32,
+                        int T, int B, int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes,
+                        void* stream);
 int ds2_rnn_relu_bwd(const float* dout, const void* u, const int* lens, const void* hs, void* dz, float* dbias, int dtype, int T,
                      int B, int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes, void* stream);
 size_t ds2_rnn_workspace_bytes(int T, int B, int H, int ND, int dtype);

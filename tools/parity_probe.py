@@ -5,7 +5,8 @@ layer and at the logits:  usage: tools/parity_probe.py [variant ...]
   base        the shipped bf16 path
   fe32        fp32 front-end (direct conv kernels), bf16 recurrent stack
   w16         oracle run on bf16-ROUNDED weights (isolates the weight rounding)
-  slab32      DS2_RNN_SLAB_F32=1 (fp32 partial sums across the cluster)"""
+  slab32      DS2_RNN_SLAB_F32=1 (fp32 partial sums across the cluster)
+  sum16       layer output fw + bw formed from the bf16-rounded hidden states (round 1 behaviour)"""
 import os
 import sys
 import time
@@ -52,6 +53,7 @@ ref_w16 = oracle(True)[0] if "w16" in variants else None
 print("oracle: %.0f s" % (time.time() - t0))
 lens_d = torch.from_numpy(np.asarray(lens, np.int32)).cuda()
 for v in variants:
+    ops.USE_FP32_LAYER_SUM = v not in ("sum16",)
     if v == "slab32":
         os.environ["DS2_RNN_SLAB_F32"] = "1"
     else:
