@@ -106,33 +106,51 @@ def step_flops(B, T, H, L, nf=32, cell="relu_clip"):
     return 3.0 * (conv + rnn + fc), 3.0 * rnn, T2
 
 
+def _pick_cpu_bucket(timer, batch, n_steps, budget_s):
+    """Largest dummy bucket whose n_steps steps fit budget_s seconds.  Step time grows faster than linearly with the
+    bucket length on some hosts (measured: 1.1 s at T=100, 7.6 s at T=400, 131 s at T=1500 on 8 cores), so the buckets
+    are probed in increasing order with one real step each, and a longer one is only tried when a quadratic
+    extrapolation of the last measurement still fits.  Parameter construction is not part of any probe."""
+    t0 = time.perf_counter()
+    timer.step(batch, 0)                               # warm-up (allocator, thread pool)
+    chosen, T_c, t_c = 0, 100, timer.step(batch, 0)[0]
+    for b, T in ((1, 200), (3, 400), (7, 800), (14, 1500)):
+        pred = t_c * (T / float(T_c)) ** 2
+        spent = time.perf_counter() - t0
+        if pred * (n_steps + 1) > budget_s or spent + pred > budget_s:
+            break
+        t = timer.step(batch, b)[0]
+        if t * n_steps > budget_s:
+            break
+        chosen, T_c, t_c = b, T, t
+    return chosen, T_c, t_c
+
+
 def reference_arm(args, rank):
     """The reference's own TF-CPU path is unavailable (no tensorflow, py2 source): time the oracle's fp32
-    torch-CPU port of the same step on this box's host cores (kind 'port')."""
+    torch-CPU port of the same step on this box's host cores (kind 'port'), on the bench workload's own bucket when the
+    K + W steps fit ~4 minutes, else on the largest bucket that does (stated in the line)."""
     if rank != 0:
         return
     from oracle import ds2_cpu_baseline as cb
     threads = os.cpu_count() or 1
-    # bounded sample: pick the dummy bucket so that (K+W) steps end within ~2.5 minutes
-    t0 = time.perf_counter()
-    cb.time_steps(args.batch, 0, 1, 0, threads, args.hidden, args.layers)
-    est100 = time.perf_counter() - t0
-    budget = 150.0 / max(1, args.steps + args.warmup)
-    bucket = 0
-    for b, T in ((1, 200), (3, 400), (7, 800), (14, 1500)):
-        if est100 * (T / 100.0) * 1.1 <= budget:
-            bucket = b
-    val, ms, loss = cb.time_steps(args.batch, bucket, args.steps, args.warmup, threads, args.hidden, args.layers)
-    frames = cb.O.UTT_LENGTHS[bucket]
-    sample = "dummy bucket T=%d frames x B=%d (%.0f audio-s per step), %d warm-up + %d timed steps, fp32 torch-CPU port" % (
-        frames, args.batch, args.batch * frames / 100.0, args.warmup, args.steps)
-    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+    timer = cb.StepTimer(threads, args.hidden, args.layers)
+    bucket, frames, est100 = _pick_cpu_bucket(timer, args.batch, args.steps + args.warmup, 240.0)
+    r = timer.run(args.batch, bucket, args.steps, args.warmup)
+    same = frames == args.frames
+    sample = "dummy bucket T=%d frames x B=%d (%.0f audio-s per step), %d warm-up + %d timed steps, fp32 torch-CPU port%s" % (
+        frames, args.batch, r["audio_s_per_step"], args.warmup, args.steps,
+        "" if same else " (the T=%d bucket does not fit the time budget on this host: one step of this bucket takes %.1f s)" % (args.frames, est100))
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "DS2 dummy-data training step (train.sh: B=%d, %d bi-RNN layers, H=%d, 32 filters), CPU sample: %s"
-                       % (args.batch, args.layers, args.hidden, sample)},
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
-            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "config": {"workload": "DS2 dummy-data training step (fwd+bwd+CTC), train.sh config: B=%d/GPU, %d-layer bi-RNN(clipped ReLU) H=%d, "
+                                   "32 conv filters, bucket T=%d frames, stacked wiring, no optimizer; CPU sample: %s"
+                                   % (args.batch, args.layers, args.hidden, frames, sample),
+                       "global_batch": args.batch, "frames": frames, "same_bucket_as_gpu_arm": same},
+            "step_ms": {"min": r["ms_min"], "median": r["ms_median"], "max": r["ms_max"]},
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "note": "reference TF-1.x CPU path unavailable on this box (no tensorflow; py2-only source): oracle port timed instead"}
     print(json.dumps(line), flush=True)
 
@@ -403,19 +421,24 @@ def extras(args, dev, model, ops, _lib, B, T2, H, L, peak_tf, peak_hbm, peak_src
                                  "note": "Adam + EMA, one launch, 20 B read + 16 B written per parameter; not in the timed step"}
     except Exception as e:  # noqa: BLE001 - reported, never fatal for the headline
         out["optimizer_step"] = {"error": str(e)}
-    # ---- CPU baseline on this box's host cores (bounded sample)
+    # ---- CPU baseline on this box's host cores (bounded sample: 3 warm-up + 5 timed steps on the largest bucket that
+    #      keeps them within ~45 s)
     if args.gpus == 1:
         from oracle import ds2_cpu_baseline as cb
         threads = os.cpu_count() or 1
-        val, ms, _ = cb.time_steps(B, 0, 2, 1, threads, H, L)
-        out["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                               "sample": "dummy bucket T=100 frames x B=%d (%.0f audio-s/step), 1 warm-up + 2 timed steps, fp32 torch-CPU "
-                                         "port of the same step (reference TF path unavailable on this box)" % (B, B * 1.0),
-                               "ms_per_step": ms}
+        timer = cb.StepTimer(threads, H, L)
+        bucket, frames, _ = _pick_cpu_bucket(timer, B, 8, 45.0)
+        r = timer.run(B, bucket, 5, 3)
+        out["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": threads, "kind": "port",
+                               "sample": "dummy bucket T=%d frames x B=%d (%.0f audio-s/step), 3 warm-up + 5 timed steps, fp32 torch-CPU "
+                                         "port of the same step (reference TF path unavailable on this box)" % (frames, B, r["audio_s_per_step"]),
+                               "ms_per_step": r["ms_per_step"], "step_ms": {"min": r["ms_min"], "median": r["ms_median"], "max": r["ms_max"]}}
         if threads > 8:
             # the reference's own setting: OMP_NUM_THREADS=8 / intra_op=8 (src/setenvs.py:22-23, src/deepSpeech_train.py:518-523)
-            val8, ms8, _ = cb.time_steps(B, 0, 2, 1, 8, H, L)
-            out["cpu_baseline"]["at_8_threads"] = {"value": val8, "ms_per_step": ms8}
+            t8 = cb.StepTimer(8, H, L)
+            t8.step(B, bucket)
+            r8 = t8.run(B, bucket, 2, 0)
+            out["cpu_baseline"]["at_8_threads"] = {"value": r8["value"], "ms_per_step": r8["ms_per_step"]}
     return out
 
 

@@ -39,9 +39,9 @@ static constexpr int MAX_NBOX = 9;        // K slice <= 576 columns
 static constexpr int RING = 8;            // exchange slots (>= 4: a slot is reset two steps before it is rewritten)
 static constexpr int BOX_BYTES = BP * 128;   // one [16 x 64] bf16 box of the operand image
 // Step counters exist in NCOPY copies, each in its own 4 KB block of the workspace.  B200's L2 is split over two dies and
-// an address is homed on one of them (4 KB granularity, measured: tools/microbench/topo2.cu): a strong load or an atomic
+// an address is homed on one of them (4 KB granularity, measured: tools/microbench/topo2.cu, profiles/r2_microbench_topo2.txt): a strong load or an atomic
 // on a far-die address costs ~700 clk against ~300 clk on the near die, so a single counter makes half of the pollers
-// pay the die crossing on every poll (counter barrier among 56 CTAs: 1320 clk with a far counter, 750 clk with a near
+// pay the die crossing on every poll (counter barrier among 56 same-die CTAs: 1250 clk with a far counter, 650 clk with a near
 // one).  Publishers add to every copy (fire and forget); each poller times the copies during its first steps and then
 // polls the one that answers fastest.
 static constexpr int NCOPY = 4;

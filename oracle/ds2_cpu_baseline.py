@@ -69,25 +69,44 @@ def train_step(feats, sparse, seq_lens, p, layers):
                       reduction="none").mean()
     leaves = list(p.values()) + [t for lp in layers for d in lp.values() for t in d.values()]
     torch.autograd.grad(loss, leaves, allow_unused=True)
-    return float(loss)
+    return float(loss.detach())
+
+
+class StepTimer(object):
+    """Parameters are built ONCE (89 M values for the train.sh model: seconds of work that is not part of a step);
+    `run` then times training steps on one dummy bucket the way the reference does (src/deepSpeech_train.py:306-332:
+    wall time of the step including host batch generation, the first `warmup` steps discarded)."""
+
+    def __init__(self, threads, num_hidden=1760, num_layers=7, num_filters=32, seed=1234):
+        torch.set_num_threads(threads)
+        self.threads = threads
+        self.p, self.layers = make_params(num_filters, num_hidden, num_layers, seed)
+        self.rng = np.random.default_rng(seed)
+
+    def step(self, batch_size, bucket):
+        t0 = time.perf_counter()
+        feats, idx, vals, shape, lens = O.dummy_batch(self.rng, batch_size, bucket)
+        loss = train_step(feats, (idx, vals, shape), lens, self.p, self.layers)
+        return time.perf_counter() - t0, loss
+
+    def run(self, batch_size, bucket, steps, warmup):
+        """-> dict(value = audio-s/s from the MEAN step time (the reference's formula), ms_per_step, min/median/max ms, loss)"""
+        times, loss = [], float("nan")
+        for i in range(warmup + steps):
+            dt, loss = self.step(batch_size, bucket)
+            if i >= warmup:
+                times.append(dt)
+        t = np.asarray(times)
+        audio_s = batch_size * O.UTT_LENGTHS[bucket] / 100.0
+        return {"value": audio_s / float(t.mean()), "ms_per_step": float(t.mean()) * 1e3, "ms_min": float(t.min()) * 1e3,
+                "ms_median": float(np.median(t)) * 1e3, "ms_max": float(t.max()) * 1e3, "loss": loss, "audio_s_per_step": audio_s}
 
 
 def time_steps(batch_size, bucket, steps, warmup, threads, num_hidden=1760, num_layers=7, num_filters=32, seed=1234):
     """-> (audio_seconds_per_second, ms_per_step, loss).  Step time includes host batch generation, as the
     reference's own timing does (src/deepSpeech_train.py:306-324)."""
-    torch.set_num_threads(threads)
-    p, layers = make_params(num_filters, num_hidden, num_layers, seed)
-    rng = np.random.default_rng(seed)
-    times, loss = [], float("nan")
-    for i in range(warmup + steps):
-        t0 = time.perf_counter()
-        feats, idx, vals, shape, lens = O.dummy_batch(rng, batch_size, bucket)
-        loss = train_step(feats, (idx, vals, shape), lens, p, layers)
-        if i >= warmup:
-            times.append(time.perf_counter() - t0)
-    dt = float(np.mean(times))
-    audio_s = batch_size * O.UTT_LENGTHS[bucket] / 100.0
-    return audio_s / dt, dt * 1e3, loss
+    r = StepTimer(threads, num_hidden, num_layers, num_filters, seed).run(batch_size, bucket, steps, warmup)
+    return r["value"], r["ms_per_step"], r["loss"]
 
 
 def time_ctc(T, B, L, steps, threads, seed=7):
