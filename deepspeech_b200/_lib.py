@@ -40,6 +40,7 @@ _SIGS = {
     "ds2_gemm_generic": (I, [P, I, L, L, P, I, L, L, P, I, L, I, I, I, F, F, P, P]),
     "ds2_rnn_relu_fwd": (I, [P, F, P, P, P, P, I, I, I, I, I, I, F, P, SZ, P]),
     "ds2_rnn_relu_fwd_ex": (I, [P, F, P, P, P, P, P, I, I, I, I, I, F, P, SZ, P]),
+    "ds2_rnn_relu_bwd_ex": (I, [P, P, P, P, P, P, P, I, I, I, I, I, F, P, SZ, P]),
     "ds2_rnn_relu_bwd": (I, [P, P, P, P, P, P, I, I, I, I, I, I, F, P, SZ, P]),
     "ds2_rnn_workspace_bytes": (SZ, [I, I, I, I, I]),
     "ds2_rnn_relu_persistent_supported": (I, [I, I, I]),

@@ -163,6 +163,18 @@ extern "C" int ds2_rnn_relu_bwd(const float* dout, const void* u, const int* len
   return rnn_relu_bwd_persist(dout, u, nullptr, lens, hs, dz, dbias, T, B, H, ND, reverse_mask, cap, workspace, workspace_bytes, st);
 }
 
+extern "C" int ds2_rnn_relu_bwd_ex(const float* dout, const void* u, const void* ut, const int* lens, const void* hs, void* dz, float* dbias,
+                                   int T, int B, int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes,
+                                   void* stream) {
+  int rc = rnn_check(dout, ut ? ut : u, hs, dz, T, B, H, ND, DS2_BF16);
+  if (rc) return rc;
+  DS2_REQUIRE(lens, DS2_ERR_BAD_ARG, "ds2_rnn_relu_bwd_ex: lens is null");
+  DS2_REQUIRE(rnn_persist_supported(B, H, ND), DS2_ERR_UNSUPPORTED,
+              "ds2_rnn_relu_bwd_ex: persistent bf16 kernel does not take B=%d H=%d ND=%d", B, H, ND);
+  return rnn_relu_bwd_persist(dout, u, ut, lens, hs, dz, dbias, T, B, H, ND, reverse_mask, cap, workspace, workspace_bytes,
+                              static_cast<cudaStream_t>(stream));
+}
+
 extern "C" size_t ds2_rnn_workspace_bytes(int T, int B, int H, int ND, int dtype) {
   if (dtype != DS2_BF16) return 0;
   return rnn_persist_workspace_bytes(T, B, H, ND);

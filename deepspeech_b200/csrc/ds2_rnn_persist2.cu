@@ -430,10 +430,11 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
           }
         }
       }
+      float o[4] = {0.f, 0.f, 0.f, 0.f};
+      uint2 pk = make_uint2(0u, 0u);
       if (jvalid) {
         const bool live = t < len_b;
         const float av[4] = {add.x, add.y, add.z, add.w};
-        float o[4];
         if (!BWD) {
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
@@ -449,7 +450,6 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
             dbs[i] += o[i];
           }
         }
-        uint2 pk;
         __nv_bfloat162 b0v = __floats2bfloat162_rn(o[0], o[1]), b1v = __floats2bfloat162_rn(o[2], o[3]);
         pk.x = *reinterpret_cast<uint32_t*>(&b0v);
         pk.y = *reinterpret_cast<uint32_t*>(&b1v);
@@ -457,19 +457,21 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
           pk.x = scrub_fill2(pk.x);       // a NaN gradient must not look like the sentinel
           pk.y = scrub_fill2(pk.y);
         }
-        // the exchange ring first (the other CTAs wait for it), the slot two steps ahead back to the sentinel, then the
-        // caller's tensor
+        // the exchange ring first (the other CTAs wait for it) and the slot two steps ahead back to the sentinel
         st_relaxed_b64(ring_cell + (size_t)(step % RING) * slot_stride, pk.x, pk.y);
         st_relaxed_b64(ring_cell + (size_t)((step + 2) % RING) * slot_stride, 0xFFFFFFFFu, 0xFFFFFFFFu);
+      }
+      // publish: one relaxed increment per counter copy after the warp's stores (no fence: the image validates itself)
+      __syncwarp();
+      if (lane < NCOPY) red_relaxed_gpu_add(ctr + lane * CTR_COPY_STRIDE, 1u);
+      // the caller's tensors afterwards: nobody inside the kernel waits for them
+      if (jvalid) {
         *reinterpret_cast<uint2*>(out_ptr) = pk;
         if (!BWD && out32_ptr) {
           *reinterpret_cast<float4*>(out32_ptr) = make_float4(o[0], o[1], o[2], o[3]);
           out32_ptr += out_inc;            // fwd: the fp32 tensor has the pitch of the bf16 one
         }
       }
-      // publish: one relaxed increment per counter copy after the warp's stores (no fence: the image validates itself)
-      __syncwarp();
-      if (lane < NCOPY) red_relaxed_gpu_add(ctr + lane * CTR_COPY_STRIDE, 1u);
       if (pr) p.prof[step * 16 + 12] = dev_clock();
     }
     if (BWD && p.dbias != nullptr) {
@@ -654,13 +656,17 @@ int rnn_relu_fwd_persist(const float* wx, float scale, const void* u, const floa
 // the caller has no transposed copy (ut_in == nullptr) U is transposed into the workspace first.
 int rnn_relu_bwd_persist(const float* dout, const void* u, const void* ut_in, const int* lens, const void* hs, void* dz, float* dbias, int T,
                          int B, int H, int ND, int reverse_mask, float cap, void* ws, size_t ws_bytes, cudaStream_t st) {
-  if (env().rnn_v1) return rnn_relu_bwd_persist_v1(dout, u, lens, hs, dz, dbias, T, B, H, ND, reverse_mask, cap, ws, ws_bytes, st);
+  if (env().rnn_v1) {
+    DS2_REQUIRE(u, DS2_ERR_BAD_ARG, "ds2_rnn_relu_bwd_ex: the round-1 kernel (DS2_RNN_V1) needs U itself");
+    return rnn_relu_bwd_persist_v1(dout, u, lens, hs, dz, dbias, T, B, H, ND, reverse_mask, cap, ws, ws_bytes, st);
+  }
   Params p = {};
   Geom g;
   int rc = common_setup(p, g, T, B, H, ND, ws, ws_bytes, "ds2_rnn_relu_bwd", st);
   if (rc) return rc;
   const void* ut = ut_in;
   if (!ut) {
+    DS2_REQUIRE(u, DS2_ERR_BAD_ARG, "ds2_rnn_relu_bwd: neither U nor U^T given");
     __nv_bfloat16* utw = reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + WS_CTR_BYTES + WS_PROF_BYTES);
     for (int d = 0; d < ND; ++d) {
       rc = ds2_transpose(static_cast<const __nv_bfloat16*>(u) + (size_t)d * H * H, DS2_BF16, H, H, H, utw + (size_t)d * H * H, DS2_BF16, H, st);

@@ -5,6 +5,7 @@ libds2_b200.so.  Tensors handed to the C ABI must be CUDA + contiguous."""
 from __future__ import annotations
 
 import math
+import weakref
 from ctypes import c_void_p
 from typing import List, Optional, Sequence, Tuple
 
@@ -100,6 +101,52 @@ def cast(x: torch.Tensor, dtype) -> torch.Tensor:
     out = torch.empty(x.shape, dtype=dtype, device=x.device)
     check(lib.ds2_cast(_p(x.contiguous()), _dt(x), _p(out), _dt(out), x.numel(), _stream()), "ds2_cast")
     return out
+
+
+# bf16 copies of the fp32 master weights (and U^T for the backward recurrence) are made once per weight VERSION, not once
+# per step: keyed by storage address + shape, valid while the tensor's autograd version and the global epoch (bumped by
+# optimizers that update parameters through the C ABI, which autograd cannot see) are unchanged.
+_wcache = {}
+_weight_epoch = 0
+
+
+def invalidate_weight_cache():
+    global _weight_epoch
+    _weight_epoch += 1
+    _wcache.clear()
+
+
+def _cached(w: torch.Tensor, kind: str, make):
+    # only long-lived parameters are cached, and an entry belongs to one tensor OBJECT (weak reference): a temporary
+    # that happens to reuse a freed tensor's address must never hit
+    if not isinstance(w, torch.nn.Parameter):
+        return make()
+    key = (id(w), kind)
+    tag = (w._version, _weight_epoch, w.data_ptr())
+    e = _wcache.get(key)
+    if e is not None and e[0]() is w and e[1] == tag:
+        return e[2]
+    out = make()
+    _wcache[key] = (weakref.ref(w), tag, out)
+    return out
+
+
+def cached_bf16(w: torch.Tensor) -> torch.Tensor:
+    if w.dtype == torch.bfloat16:
+        return w
+    return _cached(w, "bf16", lambda: cast(w.contiguous(), torch.bfloat16))
+
+
+def cached_ut_bf16(U: torch.Tensor) -> torch.Tensor:
+    """U [ND,H,H] -> bf16 [ND,H,H] with ut[d] = U[d]^T (the resident operand of the backward recurrence)."""
+    def make():
+        ND, H, _ = U.shape
+        Uc = U.contiguous()
+        ut = torch.empty((ND, H, H), dtype=torch.bfloat16, device=U.device)
+        for d in range(ND):
+            check(lib.ds2_transpose(_p(Uc[d]), _dt(Uc), H, H, H, _p(ut[d]), DS2_BF16, H, _stream()), "ds2_transpose")
+        return ut
+    return _cached(U, "ut", make)
 
 
 def add2(a: torch.Tensor, b: torch.Tensor, out_dtype) -> torch.Tensor:
@@ -436,7 +483,7 @@ class _BiRNNLayerFn(torch.autograd.Function):
         dev = x.device
         cdt = rnn_path_dtype(B, H, ND, want_bf16)
         if cdt == torch.bfloat16:
-            xg, Wg, Ug = cast(x.contiguous(), torch.bfloat16), cast(Wcat, torch.bfloat16), cast(U, torch.bfloat16)
+            xg, Wg, Ug = cast(x.contiguous(), torch.bfloat16), cached_bf16(Wcat), cached_bf16(U)
         else:
             xg, Wg, Ug = cast(x.contiguous(), torch.float32), Wcat, U
         wx = gemm_nt(xg.view(T * B, I), Wg)                                       # [TB, ND*H] fp32
@@ -513,7 +560,7 @@ class _BiGRULayerFn(torch.autograd.Function):
         hs = torch.empty((ND, T, B, H), dtype=cdt, device=dev)
         gates = torch.empty((ND, T, B, 4 * H), dtype=cdt, device=dev)
         if cdt == torch.bfloat16:
-            xg, Wg, Ug = cast(x.contiguous(), torch.bfloat16), cast(Wcat, torch.bfloat16), cast(U, torch.bfloat16)
+            xg, Wg, Ug = cast(x.contiguous(), torch.bfloat16), cached_bf16(Wcat), cached_bf16(U)
             wx = gemm_nt(xg.view(T * B, I), Wg)                                    # [TB, ND*3H] fp32
             wsb = lib.ds2_gru_workspace_bytes(T, B, H, ND)
             ws = _workspace(wsb, dev, "gru")
@@ -636,7 +683,7 @@ class _RecStackFn(torch.autograd.Function):
             W, U = params[l * npl], params[l * npl + 1]
             ND, H = U.shape[0], U.shape[2]
             I = cur.shape[2]
-            Wg, Ug = cast(W, torch.bfloat16), cast(U, torch.bfloat16)
+            Wg, Ug = cached_bf16(W), cached_bf16(U)
             wx = gemm_nt(cur.view(T * B, I), Wg)
             hs = torch.empty((ND, T, B, H), dtype=torch.bfloat16, device=dev)
             if gru:
@@ -715,8 +762,9 @@ class _RecStackFn(torch.autograd.Function):
                 else:
                     wsb = lib.ds2_rnn_workspace_bytes(T, B, H, ND, DS2_BF16)
                     ws = _workspace(wsb, dev, "rnn")
-                    check(lib.ds2_rnn_relu_bwd(_p(d_cur), _p(Ug), _p(lens), _p(hs), _p(dz), _p(db if FUSED_BIAS_GRAD else None), DS2_BF16, T, B, H, ND,
-                                               reverse_mask, RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_bwd")
+                    Ut = cached_ut_bf16(ctx.param_objs[l * npl + 1])          # once per weight version, not per step
+                    check(lib.ds2_rnn_relu_bwd_ex(_p(d_cur), _p(Ug), _p(Ut), _p(lens), _p(hs), _p(dz), _p(db if FUSED_BIAS_GRAD else None), T, B, H,
+                                                  ND, reverse_mask, RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_bwd_ex")
                 if STACK_TRACE is not None:
                     ev1 = torch.cuda.Event(enable_timing=True)
                     ev1.record()
@@ -798,7 +846,7 @@ class _LinearFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x2d, W, b, want_bf16):
         if want_bf16 and x2d.dtype == torch.bfloat16:
-            Wg = cast(W, torch.bfloat16)
+            Wg = cached_bf16(W)
         else:
             Wg = W
             x2d = cast(x2d, torch.float32)
@@ -822,7 +870,7 @@ class _LinearFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             if tc:
                 # dx[R,K] = dy . W: dy^T is the MN-major A operand, W [N,K] the MN-major B operand, contraction over N classes
-                dx = gemm_nt(dyT, cast(W, torch.bfloat16), a_mn=True, b_mn=True, M=R, N=K, K=N, out_dtype=torch.bfloat16)
+                dx = gemm_nt(dyT, cached_bf16(W), a_mn=True, b_mn=True, M=R, N=K, K=N, out_dtype=torch.bfloat16)
             else:
                 dx = gemm_nt(dy, W, b_mn=True)                  # [R,K] = dy[R,N] . W[N,K]
                 if x2d.dtype != torch.float32:

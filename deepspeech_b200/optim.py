@@ -7,6 +7,7 @@ from __future__ import annotations
 
 import torch
 
+from . import ops
 from ._lib import check, lib
 
 NUM_PER_EPOCH_FOR_TRAIN = 28535          # src/deepSpeech_input.py:15, read at src/deepSpeech_train.py:240
@@ -72,6 +73,7 @@ class AdamEMA:
         check(lib.ds2_adam_ema_step(self._table.data_ptr(), len(self.params), self._n_chunks, lr, self.beta1, self.beta2,
                                     self.eps, n, keep, float(grad_scale), torch.cuda.current_stream().cuda_stream),
               "ds2_adam_ema_step")
+        ops.invalidate_weight_cache()          # the parameters changed behind autograd's back: bf16 copies are stale
 
     def zero_grad(self, set_to_none: bool = True):
         for p in self.params:

@@ -123,6 +123,12 @@ int ds2_rnn_relu_fwd_ex(const float* wx, float scale, const void* u, const float
                         void* stream);
 int ds2_rnn_relu_bwd(const float* dout, const void* u, const int* lens, const void* hs, void* dz, float* dbias, int dtype, int T,
                      int B, int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes, void* stream);
+/* ds2_rnn_relu_bwd on the bf16 path with the transposed recurrent weights supplied by the caller: ut [ND,H,H] bf16,
+ * ut[d][k][j] = u[d][j][k] (the operand the backward contraction U^T dz keeps resident).  Weights change once per
+ * optimizer step, so a caller can transpose them once instead of once per layer and step; with ut == NULL the call
+ * transposes u into the workspace like ds2_rnn_relu_bwd (u may be NULL when ut is given). */
+int ds2_rnn_relu_bwd_ex(const float* dout, const void* u, const void* ut, const int* lens, const void* hs, void* dz, float* dbias, int T,
+                        int B, int H, int ND, int reverse_mask, float cap, void* workspace, size_t workspace_bytes, void* stream);
 size_t ds2_rnn_workspace_bytes(int T, int B, int H, int ND, int dtype);
 int ds2_rnn_relu_persistent_supported(int B, int H, int ND);
 
