@@ -304,6 +304,11 @@ def main():
         "gpu_launches": int(launches),
         "loss": final_loss,
         "step_tflops": total_flops / (ms_step * 1e-3) / 1e12 / 1.0,
+        # whole step against the SUSTAINED bf16 peak (the step is long; the burst figure applies to a kernel timed alone)
+        "roofline_step": {"bound": "tensor", "achieved": total_flops / (ms_step * 1e-3) / 1e12, "unit": "TFLOP/s",
+                          "peak": float(peaks.get("bf16_tflops_sustained", 1377.0)),
+                          "frac": total_flops / (ms_step * 1e-3) / 1e12 / float(peaks.get("bf16_tflops_sustained", 1377.0)),
+                          "flops_per_step": total_flops},
         "model_flops_per_step": total_flops,
     }
 
@@ -318,6 +323,15 @@ def main():
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def _profiled_traffic(dom_gemm, T2, B, H):
+    if dom_gemm or (T2, B, H) != (366, 32, 1760):
+        return None
+    try:
+        return float(json.load(open(os.path.join(ROOT, "profiles", "r2_rnn2_ncu.json")))["dram_bytes_per_launch"])
+    except Exception:
+        return None
 
 
 def _time_kernel(fn, iters=10, warm=3):
@@ -370,13 +384,16 @@ def extras(args, dev, model, ops, _lib, B, T2, H, L, peak_tf, peak_hbm, peak_src
         out["roofline"] = {"kernel": "gemm_tcgen05_kernel (W.x, M=%d N=%d K=%d)" % (T2 * B, 2 * H, H) if dom_gemm
                            else "recurrent forward kernel (T=%d steps, B=%d, H=%d, 2 directions)" % (T2, B, H),
                            "bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
-                           # dram__bytes_read+write of one launch from the committed ncu --set full capture
-                           # (profiles/r1_rnn_persist_ncu_v6.txt, same shape); algorithmic bytes 259.7 MB
-                           "traffic": None if dom_gemm else 238.0e6, "peak_source": peak_src,
-                           "note": "latency-bound T-step dependency chain (4 chains x 366 steps); see profiles/r1_rnn_stage_cycles_v5.txt"}
+                           # dram__bytes_read+write of one launch of this kernel, read from the committed ncu --set full
+                           # extract of the same shape (profiles/r2_rnn2_ncu.json); null for any other shape / kernel
+                           "traffic": _profiled_traffic(dom_gemm, T2, B, H), "traffic_source": "profiles/r2_rnn2_ncu.json",
+                           "algorithmic_bytes": 4.0 * T2 * B * 2 * H + 2.0 * 2 * H * H + 2.0 * 2 * T2 * B * H,
+                           "peak_source": peak_src,
+                           "note": "latency-bound T-step dependency chain (4 chains x %d steps); stage cycles in profiles/r2_rnn_stage_cycles_v2.txt" % T2}
     total_flops, rnn_flops, _ = step_flops(B, args.frames, H, L, 32, args.cell)
     out["rnn_tflops_in_step"] = {"note": "all RNN-stack GEMM FLOPs (fwd+bwd) / whole step time (lower bound)",
-                                 "value": rnn_flops / (ms_step * 1e-3) / 1e12}
+                                 "value": rnn_flops / (ms_step * 1e-3) / 1e12,
+                                 "frac_of_sustained_peak": rnn_flops / (ms_step * 1e-3) / 1e12 / 1377.0}
     # ---- config 2: standalone CTC sweep, B=64 (+ B=512 bandwidth-regime point)
     sweep = []
     for (Tc, Lc, Bc) in [(200, 50, 64), (400, 100, 64), (800, 200, 64), (1600, 400, 64), (400, 100, 512)]:
