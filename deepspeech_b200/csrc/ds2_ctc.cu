@@ -67,6 +67,7 @@ static constexpr int CTC_NSMAX = 4;   // lattice states per thread (S <= 4096)
 }  // namespace ds2
 
 #include "ds2_ctc_chain.cuh"
+#include "ds2_ctc2.cuh"
 
 namespace ds2 {
 
@@ -166,9 +167,60 @@ extern "C" int ds2_ctc_scale_grad(const float* grad, const float* dloss, float* 
   return DS2_OK;
 }
 
+namespace ds2 {
+// the round-2 kernels take K <= 32 classes and up to 1024 lattice states (labels up to 511); anything else, and
+// DS2_CTC_V1=1, runs the round-1 kernels.  One workspace size serves both.
+static bool ctc2_takes(int K, int Lmax) { return K <= c2::CTC2_KP && 2 * Lmax + 1 <= 1024; }
+static size_t ctc_ws_bytes_both(int T, int B, int K, int Lmax) {
+  const size_t a = ctc_ws_layout(T, B, K, Lmax, nullptr, nullptr);
+  const size_t b = ctc2_takes(K, Lmax) ? c2::ctc2_ws_layout(T, B, K, Lmax, nullptr, nullptr) : 0;
+  return a > b ? a : b;
+}
+
+template <int NS>
+static int ctc2_launch_chain(int T, int B, int K, const int* labels, int Lmax, const int* label_lens, const int* seq_lens, float* loss,
+                             const c2::Ws2& ws, size_t smem, cudaStream_t st) {
+  static unsigned long long attr_done_devs = 0;
+  if (first_use_on_device(&attr_done_devs))
+    DS2_CUDA(cudaFuncSetAttribute(c2::ctc2_chain_kernel<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+  c2::ctc2_chain_kernel<NS><<<dim3(B, 2), 32, smem, st>>>(T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws);
+  DS2_LAUNCH_CHECK("ctc2_chain_kernel");
+  count_launch();
+  return DS2_OK;
+}
+
+static int ctc2_launch(const float* logits, int T, int B, int K, const int* labels, int Lmax, const int* label_lens,
+                       const int* seq_lens, const float* dloss, float* loss, float* grad, void* workspace, cudaStream_t st) {
+  c2::Ws2 ws;
+  c2::ctc2_ws_layout(T, B, K, Lmax, reinterpret_cast<char*>(workspace), &ws);
+  const long rows = (long)T * B;
+  c2::ctc2_rows_kernel<<<(unsigned)((rows * 32 + 255) / 256), 256, 0, st>>>(logits, rows, K, ws.yhat, ws.lz);
+  DS2_LAUNCH_CHECK("ctc2_rows_kernel");
+  count_launch();
+  const size_t smem = sizeof(float) * (2 * c2::CTC2_RB * c2::CTC2_KP + 2 * (size_t)c2::CTC2_RB * ws.pitch) + sizeof(int) * (size_t)(Lmax + 4);
+  int rc = DS2_ERR_UNSUPPORTED;
+  switch (ws.NS) {
+#define DS2_C2_CASE(N) case N: rc = ctc2_launch_chain<N>(T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws, smem, st); break;
+    DS2_C2_CASE(2) DS2_C2_CASE(4) DS2_C2_CASE(6) DS2_C2_CASE(8) DS2_C2_CASE(10) DS2_C2_CASE(12) DS2_C2_CASE(14) DS2_C2_CASE(16)
+    DS2_C2_CASE(18) DS2_C2_CASE(20) DS2_C2_CASE(22) DS2_C2_CASE(24) DS2_C2_CASE(26) DS2_C2_CASE(28) DS2_C2_CASE(30) DS2_C2_CASE(32)
+#undef DS2_C2_CASE
+    default: set_error("ds2_ctc: no kernel for %d states per lane", ws.NS);
+  }
+  if (rc) return rc;
+  if (grad) {
+    const int warps = 8;
+    const size_t gsmem = sizeof(float) * (size_t)warps * ws.pitch;
+    c2::ctc2_grad_kernel<<<dim3((T + warps - 1) / warps, B), warps * 32, gsmem, st>>>(T, B, K, Lmax, label_lens, seq_lens, dloss, grad, ws);
+    DS2_LAUNCH_CHECK("ctc2_grad_kernel");
+    count_launch();
+  }
+  return DS2_OK;
+}
+}  // namespace ds2
+
 extern "C" size_t ds2_ctc_workspace_bytes(int T, int B, int K, int Lmax) {
   if (T <= 0 || B <= 0 || K <= 1 || Lmax < 0) return 0;
-  return ctc_ws_layout(T, B, K, Lmax, nullptr, nullptr);
+  return ds2::ctc_ws_bytes_both(T, B, K, Lmax);
 }
 
 namespace ds2 {
@@ -178,10 +230,13 @@ int ctc_launch(const float* logits, int T, int B, int K, const int* labels, int 
   DS2_REQUIRE(logits && labels && label_lens && seq_lens && loss, DS2_ERR_BAD_ARG, "ds2_ctc: null pointer argument");
   DS2_REQUIRE(T > 0 && B > 0 && K > 1 && Lmax >= 0, DS2_ERR_BAD_SHAPE, "ds2_ctc: bad shape T=%d B=%d K=%d Lmax=%d", T, B, K, Lmax);
   CtcWs ws;
-  size_t need = ctc_ws_layout(T, B, K, Lmax, reinterpret_cast<char*>(workspace), &ws);
+  ctc_ws_layout(T, B, K, Lmax, reinterpret_cast<char*>(workspace), &ws);
+  const size_t need = ctc_ws_bytes_both(T, B, K, Lmax);
   DS2_REQUIRE(workspace && workspace_bytes >= need, DS2_ERR_WORKSPACE, "ds2_ctc: workspace too small (%zu < %zu bytes)",
               workspace_bytes, need);
   DS2_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, DS2_ERR_BAD_ARG, "ds2_ctc: workspace must be 256-byte aligned");
+  if (!env().ctc_v1 && ctc2_takes(K, Lmax))
+    return ctc2_launch(logits, T, B, K, labels, Lmax, label_lens, seq_lens, dloss, loss, grad, workspace, st);
   const int Smax = 2 * Lmax + 1;
   // states per thread: 1 measured fastest (one thread per lattice state keeps the per-step chain shortest; 2 and 4
   // halve / quarter the warps at the barrier but lengthen the serial work of a step); DS2_CTC_NS overrides for tuning
@@ -281,7 +336,7 @@ extern "C" int ds2_ctc_loss_fwd_bwd_noalloc(const float* logits, int T, int B, i
                                             float* grad, void* stream) {
   DS2_REQUIRE(T > 0 && B > 0 && K > 1 && Lmax >= 0, DS2_ERR_BAD_SHAPE, "ds2_ctc_loss_fwd_bwd_noalloc: bad shape T=%d B=%d K=%d Lmax=%d",
               T, B, K, Lmax);
-  const size_t need = ctc_ws_layout(T, B, K, Lmax, nullptr, nullptr);
+  const size_t need = ctc_ws_bytes_both(T, B, K, Lmax);
   DS2_REQUIRE(need <= (size_t)DS2_CTC_NOALLOC_MAX_BYTES, DS2_ERR_WORKSPACE,
               "ds2_ctc_loss_fwd_bwd_noalloc: T=%d B=%d Lmax=%d needs %zu bytes of scratch, the built-in array holds %zu; "
               "use ds2_ctc_loss_fwd_bwd with a caller-provided workspace",
