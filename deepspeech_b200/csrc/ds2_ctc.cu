@@ -177,13 +177,13 @@ static size_t ctc_ws_bytes_both(int T, int B, int K, int Lmax) {
   return a > b ? a : b;
 }
 
-template <int NS>
+template <int NS, int W>
 static int ctc2_launch_chain(int T, int B, int K, const int* labels, int Lmax, const int* label_lens, const int* seq_lens, float* loss,
                              const c2::Ws2& ws, size_t smem, cudaStream_t st) {
   static unsigned long long attr_done_devs = 0;
   if (first_use_on_device(&attr_done_devs))
-    DS2_CUDA(cudaFuncSetAttribute(c2::ctc2_chain_kernel<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-  c2::ctc2_chain_kernel<NS><<<dim3(B, 2), 32, smem, st>>>(T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws);
+    DS2_CUDA(cudaFuncSetAttribute(c2::ctc2_chain_kernel<NS, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+  c2::ctc2_chain_kernel<NS, W><<<dim3(B, 2), 32 * W, smem, st>>>(T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws);
   DS2_LAUNCH_CHECK("ctc2_chain_kernel");
   count_launch();
   return DS2_OK;
@@ -194,18 +194,15 @@ static int ctc2_launch(const float* logits, int T, int B, int K, const int* labe
   c2::Ws2 ws;
   c2::ctc2_ws_layout(T, B, K, Lmax, reinterpret_cast<char*>(workspace), &ws);
   const long rows = (long)T * B;
-  c2::ctc2_rows_kernel<<<(unsigned)((rows * 32 + 255) / 256), 256, 0, st>>>(logits, rows, K, ws.yhat, ws.lz);
+  c2::ctc2_rows_kernel<<<(unsigned)((rows * 32 + 255) / 256), 256, 0, st>>>(logits, rows, K, ws.ly);
   DS2_LAUNCH_CHECK("ctc2_rows_kernel");
   count_launch();
-  const size_t smem = sizeof(float) * (2 * c2::CTC2_RB * c2::CTC2_KP + 2 * (size_t)c2::CTC2_RB * ws.pitch) + sizeof(int) * (size_t)(Lmax + 4);
+  const size_t smem = sizeof(float) * (2 * c2::CTC2_RB * c2::CTC2_KP + 2 * (size_t)c2::CTC2_RB * ws.pitch + 16) + sizeof(int) * (size_t)(Lmax + 4);
   int rc = DS2_ERR_UNSUPPORTED;
-  switch (ws.NS) {
-#define DS2_C2_CASE(N) case N: rc = ctc2_launch_chain<N>(T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws, smem, st); break;
-    DS2_C2_CASE(2) DS2_C2_CASE(4) DS2_C2_CASE(6) DS2_C2_CASE(8) DS2_C2_CASE(10) DS2_C2_CASE(12) DS2_C2_CASE(14) DS2_C2_CASE(16)
-    DS2_C2_CASE(18) DS2_C2_CASE(20) DS2_C2_CASE(22) DS2_C2_CASE(24) DS2_C2_CASE(26) DS2_C2_CASE(28) DS2_C2_CASE(30) DS2_C2_CASE(32)
+#define DS2_C2_CASE(N, WW) if (ws.NS == N && ws.W == WW) rc = ctc2_launch_chain<N, WW>(T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws, smem, st);
+  DS2_C2_CASE(2, 1) DS2_C2_CASE(2, 2) DS2_C2_CASE(2, 4) DS2_C2_CASE(4, 4) DS2_C2_CASE(6, 4) DS2_C2_CASE(8, 4)
 #undef DS2_C2_CASE
-    default: set_error("ds2_ctc: no kernel for %d states per lane", ws.NS);
-  }
+  if (rc == DS2_ERR_UNSUPPORTED) set_error("ds2_ctc: no kernel for %d states per lane x %d warps", ws.NS, ws.W);
   if (rc) return rc;
   if (grad) {
     const int warps = 8;
