@@ -194,7 +194,7 @@ static int ctc2_launch(const float* logits, int T, int B, int K, const int* labe
   c2::Ws2 ws;
   c2::ctc2_ws_layout(T, B, K, Lmax, reinterpret_cast<char*>(workspace), &ws);
   const long rows = (long)T * B;
-  c2::ctc2_rows_kernel<<<(unsigned)((rows * 32 + 255) / 256), 256, 0, st>>>(logits, rows, K, ws.ly);
+  c2::ctc2_rows_kernel<<<(unsigned)(((rows + c2::C2_ROWS - 1) / c2::C2_ROWS * 32 + 255) / 256), 256, 0, st>>>(logits, rows, K, ws.ly);
   DS2_LAUNCH_CHECK("ctc2_rows_kernel");
   count_launch();
   const size_t smem = sizeof(float) * (2 * c2::CTC2_RB * c2::CTC2_KP + 2 * (size_t)c2::CTC2_RB * ws.pitch + 16) + sizeof(int) * (size_t)(Lmax + 4);
@@ -206,8 +206,9 @@ static int ctc2_launch(const float* logits, int T, int B, int K, const int* labe
   if (rc) return rc;
   if (grad) {
     const int warps = 8;
-    const size_t gsmem = sizeof(float) * (size_t)warps * ws.pitch;
-    c2::ctc2_grad_kernel<<<dim3((T + warps - 1) / warps, B), warps * 32, gsmem, st>>>(T, B, K, Lmax, label_lens, seq_lens, dloss, grad, ws);
+    const size_t gsmem = sizeof(float) * ((size_t)warps * ws.pitch + ((Lmax + 3) & ~3) + ((K + 1 + 3) & ~3));
+    const int rows_per_block = warps * c2::C2_GROWS;
+    c2::ctc2_grad_kernel<<<dim3((T + rows_per_block - 1) / rows_per_block, B), warps * 32, gsmem, st>>>(T, B, K, Lmax, label_lens, seq_lens, dloss, grad, ws);
     DS2_LAUNCH_CHECK("ctc2_grad_kernel");
     count_launch();
   }

@@ -87,16 +87,23 @@ static size_t ctc2_ws_layout(int T, int B, int K, int Lmax, char* base, Ws2* ws)
   return off;
 }
 
-// ---- kernel 1: one warp per logits row (t, b): log2-softmax
+// ---- kernel 1: log2-softmax of every logits row (t, b); a warp takes C2_ROWS rows at a time so that their loads and
+// reductions overlap
+static constexpr int C2_ROWS = 4;
 __global__ void __launch_bounds__(256) ctc2_rows_kernel(const float* __restrict__ logits, long rows, int K, float* __restrict__ ly) {
   const int lane = threadIdx.x & 31;
-  const long row = (blockIdx.x * (long)blockDim.x + threadIdx.x) >> 5;
-  if (row >= rows) return;
-  const float x = lane < K ? __ldg(logits + row * K + lane) : -INFINITY;
-  const float m = warp_max(x);
-  const float e = lane < K ? __expf(x - m) : 0.f;
-  const float z = warp_sum(e);
-  ly[row * CTC2_KP + lane] = lane < K ? (x - m) * C2_LOG2E - __log2f(z) : C2_NEG;
+  const long row0 = ((blockIdx.x * (long)blockDim.x + threadIdx.x) >> 5) * C2_ROWS;
+  float x[C2_ROWS];
+#pragma unroll
+  for (int r = 0; r < C2_ROWS; ++r) x[r] = (lane < K && row0 + r < rows) ? __ldg(logits + (row0 + r) * K + lane) : -INFINITY;
+#pragma unroll
+  for (int r = 0; r < C2_ROWS; ++r) {
+    if (row0 + r >= rows) break;
+    const float m = warp_max(x[r]);
+    const float e = lane < K ? __expf(x[r] - m) : 0.f;
+    const float z = warp_sum(e);
+    ly[(row0 + r) * CTC2_KP + lane] = lane < K ? (x[r] - m) * C2_LOG2E - __log2f(z) : C2_NEG;
+  }
 }
 
 __device__ __forceinline__ void c2_bulk_store_s2g(void* gdst, const void* ssrc, uint32_t bytes) {
@@ -315,54 +322,64 @@ __global__ void __launch_bounds__(32 * W) ctc2_chain_kernel(int T, int B, int K,
   else ctc2_chain<1, NS, W>(T, B, K, labels, Lmax, label_lens, seq_lens, loss, ws, c2_smem);
 }
 
-// ---- kernel 3: one warp per (t, b) row: grad = (softmax - occupancy) * dloss.  dynamic smem per warp: float e[pitch]
+// ---- kernel 3: grad = (softmax - occupancy) * dloss, one warp per (t, b) row, C2_GROWS rows per warp; the block's rows
+// belong to one utterance, whose class-sorted label positions are staged in shared memory once.
+// dynamic smem: int perm[Lmax] + int cls[K+1] (rounded up to 4) + per warp float e[pitch]
+static constexpr int C2_GROWS = 4;
 __global__ void __launch_bounds__(256) ctc2_grad_kernel(int T, int B, int K, int Lmax, const int* __restrict__ label_lens,
                                                         const int* __restrict__ seq_lens, const float* __restrict__ dloss,
                                                         float* __restrict__ grad, Ws2 ws) {
   extern __shared__ __align__(16) float c2_gsm[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int b = blockIdx.y;
-  const int t = blockIdx.x * nwarps + warp;
-  if (t >= T) return;
-  float* e = c2_gsm + (size_t)warp * ws.pitch;
+  int* s_perm = reinterpret_cast<int*>(c2_gsm);
+  int* s_cls = s_perm + ((Lmax + 3) & ~3);
+  float* e = c2_gsm + ((Lmax + 3) & ~3) + ((K + 1 + 3) & ~3) + (size_t)warp * ws.pitch;
   const int Tb = min(max(seq_lens[b], 0), T);
   int L = label_lens[b];
   if (L < 0 || L > Lmax) L = 0;
   const int S = 2 * L + 1;
   const int blank = K - 1;
-  float* g = grad + ((size_t)t * B + b) * K;
   const double logp = ws.logp[b];
-  if (t >= Tb || logp < 0.5 * (double)C2_NEG) {       // outside the utterance, or a row that cannot be aligned
-    if (lane < K) g[lane] = 0.f;
-    return;
-  }
   const float up = dloss ? dloss[b] : 1.f;
-  // alpha rows written at step t carry coff_a[t / RB]; beta rows written at step Tb-1-t carry coff_b[(Tb-1-t) / RB]
-  const double ca = ws.coff[((size_t)b * 2 + 0) * ws.NB + t / CTC2_RB];
-  const double cb = ws.coff[((size_t)b * 2 + 1) * ws.NB + (Tb - 1 - t) / CTC2_RB];
-  const float c = (float)(ca + cb - logp);
-  const float* ar = ws.alpha + ((size_t)b * T + t) * ws.pitch;
-  const float* br = ws.beta + ((size_t)b * T + t) * ws.pitch;     // beta is stored in reversed state order
-  float blank_sum = 0.f;
-  for (int s = lane; s < S; s += 32) {
-    const float v = exp2f(fminf(ar[s] + br[S - 1 - s] + c, 1e-3f));
-    e[s] = v;
-    if (!(s & 1)) blank_sum += v;
-  }
-  blank_sum = warp_sum(blank_sum);
-  __syncwarp();
-  const int* perm = ws.perm + (size_t)b * Lmax;
-  const int* cls = ws.cls_off + (size_t)b * (K + 1);
-  if (lane < K) {
-    const float y = exp2f(ws.ly[((size_t)t * B + b) * CTC2_KP + lane]);
-    float occ;
-    if (lane == blank) {
-      occ = blank_sum;
-    } else {
-      occ = 0.f;
-      for (int i = cls[lane]; i < cls[lane + 1]; ++i) occ += e[2 * perm[i] + 1];
+  for (int i = threadIdx.x; i < L; i += blockDim.x) s_perm[i] = ws.perm[(size_t)b * Lmax + i];
+  for (int i = threadIdx.x; i <= K; i += blockDim.x) s_cls[i] = ws.cls_off[(size_t)b * (K + 1) + i];
+  __syncthreads();
+  const bool feasible = logp > 0.5 * (double)C2_NEG;
+  const int t0 = (blockIdx.x * nwarps + warp) * C2_GROWS;
+  const int c_lo = lane < K ? s_cls[lane] : 0, c_hi = lane < K ? s_cls[lane + 1] : 0;
+  for (int t = t0; t < min(t0 + C2_GROWS, T); ++t) {
+    float* g = grad + ((size_t)t * B + b) * K;
+    if (t >= Tb || !feasible) {                        // outside the utterance, or a row that cannot be aligned
+      if (lane < K) g[lane] = 0.f;
+      continue;
     }
-    g[lane] = (y - occ) * up;
+    const float yl2 = lane < K ? __ldg(ws.ly + ((size_t)t * B + b) * CTC2_KP + lane) : C2_NEG;
+    // alpha rows written at step t carry coff_a[t / RB]; beta rows written at step Tb-1-t carry coff_b[(Tb-1-t) / RB]
+    const double ca = ws.coff[((size_t)b * 2 + 0) * ws.NB + t / CTC2_RB];
+    const double cb = ws.coff[((size_t)b * 2 + 1) * ws.NB + (Tb - 1 - t) / CTC2_RB];
+    const float c = (float)(ca + cb - logp);
+    const float* ar = ws.alpha + ((size_t)b * T + t) * ws.pitch;
+    const float* br = ws.beta + ((size_t)b * T + t) * ws.pitch;     // beta is stored in reversed state order
+    float blank_sum = 0.f;
+    for (int s = lane; s < S; s += 32) {
+      const float v = exp2f(fminf(__ldg(ar + s) + __ldg(br + S - 1 - s) + c, 1e-3f));
+      e[s] = v;
+      if (!(s & 1)) blank_sum += v;
+    }
+    blank_sum = warp_sum(blank_sum);
+    __syncwarp();
+    if (lane < K) {
+      float occ;
+      if (lane == blank) {
+        occ = blank_sum;
+      } else {
+        occ = 0.f;
+        for (int i = c_lo; i < c_hi; ++i) occ += e[2 * s_perm[i] + 1];
+      }
+      g[lane] = (exp2f(yl2) - occ) * up;
+    }
+    __syncwarp();
   }
 }
 
