@@ -26,9 +26,11 @@ class GradAllReducer(object):
     """Registers post-accumulate hooks on `params`; each gradient is all-reduced (sum) asynchronously as
     soon as autograd has produced it - backward visits layers last-to-first, so layer l's reduction runs
     while layers < l are still back-propagating.  Small tensors are packed into buckets of
-    `bucket_bytes` to amortise launch latency.  `finish()` waits for all reductions and applies 1/world."""
+    `bucket_bytes` to amortise launch latency.  `finish()` waits for all reductions and applies 1/world - unless
+    `prescaled`: the caller then back-propagates loss / world (`loss_scale`), the sums ARE the means and no scaling
+    kernel runs at all."""
 
-    def __init__(self, params: Iterable[torch.nn.Parameter], group=None, bucket_bytes: int = 32 << 20):
+    def __init__(self, params: Iterable[torch.nn.Parameter], group=None, bucket_bytes: int = 32 << 20, prescaled: bool = False):
         self.params: List[torch.nn.Parameter] = [p for p in params if p.requires_grad]
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -45,6 +47,8 @@ class GradAllReducer(object):
         # tensor.  This relies on .grad being a fresh tensor of this backward pass, i.e. on gradients having been reset
         # with zero_grad(set_to_none=True): accumulating into an older .grad would add the not-yet-reduced values.
         self._early = {}            # id(parameter) -> (work handle, reduced tensor)
+        self._keep = []             # flat buffers whose views are in flight
+        self.prescaled = prescaled
         if self.world > 1:
             # replicas must start from the same weights whatever seeded them: rank 0's values go to everybody
             with torch.no_grad():
@@ -53,15 +57,29 @@ class GradAllReducer(object):
             from . import ops
             ops.STACK_GRAD_HOOK = self._on_stack_layer
 
-    def _on_stack_layer(self, layer, tensors, params):
-        for t, p in zip(tensors, params):
-            if t is None:
-                continue
+    def _on_stack_layer(self, layer, tensors, params, flat=None):
+        """All gradients of one recurrent layer, offered from inside the stack's backward.  When they are views of one
+        flat buffer (ops._RecStackFn allocates them so) the layer goes out as ONE all-reduce."""
+        live = [(t, p) for t, p in zip(tensors, params) if t is not None]
+        for t, p in live:
             if p.grad is not None:
                 raise RuntimeError("GradAllReducer: reset gradients with zero_grad(set_to_none=True) before backward")
+        if flat is not None and sum(t.numel() for t, _ in live) == flat.numel():
+            w = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            for t, p in live:
+                self._early[id(p)] = (w, t)
+            self._keep.append(flat)
+            self.launched += 1
+            return
+        for t, p in live:
             w = dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
             self._early[id(p)] = (w, t)
             self.launched += 1
+
+    @property
+    def loss_scale(self) -> float:
+        """Factor to apply to the loss before backward() when the reducer was built with prescaled=True."""
+        return 1.0 / self.world if self.prescaled else 1.0
 
     def _flush(self):
         if not self._bucket:
@@ -113,9 +131,11 @@ class GradAllReducer(object):
                     if p.grad.data_ptr() != flat.data_ptr() or n != flat.numel():
                         p.grad.copy_(flat[off:off + n].view_as(p.grad))
                     off += n
-            for p in ps:
-                _scale_(p.grad, inv)
+            if not self.prescaled:
+                for p in ps:
+                    _scale_(p.grad, inv)
         self._pending = []
+        self._keep = []
         self._seen = 0
 
     def remove(self):

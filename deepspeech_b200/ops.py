@@ -742,9 +742,13 @@ class _RecStackFn(torch.autograd.Function):
             #      scattered over the SMs, could keep some clusters from being placed
             dz = torch.empty((T * B, G), dtype=torch.bfloat16, device=dev)
             dgh = torch.empty((T * B, G), dtype=torch.bfloat16, device=dev) if gru else dz
-            db = torch.empty((ND, G // ND), dtype=torch.float32, device=dev)           # bias gradients come out of the kernel
-            dbu = torch.empty((ND, G // ND), dtype=torch.float32, device=dev) if gru else None
-            keep += [dz, dgh, d_cur]
+            # dW, dU, db (, dbu) of a layer live in ONE flat buffer: a data-parallel reducer sends it with one call
+            GH = G // ND
+            n_w, n_u, n_b = G * I, ND * GH * H, ND * GH
+            flat = torch.empty(n_w + n_u + n_b * (2 if gru else 1), dtype=torch.float32, device=dev)
+            db = flat[n_w + n_u:n_w + n_u + n_b].view(ND, GH)                           # bias gradients come out of the kernel
+            dbu = flat[n_w + n_u + n_b:].view(ND, GH) if gru else None
+            keep += [dz, dgh, d_cur, flat]
             if overlap:
                 rec.wait_stream(main)
                 if l + 2 in side_done:
@@ -786,10 +790,9 @@ class _RecStackFn(torch.autograd.Function):
                 if STACK_TRACE is not None:
                     ev2 = torch.cuda.Event(enable_timing=True)
                     ev2.record()
-                dW = torch.empty((G, I), dtype=torch.float32, device=dev)
+                dW = flat[:n_w].view(G, I)
+                dU = flat[n_w:n_w + n_u].view(ND, GH, H)
                 gemm_wgrad(dz, xg.view(T * B, I), G, I, T * B, G, I, dW, alpha=SBN_SCALE)
-                GH = G // ND
-                dU = torch.empty((ND, GH, H), dtype=torch.float32, device=dev)
                 for d in range(ND):
                     rev = (reverse_mask >> d) & 1
                     if T > 1:
@@ -799,14 +802,15 @@ class _RecStackFn(torch.autograd.Function):
                     else:
                         dU[d].zero_()
                 if not FUSED_BIAS_GRAD:
-                    db = colsum(dz, T * B, G, G).view(ND, GH)
-                    dbu = colsum(dgh, T * B, G, G).view(ND, GH) if gru else None
+                    db.copy_(colsum(dz, T * B, G, G).view(ND, GH))
+                    if gru:
+                        dbu.copy_(colsum(dgh, T * B, G, G).view(ND, GH))
                 outs = [dW, dU, db]
                 if gru:
                     outs.append(dbu)
                 if STACK_GRAD_HOOK is not None:
                     # on the stream that produced them: the reducer orders itself after it
-                    STACK_GRAD_HOOK(l, outs, ctx.param_objs[l * npl:(l + 1) * npl])
+                    STACK_GRAD_HOOK(l, outs, ctx.param_objs[l * npl:(l + 1) * npl], flat)
                 if STACK_TRACE is not None:
                     ev3 = torch.cuda.Event(enable_timing=True)
                     ev3.record()
