@@ -65,8 +65,10 @@ for r in range(world):
 ref = [a / world for a in ref]
 tol = 2e-2 if use_bf16 else 1e-5          # bf16 path: split-K atomics reorder fp32 sums from run to run
 worst = 0.0
+gmax = max(float(b.abs().max()) for b in ref)
 for (name, _), a, b in zip(m.named_parameters(), g_dp, ref):
-    e = float((a - b).abs().max() / b.abs().max().clamp_min(1e-20))
+    # relative to the tensor's own scale, with a floor: the gradient of a bias that batch norm cancels is pure round-off
+    e = float((a - b).abs().max() / max(float(b.abs().max()), 1e-3 * gmax))
     worst = max(worst, e)
     assert e < tol, (name, e)
 # every rank holds the same reduced gradients
