@@ -13,12 +13,14 @@ _MODELS = {}
 
 def _model_for(params, layout, wiring):
     key = (layout, wiring, params.num_filters, params.num_hidden, params.num_rnn_layers, bool(params.use_fp16),
-           getattr(params, "rnn_type", "bi-dir"), getattr(params, "cell", "relu_clip"))
+           getattr(params, "rnn_type", "bi-dir"), getattr(params, "cell", "relu_clip"),
+           getattr(params, "engine", "mkl") if layout == "NCHW" else "tf")
     m = _MODELS.get(key)
     if m is None:
         m = _MODELS[key] = DeepSpeech2(params.num_filters, params.num_hidden, params.num_rnn_layers, layout=layout,
                                        wiring=wiring, cell=getattr(params, "cell", "relu_clip"), use_bf16=bool(params.use_fp16),
-                                       rnn_type=getattr(params, "rnn_type", "bi-dir"), seed=getattr(params, "seed", 1234))
+                                       rnn_type=getattr(params, "rnn_type", "bi-dir"), seed=getattr(params, "seed", 1234),
+                                       engine=key[-1])
     return m
 
 

@@ -12,10 +12,9 @@ from .model import NUM_CLASSES, get_rnn_seqlen  # noqa: F401
 
 
 def model(params):
-    if getattr(params, "engine", "mkl") in ("mkldnn_rnn", "cudnn_rnn"):
-        # src/deepSpeech_NCHW.py:173-176 routes these engines to MkldnnRNNCell (Intel-fork op);
-        # the flat-blob front door lives in mkldnn_rnn_op.py, the model itself uses the same kernels.
-        pass
+    # engine 'mkldnn_rnn' / 'cudnn_rnn' (src/deepSpeech_NCHW.py:173-176) makes the recurrent layers MkldnnRNNRelu cells with
+    # one flat parameter blob each, run through the same sequence kernels (model.DeepSpeech2, mkldnn_rnn_op.py); the NHWC
+    # module ignores `engine`, as the reference's does
     return _model_for(params, "NCHW", getattr(params, "wiring", "stacked"))
 
 

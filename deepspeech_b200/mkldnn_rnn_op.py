@@ -32,6 +32,18 @@ class _MkldnnRNNRelu(object):
         out = ops.relux(_AddFn.apply(ops.linear(input_data.float(), W, bW, False), ops.linear(input_h.float(), U, bU, False)), None)
         return out, out
 
+    def sequence(self, input_data, seq_lengths, params, reverse=False, use_bf16=False):
+        """The whole-sequence form the Intel op really is (src/mkldnn_rnn_op.py:22-29 builds a num_layers=1 sequence op and
+        the reference then calls it once per timestep): input_data [T,B,I] time-major, seq_lengths int32 [B] (device),
+        params the flat blob -> outputs [T,B,H].  One batched W.x GEMM + the recurrence kernels (persistent tcgen05 kernel on
+        the bf16 path), plain ReLU (no clip, no seq-BN scale), bias = b_W + b_U; gradients reach the blob through its views."""
+        H, I = self.num_units, self.input_size
+        W = params[:H * I].view(H, I)
+        U = params[H * I:H * I + H * H].view(1, H, H)
+        bias = (params[H * I + H * H:H * I + H * H + H] + params[H * I + H * H + H:]).view(1, H)
+        odt = torch.bfloat16 if use_bf16 else torch.float32
+        return ops.birnn_layer(input_data, W, U, bias, seq_lengths, 1 if reverse else 0, use_bf16, odt, scale=1.0, cap=3.0e38)
+
 
 class MkldnnRNNCell(object):
     """src/mkldnn_rnn_op.py:16-45.  `sess` is accepted and ignored."""
@@ -53,7 +65,14 @@ class MkldnnRNNCell(object):
     def zero_state(self, batch_size, dtype=torch.float32, device="cuda"):
         return torch.zeros(batch_size, self._num_units, dtype=dtype, device=device)
 
-    def __call__(self, inputs, state, scope=None, weight_size=None):
+    def weights(self, scope=None, device="cuda"):
         sc = scope or type(self).__name__
-        w = _get_variable(sc, "rnn_weights", (self.param_size,), 1.0 / self.param_size, True, inputs.device)  # :39
+        return _get_variable(sc, "rnn_weights", (self.param_size,), 1.0 / self.param_size, True, device)          # :39
+
+    def __call__(self, inputs, state, scope=None, weight_size=None):
+        w = self.weights(scope, inputs.device)
         return self.model(input_data=inputs, input_h=state, params=w, is_training=True)
+
+    def sequence(self, inputs, seq_lengths, scope=None, reverse=False):
+        """All timesteps at once through the sequence kernels, from the same flat blob the per-step call uses."""
+        return self.model.sequence(inputs, seq_lengths, self.weights(scope, inputs.device), reverse, self.use_fp16)

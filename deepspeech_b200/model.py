@@ -26,7 +26,7 @@ def get_rnn_seqlen(seq_lens):
 
 class DeepSpeech2(torch.nn.Module):
     def __init__(self, num_filters=32, num_hidden=1760, num_rnn_layers=7, layout="NCHW", wiring="stacked",
-                 cell="relu_clip", use_bf16=False, rnn_type="bi-dir", seed=1234, device="cuda"):
+                 cell="relu_clip", use_bf16=False, rnn_type="bi-dir", seed=1234, device="cuda", engine="mkl"):
         super().__init__()
         if wiring not in ("as_written", "stacked", "two_stack"):
             raise ValueError("wiring must be as_written | stacked | two_stack")
@@ -34,6 +34,10 @@ class DeepSpeech2(torch.nn.Module):
             raise ValueError("cell must be relu_clip | gru")
         self.nf, self.H, self.L = num_filters, num_hidden, num_rnn_layers
         self.layout, self.wiring, self.cell, self.use_bf16 = layout, wiring, cell, use_bf16
+        # engine 'mkldnn_rnn' / 'cudnn_rnn' (src/deepSpeech_NCHW.py:173-176): the recurrent layers are MkldnnRNNRelu cells -
+        # one FLAT parameter blob per (layer, direction), plain ReLU, no seq-BN, no clip (src/mkldnn_rnn_op.py:22-45)
+        self.engine = engine
+        self.blob_engine = engine in ("mkldnn_rnn", "cudnn_rnn") and cell == "relu_clip" and wiring in ("as_written", "stacked")
         self.bidirectional = rnn_type != "uni-dir"          # src/deepSpeech.py:173
         self.eps = 1e-3 if layout == "NCHW" else 1e-5       # batch_norm2 vs batch_norm (custom_ops.py:111,180)
         rng = np.random.default_rng(seed)
@@ -52,8 +56,14 @@ class DeepSpeech2(torch.nn.Module):
         self.rnn_U = torch.nn.ParameterList()
         self.rnn_B = torch.nn.ParameterList()      # relu: [2,H] ; gru: bw [2,3H]
         self.rnn_BU = torch.nn.ParameterList()     # gru only
+        self.rnn_blob = torch.nn.ParameterList()   # blob engines: [fw_0, bw_0, fw_1, bw_1, ...]
         for l in range(num_rnn_layers):
             I = 75 * nf if (l == 0 or wiring == "as_written") else H
+            if self.blob_engine:
+                n = H * I + H * H + 2 * H
+                for _ in range(2):
+                    self.rnn_blob.append(P(np.full(n, 1.0 / n)))            # src/mkldnn_rnn_op.py:39: constant 1/param_size
+                continue
             self.rnn_W.append(P(np.concatenate([glorot_uniform(rng, (G * H, I)) for _ in range(2)], 0)))
             self.rnn_U.append(P(np.stack([glorot_uniform(rng, (G * H, H)) for _ in range(2)], 0)))
             self.rnn_B.append(P(np.zeros((2, G * H))))
@@ -131,6 +141,15 @@ class DeepSpeech2(torch.nn.Module):
     def recurrent_stack(self, x: torch.Tensor, rnn_lens_dev: torch.Tensor) -> torch.Tensor:
         self._lens = rnn_lens_dev
         act = torch.bfloat16 if self.use_bf16 else torch.float32
+        if self.blob_engine:
+            from .mkldnn_rnn_op import _MkldnnRNNRelu
+            layers = [self.L - 1] if self.wiring == "as_written" else range(self.L)
+            for l in layers:
+                op = _MkldnnRNNRelu(1, self.H, x.shape[2])
+                fw = op.sequence(x, self._lens, self.rnn_blob[2 * l], False, self.use_bf16)
+                bw = op.sequence(x, self._lens, self.rnn_blob[2 * l + 1], True, self.use_bf16)
+                x = _Add.apply(fw, bw)
+            return x
         if self.wiring == "as_written":                      # only the last layer is live
             return self._layer(x, self.L - 1, (0, 1), 0b10, act)
         if self.wiring == "stacked":

@@ -454,17 +454,17 @@ import os as _os0
 USE_FP32_LAYER_SUM = _os0.environ.get("DS2_NO_FP32_LAYER_SUM") is None and _os0.environ.get("DS2_RNN_V1") is None
 
 
-def _relu_recurrence_fwd(wx, Ug, bias, lens, hs, T, B, H, ND, reverse_mask, ws, wsb):
+def _relu_recurrence_fwd(wx, Ug, bias, lens, hs, T, B, H, ND, reverse_mask, ws, wsb, scale=SBN_SCALE, cap=RELU_CAP):
     """Runs the forward recurrence into hs [ND,T,B,H] and returns the tensor the layer output fw + bw
     (src/custom_ops.py:95) is formed from: on the bf16 path the kernel's fp32 copy of the hidden states (values before
     their rounding to bf16: the layer output is then rounded once instead of three times), else hs itself."""
     if hs.dtype == torch.bfloat16 and USE_FP32_LAYER_SUM:
         hs32 = torch.empty((ND, T, B, H), dtype=torch.float32, device=hs.device)
-        check(lib.ds2_rnn_relu_fwd_ex(_p(wx), SBN_SCALE, _p(Ug), _p(bias), _p(lens), _p(hs), _p(hs32), T, B, H, ND,
-                                      reverse_mask, RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_fwd_ex")
+        check(lib.ds2_rnn_relu_fwd_ex(_p(wx), scale, _p(Ug), _p(bias), _p(lens), _p(hs), _p(hs32), T, B, H, ND,
+                                      reverse_mask, cap, _p(ws), wsb, _stream()), "ds2_rnn_relu_fwd_ex")
         return hs32
-    check(lib.ds2_rnn_relu_fwd(_p(wx), SBN_SCALE, _p(Ug), _p(bias), _p(lens), _p(hs), _dt(hs), T, B, H, ND,
-                               reverse_mask, RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_fwd")
+    check(lib.ds2_rnn_relu_fwd(_p(wx), scale, _p(Ug), _p(bias), _p(lens), _p(hs), _dt(hs), T, B, H, ND,
+                               reverse_mask, cap, _p(ws), wsb, _stream()), "ds2_rnn_relu_fwd")
     return hs
 
 
@@ -477,7 +477,7 @@ class _BiRNNLayerFn(torch.autograd.Function):
        Gradients flow in fp32 between layers (x.grad has x's dtype)."""
 
     @staticmethod
-    def forward(ctx, x, Wcat, U, bias, lens, reverse_mask, want_bf16, out_dtype):
+    def forward(ctx, x, Wcat, U, bias, lens, reverse_mask, want_bf16, out_dtype, scale=SBN_SCALE, cap=RELU_CAP):
         T, B, I = x.shape
         ND, H = U.shape[0], U.shape[1]
         dev = x.device
@@ -490,19 +490,21 @@ class _BiRNNLayerFn(torch.autograd.Function):
         hs = torch.empty((ND, T, B, H), dtype=cdt, device=dev)
         wsb = lib.ds2_rnn_workspace_bytes(T, B, H, ND, _dt(hs))
         ws = _workspace(wsb, dev, "rnn") if wsb else None
-        src = _relu_recurrence_fwd(wx, Ug, bias, lens, hs, T, B, H, ND, reverse_mask, ws, wsb)
+        src = _relu_recurrence_fwd(wx, Ug, bias, lens, hs, T, B, H, ND, reverse_mask, ws, wsb, scale, cap)
         if ND == 2:
             out = add2(src[0], src[1], out_dtype)
         else:
             out = cast(src[0], out_dtype)
         ctx.save_for_backward(xg, Wg, Ug, hs, lens)
         ctx.meta = (T, B, I, H, ND, reverse_mask, x.dtype)
+        ctx.scale_cap = (float(scale), float(cap))
         return out
 
     @staticmethod
     def backward(ctx, dout):
         xg, Wg, Ug, hs, lens = ctx.saved_tensors
         T, B, I, H, ND, reverse_mask, xdtype = ctx.meta
+        scale, cap = ctx.scale_cap
         dev = xg.device
         cdt = hs.dtype
         dout = cast(dout.contiguous(), torch.float32)
@@ -511,13 +513,13 @@ class _BiRNNLayerFn(torch.autograd.Function):
         ws = _workspace(wsb, dev, "rnn") if wsb else None
         db = torch.empty((ND, H), dtype=torch.float32, device=dev)
         check(lib.ds2_rnn_relu_bwd(_p(dout), _p(Ug), _p(lens), _p(hs), _p(dz), _p(db), _dt(hs), T, B, H, ND, reverse_mask,
-                                   RELU_CAP, _p(ws), wsb, _stream()), "ds2_rnn_relu_bwd")
+                                   cap, _p(ws), wsb, _stream()), "ds2_rnn_relu_bwd")
         # dW = scale * dz^T x ; dx = scale * dz W   (both directions in one GEMM each)
         dW = torch.empty((ND * H, I), dtype=torch.float32, device=dev)
-        gemm_wgrad(dz, xg.view(T * B, I), ND * H, I, T * B, ND * H, I, dW, alpha=SBN_SCALE)    # [ND*H, I]
+        gemm_wgrad(dz, xg.view(T * B, I), ND * H, I, T * B, ND * H, I, dW, alpha=scale)    # [ND*H, I]
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = gemm_nt(dz, Wg, b_mn=True, alpha=SBN_SCALE).view(T, B, I)                   # [TB, I] fp32
+            dx = gemm_nt(dz, Wg, b_mn=True, alpha=scale).view(T, B, I)                   # [TB, I] fp32
             if xdtype != torch.float32:
                 dx = cast(dx, xdtype)
         # dU[d] = sum_t dz[d,t]^T h[d,t_prev]
@@ -531,12 +533,16 @@ class _BiRNNLayerFn(torch.autograd.Function):
                 gemm_wgrad(A, Bm, H, H, (T - 1) * B, ND * H, H, dU[d])
             else:
                 dU[d].zero_()
-        return dx, dW, dU, db, None, None, None, None
+        return dx, dW, dU, db, None, None, None, None, None, None
 
 
-def birnn_layer(x, Wcat, U, bias, lens, reverse_mask: int, want_bf16: bool, out_dtype):
+def birnn_layer(x, Wcat, U, bias, lens, reverse_mask: int, want_bf16: bool, out_dtype, scale: float = SBN_SCALE,
+                cap: float = RELU_CAP):
+    """scale multiplies W.x (the reference's seq-BN constant by default), cap clips the ReLU (3e38: plain ReLU, the
+    MkldnnRNNRelu cell of src/mkldnn_rnn_op.py)."""
     _need_cuda(x, Wcat, U, bias, lens)
-    return _BiRNNLayerFn.apply(x, Wcat.contiguous(), U.contiguous(), bias.contiguous(), lens, reverse_mask, want_bf16, out_dtype)
+    return _BiRNNLayerFn.apply(x, Wcat.contiguous(), U.contiguous(), bias.contiguous(), lens, reverse_mask, want_bf16, out_dtype,
+                               float(scale), float(cap))
 
 
 def gru_path_dtype(B: int, H: int, ND: int, want_bf16: bool):

@@ -163,6 +163,9 @@ def rnn_direction(x, lens, cell_params, reverse: bool, cell: str = "relu_clip", 
             hn = relux(z, RELU_CAP)
         elif cell == "relu_clip":
             hn = rnn_cell_step(x[t], h, cell_params["W"], cell_params["U"], cell_params["B"], sbn)
+        elif cell == "relu_plain":
+            # src/mkldnn_rnn_op.py:22-45 (MkldnnRNNRelu: plain ReLU, no seq-BN, no clip; build-defined)
+            hn = torch.relu(x[t] @ cell_params["W"].t() + h @ cell_params["U"].t() + cell_params["B"])
         else:
             hn = gru_cell_step(x[t], h, cell_params["W"], cell_params["U"], cell_params["BW"],
                                cell_params["BU"], sbn)
