@@ -49,6 +49,7 @@ _SIGS = {
     "ds2_set_sm_limit": (I, [I]),
     "ds2_ctc_greedy_decode": (I, [P, I, I, I, P, P, P, P]),
     "ds2_ctc_labels_from_sparse": (I, [P, P, I, I, I, I, I, P, P, P, P, P]),
+    "ds2_dummy_sparse_labels": (I, [P, P, I, I, P, P, P]),
     "ds2_edit_distance": (I, [P, I, P, P, I, P, I, I, P, P]),
     "ds2_adam_ema_chunk": (I, []),
     "ds2_adam_ema_step": (I, [P, I, I, F, F, F, F, L, F, F, P]),

@@ -161,3 +161,30 @@ extern "C" int ds2_ctc_labels_from_sparse(const long long* indices, const int* v
   count_launch();
   return DS2_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Dummy-batch labels on the device (src/deepSpeech_dummy.py:89-98 `_dense_to_sparse` + :115-118): every utterance of a
+// batch carries the SAME label row; the zero labels are dropped.  nz_pos / nz_val are that row's non-zero positions and
+// values (<= 209 entries); the SparseTensor triple of src/deepSpeech_train.py:437 comes back as indices [B*nnz, 2]
+// (row-major sorted) and values [B*nnz].
+namespace ds2 {
+__global__ void __launch_bounds__(256) dummy_sparse_kernel(const int* __restrict__ nz_pos, const int* __restrict__ nz_val, int nnz, int B,
+                                                           long long* __restrict__ indices, int* __restrict__ values) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * nnz) return;
+  const int b = i / nnz, j = i - b * nnz;
+  indices[2 * (size_t)i] = b;
+  indices[2 * (size_t)i + 1] = nz_pos[j];
+  values[i] = nz_val[j];
+}
+}  // namespace ds2
+
+extern "C" int ds2_dummy_sparse_labels(const int* nz_pos, const int* nz_val, int nnz, int B, long long* indices, int* values, void* stream) {
+  DS2_REQUIRE(nnz >= 0 && B > 0, DS2_ERR_BAD_SHAPE, "ds2_dummy_sparse_labels: bad shape nnz=%d B=%d", nnz, B);
+  if (nnz == 0) return DS2_OK;
+  DS2_REQUIRE(nz_pos && nz_val && indices && values, DS2_ERR_BAD_ARG, "ds2_dummy_sparse_labels: null pointer");
+  ds2::dummy_sparse_kernel<<<(B * nnz + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(nz_pos, nz_val, nnz, B, indices, values);
+  DS2_LAUNCH_CHECK("dummy_sparse_kernel");
+  ds2::count_launch();
+  return DS2_OK;
+}

@@ -23,5 +23,10 @@ def ctc_loss(labels, inputs, sequence_length, preprocess_collapse_repeated=False
         raise ValueError("ctc_loss: inputs must be [max_time, batch, num_classes]")
     indices, values, dense_shape = labels
     K = inputs.shape[2]
+    if isinstance(indices, torch.Tensor) and indices.is_cuda and isinstance(values, torch.Tensor) and values.is_cuda:
+        # labels already on the device (e.g. deepSpeech_dummy.DeviceDummyData): pre-processing and checks stay there, the
+        # step never waits for the host.  A row tf.nn.ctc_loss would raise for - a valid label after a terminator, or fewer
+        # frames than labels + repeats - comes back with loss = +inf and a zero gradient row instead of an exception.
+        return ops.ctc_loss_sparse_device(inputs, indices, values, dense_shape, sequence_length, preprocess_collapse_repeated)
     lab, ll, reps = ops.ctc_prepare_labels(indices, values, dense_shape, K, preprocess_collapse_repeated)
     return ops.ctc_loss_dense(inputs, lab, ll, reps, sequence_length)

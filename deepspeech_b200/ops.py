@@ -1020,3 +1020,25 @@ def ctc_loss_dense(logits: torch.Tensor, labels_np, label_lens_np, repeats_np, s
     ll_d = packed[B * Lmax:B * Lmax + B]
     sl_d = packed[B * Lmax + B:]
     return _CTCFn.apply(logits.contiguous(), lab_d, ll_d, sl_d, Lmax)
+
+
+def ctc_loss_sparse_device(logits: torch.Tensor, indices: torch.Tensor, values: torch.Tensor, dense_shape, seq_lens,
+                           preprocess_collapse_repeated: bool) -> torch.Tensor:
+    """tf.nn.ctc_loss on SparseTensor labels that live on the device: label pre-processing (ds2_ctc_labels_from_sparse) and
+    the loss without any device -> host transfer.  Rows that TF would reject carry label_len = -1 into the kernels, which
+    answer loss = +inf and a zero gradient row (include/ds2_b200.h)."""
+    _need_cuda(logits, indices, values)
+    if logits.dtype != torch.float32:
+        logits = cast(logits, torch.float32)
+    T, B, K = logits.shape
+    if int(dense_shape[0]) != B:
+        raise ValueError("ctc_loss: batch size mismatch (logits %d, labels %d)" % (B, int(dense_shape[0])))
+    lab, ll, reps, status = ctc_prepare_labels_device(indices, values, dense_shape, K, preprocess_collapse_repeated)
+    if isinstance(seq_lens, torch.Tensor):
+        sl = seq_lens.to(device=logits.device, dtype=torch.int32, non_blocking=True)
+    else:
+        sl = torch.from_numpy(np.ascontiguousarray(seq_lens, dtype=np.int32)).to(logits.device, non_blocking=True)
+    if sl.shape[0] != B:
+        raise ValueError("ctc_loss: batch size mismatch (logits %d, sequence_length %d)" % (B, sl.shape[0]))
+    ll = torch.where(status != 0, torch.full_like(ll, -1), ll)
+    return _CTCFn.apply(logits.contiguous(), lab, ll, sl, lab.shape[1])

@@ -251,6 +251,10 @@ int ds2_edit_distance(const int* a, int lda, const int* a_lens, const int* b, in
  * The host form with the reference's exceptions is deepspeech_b200.ops.ctc_prepare_labels. */
 int ds2_ctc_labels_from_sparse(const long long* indices, const int* values, int n, int B, int Lcap, int num_classes,
                                int collapse_repeated, int* labels, int* label_lens, int* repeats, int* status, void* stream);
+/* The label half of the dummy batch producer on the device (src/deepSpeech_dummy.py:89-98, :115-118): one label row shared
+ * by all B utterances, zeros dropped; nz_pos / nz_val [nnz] are the row's non-zero positions and values (device);
+ * indices [B*nnz,2] int64 and values [B*nnz] int32 are the SparseTensor of src/deepSpeech_train.py:437. */
+int ds2_dummy_sparse_labels(const int* nz_pos, const int* nz_val, int nnz, int B, long long* indices, int* values, void* stream);
 
 #ifdef __cplusplus
 }

@@ -97,3 +97,45 @@ def test_linear_and_custom_rnn_cell_positive_paths():
     refc = np.clip(np.concatenate([x.cpu().numpy(), h.cpu().numpy()], 1).astype(np.float64) @ Mc.T, 0.0, 6.0)
     assert out is state and _rel(out.detach().cpu().numpy(), refc) < 1e-5
     assert cell.output_size == H and cell.zero_state(3).shape == (3, H)
+
+
+def test_device_dummy_producer_matches_host_generator_bit_for_bit():
+    """the device-side dummy batch producer against the host generator with the same seed - features,
+    SparseTensor indices / values, shapes and lengths identical over a walk through the bucket schedule."""
+    from deepspeech_b200.deepSpeech_dummy import DeviceDummyData, DummyData
+    host, dev = DummyData(4, seed=11), DeviceDummyData(4, seed=11)
+    for step in range(40):
+        f0, i0, v0, s0, l0 = host.inputs()
+        f1, i1, v1, s1, l1 = dev.inputs()
+        assert f1.is_cuda and i1.is_cuda and v1.is_cuda
+        assert np.array_equal(f0, f1.cpu().numpy()) and np.array_equal(i0, i1.cpu().numpy()) and np.array_equal(v0, v1.cpu().numpy())
+        assert np.array_equal(s0, s1) and np.array_equal(l0, l1)
+    assert host.current == dev.current
+
+
+def test_ctc_loss_with_device_labels_matches_host_path_and_flags_bad_rows():
+    from deepspeech_b200 import ctc
+    rng = np.random.default_rng(8)
+    T, B, K, L = 40, 6, 29, 9
+    x = torch.tensor(rng.standard_normal((T, B, K)), dtype=torch.float32, device="cuda")
+    dense = rng.integers(0, 28, size=(B, L))
+    dense[:, -1] = 28                                                   # the dummy generator's terminator
+    keep = dense != 0
+    idx = np.argwhere(keep).astype(np.int64)
+    vals = dense[keep].astype(np.int32)
+    sl = np.full(B, T, np.int32)
+    xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    la = ctc.ctc_loss((idx, vals, np.asarray([B, L])), xa, sl, preprocess_collapse_repeated=True)
+    lb = ctc.ctc_loss((torch.from_numpy(idx).cuda(), torch.from_numpy(vals).cuda(), np.asarray([B, L])), xb, sl, preprocess_collapse_repeated=True)
+    la.sum().backward(); lb.sum().backward()
+    assert torch.equal(la, lb) and torch.equal(xa.grad, xb.grad)
+    # a row with too few frames: the host path raises as TF does, the device path answers inf and a zero gradient row
+    sl2 = sl.copy(); sl2[2] = 3
+    with pytest.raises(ValueError):
+        ctc.ctc_loss((idx, vals, np.asarray([B, L])), x, sl2, preprocess_collapse_repeated=True)
+    xc = x.clone().requires_grad_(True)
+    lc = ctc.ctc_loss((torch.from_numpy(idx).cuda(), torch.from_numpy(vals).cuda(), np.asarray([B, L])), xc, sl2, preprocess_collapse_repeated=True)
+    ok = torch.ones(B, dtype=torch.bool, device="cuda"); ok[2] = False
+    lc[ok].sum().backward()
+    assert torch.isinf(lc[2]) and torch.isfinite(lc[ok]).all() and torch.equal(lc[ok], la[ok].detach())
+    assert xc.grad[:, 2].abs().max().item() == 0.0
