@@ -9,7 +9,8 @@
   src/deepSpeech_test.py:218-220) and the global step.
 
 The container is numpy's .npz (TensorFlow's own checkpoint format needs TensorFlow): one array per variable under the
-variable's name.  Values are fp32 bit patterns, so save -> load -> next step is bit-identical (tests/test_gpu_checkpoint.py).
+variable's name.  Values are fp32 bit patterns: the restored state equals the saved one bit for bit and the next step's loss
+is identical (tests/test_gpu_checkpoint.py; its gradients are atomic sums, reproducible to fp32 round-off only).
 Host-side code: tensors cross the PCIe bus once per save / restore, nothing here is on the timed path."""
 from __future__ import annotations
 
