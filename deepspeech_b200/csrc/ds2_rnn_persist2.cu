@@ -258,6 +258,7 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
       unsigned int round = 0;                    // fetches issued so far = id of the last one (0: none yet)
       const unsigned int* poll = ctr;            // the counter copy this thread polls
       long long best_rt = 0x7fffffffffffffffll;
+      long long wait_sum = 0, fetch_sum = 0;       // DS2_RNN_PROF: per-CTA totals (waiting for the others / fetch + MMA issue)
       // fetch the operand image at `src`, issue the step's MMAs, hand the accumulators over
       auto fetch_and_issue = [&]() {
         mbar_arrive_expect_tx(copy_bar_a, img_bytes);
@@ -271,7 +272,7 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
       };
       // step == T: nothing to fetch, but the last step's fetch may still have to be repeated
       for (int step = 1; step <= T; ++step) {
-        const bool pr = prof_cta && step < 1024;
+        const bool pr = prof_cta && step < 512;
         if (pr) p.prof[step * 16 + 0] = dev_clock();
         // every CTA of this direction has published step-1 of this instance
         const unsigned int need = arrivals_per_step * (unsigned int)step;
@@ -297,12 +298,25 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
             const long long rt = (dev_clock() - t0) / npoll;
             if (rt < best_rt) { best_rt = rt; poll = q; }
           }
+          if (p.prof && step > 2 * NCOPY) wait_sum += dev_clock() - t0;
         }
         if (step == T) break;
         if (pr) p.prof[step * 16 + 1] = dev_clock();
+        const long long tf0 = p.prof ? dev_clock() : 0;
         src = my_img + (size_t)((step - 1) % RING) * slot_stride;
         fetch_and_issue();
         if (pr) p.prof[step * 16 + 4] = dev_clock();
+        if (p.prof) fetch_sum += dev_clock() - tf0;
+      }
+      if (p.prof && inst == 0) {
+        // per-CTA totals behind the per-step stamps of CTA 0: 4 values per CTA from slot 8192 on
+        const int cta = (blockIdx.z * gridDim.y + blockIdx.y) * KS + (int)rank;
+        unsigned int sm;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+        p.prof[8192 + cta * 4 + 0] = wait_sum;
+        p.prof[8192 + cta * 4 + 1] = fetch_sum;
+        p.prof[8192 + cta * 4 + 2] = (long long)sm;
+        p.prof[8192 + cta * 4 + 3] = (long long)(poll - ctr) / CTR_COPY_STRIDE;
       }
     }
     __syncwarp();
@@ -341,7 +355,7 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
     uint32_t phc = 0, pho = 0, phm = 0, phs = 0, vround = 0;
     int t = t_first;
     for (int step = 0; step < T; ++step, t += (int)t_inc, add_ptr += add_inc, out_ptr += out_inc) {
-      const bool pr = prof_cta && et == 0 && step < 1024;
+      const bool pr = prof_cta && et == 0 && step < 512;
       // prefetch the additive term (s*Wx_t or dout_t) and, for the backward, h_t for the mask
       float4 add = make_float4(0.f, 0.f, 0.f, 0.f);
       uint2 hm = make_uint2(0u, 0u);

@@ -64,3 +64,17 @@ else:
     print("control: counter seen -> copy landed, MMAs issued, commit: mean %.1f cyc;  re-fetches: %d" % (g.mean(), int(S[:, 7].sum())))
     g = (s[:, 12] - s[:, 1]).astype(np.float64)
     print("counter seen -> own publication: mean %.1f cyc  (the rest of the step is the wait for the other CTAs)" % g.mean())
+if not os.environ.get("DS2_RNN_V1"):
+    # per-CTA totals (instance 0): time spent waiting for the other CTAs and in fetch + MMA issue, SM id, counter copy polled
+    nct = 4 * ((H + 127) // 128) * 2
+    C = ws[2048 + 8192 * 8:2048 + (8192 + nct * 4) * 8].view(torch.int64).cpu().numpy().reshape(-1, 4)
+    steps = T - 1 - 8
+    wait, fetch = C[:, 0] / steps, C[:, 1] / max(T - 1, 1)
+    order = np.argsort(wait)
+    print("per-CTA (instance 0): wait for the others / fetch+issue, clk per step; the CTAs that wait least set the pace")
+    print("  wait: min %.0f  p10 %.0f  median %.0f  p90 %.0f  max %.0f   fetch+issue: min %.0f median %.0f max %.0f"
+          % (wait.min(), np.percentile(wait, 10), np.median(wait), np.percentile(wait, 90), wait.max(), fetch.min(), np.median(fetch), fetch.max()))
+    for i in list(order[:8]) + list(order[-4:]):
+        d, rest = divmod(int(i), nct // 2)
+        print("   dir %d tile %2d rank %d  sm %3d  copy %d: wait %5.0f  fetch+issue %5.0f" % (d, rest // 4, rest % 4, C[i, 2], C[i, 3], wait[i], fetch[i]))
+    print("  counter copies chosen: %s" % np.bincount(C[:, 3].astype(int), minlength=4))
