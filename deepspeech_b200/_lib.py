@@ -62,7 +62,8 @@ _SIGS = {
     "ds2_conv2d_wgrad": (I, [P, I, P, P, P, I, I, I, I, I, I, I, I, I, P]),
     "ds2_conv_window_supported": (I, [I, I, I, I, I, I]),
     "ds2_conv_window_weights": (I, [P, P, P, I, I, P]),
-    "ds2_conv_window_pad_cast": (I, [P, P, L, I, I, P]),
+    "ds2_conv_window_dy_layout": (I, [I, I, I, I, I, P, P]),
+    "ds2_conv_window_pad_cast": (I, [P, P, I, I, I, I, I, I, P]),
     "ds2_conv_window_fwd": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "ds2_conv_window_dgrad": (I, [P, P, P, I, I, I, I, I, I, P]),
     "ds2_conv_window_wgrad": (I, [P, P, P, I, I, I, I, I, I, P]),

@@ -10,14 +10,22 @@
 // (two filter taps x 32 channels) as a 128-byte-swizzled K-major tile, one per output position.  A filter row of KF
 // taps is KF/2 such chunks plus a half chunk (32 elements: only two of the four K=16 MMA steps are issued).
 // Positions beyond the row are out of bounds for the map and arrive as zeros.
-//   forward : tile = output row (b,to), M = 128 positions (Fo valid), N = 32 filters, K-blocks = KT x chunks,
-//             source rows b*Ti + to*st + kt, weights Wt[co][(kt,kf,ci)].
-//   dgrad   : tile = input row (b,t1), source = dy zero-padded by KF-1 positions on both sides, K-blocks over the
-//             kt with (t1-kt) % st == 0 and to = (t1-kt)/st in range, weights Wd[ci][(kt,KF-1-kf,co)].
+// A row of conv2 has 75 output positions, 79 for the data gradient: one row per 128-row MMA tile would idle 40 % of the
+// tensor pipe.  So a tile PACKS rows: the box is {64, PB positions, RB rows} with PB * RB <= 128 (75 -> 3 passes of 25
+// positions x 5 rows = 125 MMA rows; 79 -> 5 passes of 16 x 8 = 128), landing as PB*RB consecutive 128-byte rows.
+//   forward : tile = (b, group of RB output rows, position pass), M = 128, N = 32 filters, K-blocks = KT x chunks.
+//             Output rows to, to+1, .. read source rows st apart: one tensor map per residue of the source row modulo st
+//             (base shifted by that many rows, row pitch st times the tensor's), so that a box takes RB consecutive rows
+//             of its map.  Weights Wt[co][(kt,kf,ci)].
+//   dgrad   : tile = (b, residue of the input row t1 modulo st, group of RB such rows, pass); source = dy zero-padded by
+//             KF-1 positions on both sides AND by zero rows above and below every batch item (the rows to = (t1-kt)/st
+//             outside [0,To) then read zeros, whichever item's memory they fall into); K-blocks over the kt of the same
+//             residue, source rows consecutive.  Weights Wd[ci][(kt,KF-1-kf,co)].
 //   wgrad   : dW[(kt,kf,ci)][co] = sum over tiles of window^T . dy : the same boxes read as MN-major A operands
-//             (M = 64 window elements per box, two boxes per MMA block), dy rows as the MN-major B operand, all
-//             KT*KF*32 x 32 partial sums of a CTA resident in TMEM (15 blocks x 32 columns) until it has run out of
-//             tiles, then red.add into dW.
+//             (M = 64 window elements per box, two boxes per MMA block), the packed dy rows as the MN-major B operand
+//             (contraction over the PB*RB packed rows; the stage buffers are zeroed once, rows the boxes never write
+//             stay zero), all KT*KF*32 x 32 partial sums of a CTA resident in TMEM (15 blocks x 32 columns) until it has
+//             run out of tiles, then red.add into dW.
 #include "common.cuh"
 
 namespace ds2 {
@@ -33,12 +41,21 @@ static constexpr int CWG_STAGES = 4;             // wgrad: two window boxes + on
 static constexpr int CWG_STAGE_BYTES = 3 * CW_BOX;
 static constexpr int CWG_SMEM = CWG_STAGES * CWG_STAGE_BYTES + 1024 + 256;
 
+static constexpr int CW_MAXST = 4;               // row packing needs one source map per residue modulo the time stride
+struct WinMaps {
+  CUtensorMap m[CW_MAXST];
+};
 struct WinParams {
   float* out;            // fwd: y [B,Rout,Pout,32] ; dgrad: da [B,Rout,Pout,32] ; wgrad: dW [KT*KF*32][32]
   const float* bias;     // fwd only
-  int n_tiles;           // B * Rout
-  int Rout, Rsrc;        // rows per batch item of the output / of the source
+  int n_tiles;           // B * classes * G * np
+  int Rout, Rsrc;        // rows per batch item of the output / of the source (dgrad, wgrad dy: padded rows per item)
   int Pout;              // valid positions per output row
+  int PB, RB, np, G;     // packing: positions and rows per box, position passes, row groups per batch item (and class)
+  int ncls;              // dgrad: st residue classes of the output row; otherwise 1
+  int nmaps;             // fwd / wgrad source maps: st (one per residue) or 1 (RB == 1: plain rows)
+  int ptop;              // dgrad / wgrad: zero rows above every batch item in the padded dy
+  int Rdy;               // wgrad: rows per batch item of the padded dy
   int KT, st;
   int nfull, half;       // 64-element chunks per filter row, and whether a 32-element one follows
   int kstride;           // K elements per filter row (KF * 32)
@@ -46,25 +63,37 @@ struct WinParams {
   int dgrad;
 };
 
-// K-blocks of a tile, the same enumeration for the producer and the MMA warp.
-struct KtIter {
-  int kt, row;           // filter row and source row; row < 0: none left
+// tile index -> batch item, residue class, row group, position pass (pass fastest: the passes of a row group read the
+// same source rows back to back)
+struct TileId {
+  int b, cls, g, q;
 };
-__device__ __forceinline__ bool kt_source(const WinParams& p, int b, int r, int kt, int* src_row) {
+__device__ __forceinline__ TileId tile_decode(const WinParams& p, int tile) {
+  TileId t;
+  t.q = tile % p.np;
+  tile /= p.np;
+  t.g = tile % p.G;
+  tile /= p.G;
+  t.cls = tile % p.ncls;
+  t.b = tile / p.ncls;
+  return t;
+}
+// source map and first row coordinate of filter row kt for the tile's first packed row; false: kt not in the tile's class
+__device__ __forceinline__ bool kt_source(const WinParams& p, const TileId& t, int kt, int* map, int* row) {
   if (!p.dgrad) {
-    *src_row = b * p.Rsrc + r * p.st + kt;
+    const int r0 = t.b * p.Rsrc + t.g * p.RB * p.st + kt;
+    if (p.nmaps == 1) { *map = 0; *row = r0; }
+    else { *map = r0 % p.st; *row = r0 / p.st; }
     return true;
   }
-  const int d = r - kt;
-  if (d < 0 || d % p.st != 0) return false;
-  const int to = d / p.st;
-  if (to >= p.Rsrc) return false;
-  *src_row = b * p.Rsrc + to;
+  if (kt % p.st != t.cls) return false;
+  *map = 0;
+  *row = t.b * p.Rsrc + p.ptop + (t.cls - kt) / p.st + t.g * p.RB;     // (cls - kt) is a non-positive multiple of st
   return true;
 }
 
 __global__ void __launch_bounds__(CW_THREADS, 1)
-conv_window_kernel(const __grid_constant__ CUtensorMap tmap_src, const __grid_constant__ CUtensorMap tmap_w, WinParams p) {
+conv_window_kernel(const __grid_constant__ WinMaps maps, const __grid_constant__ CUtensorMap tmap_w, WinParams p) {
   extern __shared__ __align__(1024) uint8_t cw_smem_raw[];
   const uint32_t sbase = (smem_u32(cw_smem_raw) + 1023u) & ~1023u;
   const uint32_t bars = sbase + CW_STAGES * CW_STAGE_BYTES;
@@ -75,8 +104,9 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmap_src, const __grid_co
   const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const int nch = p.nfull + p.half;
 
+  const uint32_t box_bytes = (uint32_t)p.PB * p.RB * 128u;
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmap_src);
+    for (int i = 0; i < p.nmaps; ++i) tma_prefetch_desc(&maps.m[i]);
     tma_prefetch_desc(&tmap_w);
   }
   if (warp == 1 && lane == 0) {
@@ -102,18 +132,18 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmap_src, const __grid_co
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-        const int b = tile / p.Rout, r = tile - b * p.Rout;
+        const TileId t = tile_decode(p, tile);
         for (int kt = 0; kt < p.KT; ++kt) {
-          int src_row;
-          if (!kt_source(p, b, r, kt, &src_row)) continue;
+          int mi, src_row;
+          if (!kt_source(p, t, kt, &mi, &src_row)) continue;
           for (int c = 0; c < nch; ++c) {
             mbar_wait(empty_bar + 8 * stage, phase ^ 1, 100 + stage);
             const uint32_t sa = sbase + stage * CW_STAGE_BYTES;
-            mbar_arrive_expect_tx(full_bar + 8 * stage, CW_BOX + CW_WBOX);
+            mbar_arrive_expect_tx(full_bar + 8 * stage, box_bytes + CW_WBOX);
             asm volatile(
                 "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-                ::"r"(sa), "l"(reinterpret_cast<uint64_t>(&tmap_src)), "r"(full_bar + 8 * stage), "r"(0), "r"(p.win0 + 2 * c),
-                "r"(src_row)
+                ::"r"(sa), "l"(reinterpret_cast<uint64_t>(&maps.m[mi])), "r"(full_bar + 8 * stage), "r"(0),
+                "r"(p.win0 + t.q * p.PB + 2 * c), "r"(src_row)
                 : "memory");
             asm volatile(
                 "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
@@ -133,14 +163,14 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmap_src, const __grid_co
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-      const int b = tile / p.Rout, r = tile - b * p.Rout;
+      const TileId t = tile_decode(p, tile);
       mbar_wait(tempty_bar + 8 * acc, acc_phase ^ 1, 200 + acc);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * CW_C;
       bool first = true;
       for (int kt = 0; kt < p.KT; ++kt) {
-        int src_row;
-        if (!kt_source(p, b, r, kt, &src_row)) continue;
+        int mi, src_row;
+        if (!kt_source(p, t, kt, &mi, &src_row)) continue;
         for (int c = 0; c < nch; ++c) {
           mbar_wait(full_bar + 8 * stage, phase, 300 + stage);
           tc_fence_after();
@@ -171,12 +201,15 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmap_src, const __grid_co
     float bias[CW_C];
 #pragma unroll
     for (int j = 0; j < CW_C; ++j) bias[j] = p.bias ? __ldg(p.bias + j) : 0.f;
+    // accumulator row of this thread -> packed row and position inside the box
+    const int mrow = wq * 32 + lane;
+    const int pi = mrow / p.PB, pp = mrow - pi * p.PB;
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-      const int b = tile / p.Rout, r = tile - b * p.Rout;
+      const TileId t = tile_decode(p, tile);
       bool any = false;
       for (int kt = 0; kt < p.KT; ++kt) {
-        int src_row;
-        any |= kt_source(p, b, r, kt, &src_row);
+        int mi, src_row;
+        any |= kt_source(p, t, kt, &mi, &src_row);
       }
       mbar_wait(tfull_bar + 8 * acc, acc_phase, 400 + acc);
       tc_fence_after();
@@ -186,9 +219,10 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmap_src, const __grid_co
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty_bar + 8 * acc);
-      const int pos = wq * 32 + lane;
-      if (pos < p.Pout) {
-        float4* dst = reinterpret_cast<float4*>(p.out + ((size_t)tile * p.Pout + pos) * CW_C);
+      const int pos = t.q * p.PB + pp;
+      const int r = p.dgrad ? t.cls + p.st * (t.g * p.RB + pi) : t.g * p.RB + pi;
+      if (pi < p.RB && pos < p.Pout && r < p.Rout) {
+        float4* dst = reinterpret_cast<float4*>(p.out + (((size_t)t.b * p.Rout + r) * p.Pout + pos) * CW_C);
 #pragma unroll
         for (int j = 0; j < CW_C; j += 4) {
           float4 o;
@@ -212,7 +246,7 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmap_src, const __grid_co
 
 // ------------------------------------------------------------------ weight gradient
 __global__ void __launch_bounds__(CW_THREADS, 1)
-conv_window_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_dy, WinParams p) {
+conv_window_wgrad_kernel(const __grid_constant__ WinMaps maps, const __grid_constant__ CUtensorMap tmap_dy, WinParams p) {
   extern __shared__ __align__(1024) uint8_t cwg_smem_raw[];
   const uint32_t sbase = (smem_u32(cwg_smem_raw) + 1023u) & ~1023u;
   const uint32_t bars = sbase + CWG_STAGES * CWG_STAGE_BYTES;
@@ -224,10 +258,16 @@ conv_window_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   const int ngroups = p.KT * nch;                  // 64-wide groups of window elements; two per MMA block
   const int nblocks = (ngroups + 1) / 2;
 
+  const uint32_t box_bytes = (uint32_t)p.PB * p.RB * 128u;
+  const int ksteps = (p.PB * p.RB + 15) / 16;       // contraction over the packed rows, 16 per MMA
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmap_a);
+    for (int i = 0; i < p.nmaps; ++i) tma_prefetch_desc(&maps.m[i]);
     tma_prefetch_desc(&tmap_dy);
   }
+  // rows of a stage buffer that no box writes are part of the contraction: zero once
+  for (uint32_t o = threadIdx.x * 16u; o < (uint32_t)(CWG_STAGES * CWG_STAGE_BYTES); o += CW_THREADS * 16u)
+    sts_v4(sbase + o, make_uint4(0u, 0u, 0u, 0u));
+  fence_proxy_async();
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < CWG_STAGES; ++i) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full_bar + 8 * i), "r"(1));
@@ -248,24 +288,26 @@ conv_window_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-        const int b = tile / p.Rout, r = tile - b * p.Rout;        // Rout = To here
+        const TileId t = tile_decode(p, tile);
         for (int blk = 0; blk < nblocks; ++blk) {
           mbar_wait(empty_bar + 8 * stage, phase ^ 1, 100 + stage);
           const uint32_t sa = sbase + stage * CWG_STAGE_BYTES;
           const int ng = min(2, ngroups - 2 * blk);
-          mbar_arrive_expect_tx(full_bar + 8 * stage, (ng + 1) * CW_BOX);
+          mbar_arrive_expect_tx(full_bar + 8 * stage, (ng + 1) * box_bytes);
           for (int g = 0; g < ng; ++g) {
             const int gi = 2 * blk + g, kt = gi / nch, c = gi - kt * nch;
+            int mi, src_row;
+            kt_source(p, t, kt, &mi, &src_row);
             asm volatile(
                 "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-                ::"r"(sa + g * CW_BOX), "l"(reinterpret_cast<uint64_t>(&tmap_a)), "r"(full_bar + 8 * stage), "r"(0), "r"(2 * c),
-                "r"(b * p.Rsrc + r * p.st + kt)
+                ::"r"(sa + g * CW_BOX), "l"(reinterpret_cast<uint64_t>(&maps.m[mi])), "r"(full_bar + 8 * stage), "r"(0),
+                "r"(t.q * p.PB + 2 * c), "r"(src_row)
                 : "memory");
           }
           asm volatile(
               "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-              ::"r"(sa + 2 * CW_BOX), "l"(reinterpret_cast<uint64_t>(&tmap_dy)), "r"(full_bar + 8 * stage), "r"(0), "r"(p.win0),
-              "r"(tile)
+              ::"r"(sa + 2 * CW_BOX), "l"(reinterpret_cast<uint64_t>(&tmap_dy)), "r"(full_bar + 8 * stage), "r"(0),
+              "r"(p.win0 + t.q * p.PB), "r"(t.b * p.Rdy + p.ptop + t.g * p.RB)
               : "memory");
           if (++stage == CWG_STAGES) { stage = 0; phase ^= 1; }
         }
@@ -283,9 +325,8 @@ conv_window_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         if (elect_one_sync()) {
           const uint32_t sa = sbase + stage * CWG_STAGE_BYTES;
           const uint32_t sb = sa + 2 * CW_BOX;
-#pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            // contraction over the 128 positions of the row: 16 positions (16 x 128 B) per K step
+          for (int k = 0; k < ksteps; ++k) {
+            // contraction over the packed (row, position) pairs of the tile: 16 of them (16 x 128 B) per K step
             umma_bf16(tmem_base + blk * CW_C, umma_smem_desc_sw128(sa + k * 2048, CW_BOX, 1024),
                       umma_smem_desc_sw128(sb + k * 2048, CW_BOX, 1024), idesc, (first_tile && k == 0) ? 0u : 1u);
           }
@@ -329,22 +370,25 @@ conv_window_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
 }
 
 // ------------------------------------------------------------------ small helpers
-// dy fp32 [R, P, 32] -> bf16 [R, P + 2*pad, 32] with zero borders (the data gradient's and weight gradient's source)
-__global__ void conv_pad_cast_kernel(const float* __restrict__ dy, __nv_bfloat16* __restrict__ out, long R, int P, int pad) {
+// dy fp32 [B, To, P, 32] -> bf16 [B, Rdy, P + 2*pad, 32]: zero borders of `pad` positions, `ptop` zero rows above the To
+// rows of every batch item and zero rows below them up to Rdy (the data gradient's and weight gradient's source)
+__global__ void conv_pad_cast_kernel(const float* __restrict__ dy, __nv_bfloat16* __restrict__ out, int B, int To, int P, int pad,
+                                     int ptop, int Rdy) {
   const int Pp = P + 2 * pad;
-  const long n4 = R * Pp * (CW_C / 4);
+  const long n4 = (long)B * Rdy * Pp * (CW_C / 4);
   for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
     const int c4 = (int)(i % (CW_C / 4));
     const long rp = i / (CW_C / 4);
     const int pp = (int)(rp % Pp);
-    const long r = rp / Pp;
+    const long rr = rp / Pp;
+    const int b = (int)(rr / Rdy), r = (int)(rr - (long)b * Rdy) - ptop;
     const int pos = pp - pad;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (pos >= 0 && pos < P) v = __ldg(reinterpret_cast<const float4*>(dy + ((r * P + pos) * CW_C)) + c4);
-    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+    if (pos >= 0 && pos < P && r >= 0 && r < To) v = __ldg(reinterpret_cast<const float4*>(dy + ((((long)b * To + r) * P + pos) * CW_C)) + c4);
+    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b2 = __floats2bfloat162_rn(v.z, v.w);
     uint2 pk;
     pk.x = *reinterpret_cast<uint32_t*>(&a);
-    pk.y = *reinterpret_cast<uint32_t*>(&b);
+    pk.y = *reinterpret_cast<uint32_t*>(&b2);
     *reinterpret_cast<uint2*>(out + (rp * CW_C) + c4 * 4) = pk;
   }
 }
@@ -369,8 +413,9 @@ typedef CUresult (*PFN_encodeTiledW)(CUtensorMap*, CUtensorMapDataType, cuuint32
                                      const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                      CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-// window view of a channel-last bf16 tensor [R][P][32] with row pitch `pitch` elements: {64, P, R} / {64 B, pitch}
-static int make_tmap_window(CUtensorMap* out, const void* base, uint64_t P, uint64_t R, uint64_t pitch_elems) {
+// window view of a channel-last bf16 tensor [R][P][32] with row pitch `pitch` elements: {64, P, R} / {64 B, pitch}, box =
+// PB positions x RB rows
+static int make_tmap_window(CUtensorMap* out, const void* base, uint64_t P, uint64_t R, uint64_t pitch_elems, int PB, int RB) {
   static PFN_encodeTiledW enc = nullptr;
   if (!enc) {
     void* fp = nullptr;
@@ -383,7 +428,7 @@ static int make_tmap_window(CUtensorMap* out, const void* base, uint64_t P, uint
               "conv window operand must be 16-byte aligned with a 16-byte multiple row pitch");
   cuuint64_t dims[3] = {64, P, R};
   cuuint64_t strides[2] = {CW_C * 2, pitch_elems * 2};
-  cuuint32_t box[3] = {64, 128, 1};
+  cuuint32_t box[3] = {64, (cuuint32_t)PB, (cuuint32_t)RB};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -406,6 +451,50 @@ static void fill_common(WinParams& p, int KT, int KF, int st) {
   p.KT = KT; p.st = st; p.nfull = KF / 2; p.half = KF & 1; p.kstride = KF * CW_C;
 }
 
+// positions per box, rows per box and position passes for rows of Pout positions: the split that fills most of the 128 MMA
+// rows of a tile.  max_rows bounds RB (1: no packing).
+static void choose_pack(int Pout, int max_rows, int* PB, int* RB, int* np) {
+  double best = -1.0;
+  for (int n = 1; n <= 16; ++n) {
+    const int pb = (Pout + n - 1) / n;
+    if (pb > 128) continue;
+    int rb = 128 / pb;
+    if (rb > max_rows) rb = max_rows;
+    const double eff = (double)Pout * rb / (128.0 * n);
+    if (eff > best + 1e-9) { best = eff; *PB = pb; *RB = rb; *np = n; }
+  }
+}
+static constexpr int CW_MAX_RB = 16;
+struct Pack {
+  int PBf, RBf, npf;      // forward / weight gradient (rows of Fo positions, source rows st apart)
+  int PBd, RBd, npd;      // data gradient (rows of Fi positions)
+  int ptop, Rdy;          // padded dy: zero rows above an item's To rows, rows per item
+};
+static Pack pack_for(int Ti, int Fi, int KT, int KF, int st) {
+  Pack k;
+  const int To = (Ti - KT) / st + 1, Fo = Fi - KF + 1;
+  choose_pack(Fo, st <= CW_MAXST ? CW_MAX_RB : 1, &k.PBf, &k.RBf, &k.npf);
+  choose_pack(Fi, CW_MAX_RB, &k.PBd, &k.RBd, &k.npd);
+  k.ptop = (KT - 1 + st - 1) / st;
+  k.Rdy = k.ptop + To + k.ptop + 1 + (k.RBf > k.RBd ? k.RBf : k.RBd);
+  return k;
+}
+// the source maps of the forward / weight gradient: one per residue of the row modulo st (packed rows), or the plain one
+static int make_src_maps(WinMaps* m, int* nmaps, const void* a, int Fi, uint64_t rows, int st, int PB, int RB) {
+  const uint64_t pitch = (uint64_t)Fi * CW_C;
+  if (RB == 1) {
+    *nmaps = 1;
+    return make_tmap_window(&m->m[0], a, Fi, rows, pitch, PB, 1);
+  }
+  *nmaps = st;
+  for (int r = 0; r < st; ++r) {
+    if ((uint64_t)r >= rows) { m->m[r] = m->m[0]; continue; }
+    int rc = make_tmap_window(&m->m[r], static_cast<const __nv_bfloat16*>(a) + (size_t)r * pitch, Fi, (rows - r + st - 1) / st, pitch * st, PB, RB);
+    if (rc) return rc;
+  }
+  return DS2_OK;
+}
+
 }  // namespace ds2
 
 using namespace ds2;
@@ -423,12 +512,22 @@ extern "C" int ds2_conv_window_weights(const float* w, void* wt, void* wd, int K
   return DS2_OK;
 }
 
-extern "C" int ds2_conv_window_pad_cast(const float* dy, void* out, long R, int P, int pad, void* stream) {
-  DS2_REQUIRE(dy && out && R > 0 && P > 0 && pad >= 0, DS2_ERR_BAD_ARG, "ds2_conv_window_pad_cast: bad argument");
-  long n4 = R * (P + 2 * pad) * (CW_C / 4);
+extern "C" int ds2_conv_window_dy_layout(int Ti, int Fi, int KT, int KF, int st, int* ptop, int* rows_per_item) {
+  DS2_REQUIRE(Ti >= KT && Fi >= KF && KT > 0 && KF > 0 && st > 0 && ptop && rows_per_item, DS2_ERR_BAD_ARG, "ds2_conv_window_dy_layout: bad argument");
+  const Pack k = pack_for(Ti, Fi, KT, KF, st);
+  *ptop = k.ptop;
+  *rows_per_item = k.Rdy;
+  return DS2_OK;
+}
+
+extern "C" int ds2_conv_window_pad_cast(const float* dy, void* out, int B, int Ti, int Fi, int KT, int KF, int st, void* stream) {
+  DS2_REQUIRE(dy && out && B > 0 && Ti >= KT && Fi >= KF && KT > 0 && KF > 0 && st > 0, DS2_ERR_BAD_ARG, "ds2_conv_window_pad_cast: bad argument");
+  const Pack k = pack_for(Ti, Fi, KT, KF, st);
+  const int To = (Ti - KT) / st + 1, Fo = Fi - KF + 1, pad = KF - 1;
+  long n4 = (long)B * k.Rdy * (Fo + 2 * pad) * (CW_C / 4);
   long grid = (n4 + 255) / 256;
   if (grid > (long)num_sms() * 16) grid = (long)num_sms() * 16;
-  conv_pad_cast_kernel<<<(int)grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, static_cast<__nv_bfloat16*>(out), R, P, pad);
+  conv_pad_cast_kernel<<<(int)grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, static_cast<__nv_bfloat16*>(out), B, To, Fo, pad, k.ptop, k.Rdy);
   DS2_LAUNCH_CHECK("conv_pad_cast_kernel");
   count_launch();
   return DS2_OK;
@@ -450,14 +549,17 @@ extern "C" int ds2_conv_window_fwd(const void* a, const void* wt, const float* b
   if (rc) return rc;
   if ((rc = window_attr())) return rc;
   const int To = (Ti - KT) / st + 1, Fo = Fi - KF + 1;
-  CUtensorMap ts, tw;
-  if ((rc = make_tmap_window(&ts, a, Fi, (uint64_t)B * Ti, (uint64_t)Fi * CW_C))) return rc;
-  if ((rc = make_tmap_2d_bf16(&tw, wt, (uint64_t)KT * KF * CW_C, CW_C, (uint64_t)KT * KF * CW_C, 64, CW_C))) return rc;
+  const Pack k = pack_for(Ti, Fi, KT, KF, st);
+  WinMaps ms = {};
+  CUtensorMap tw;
   WinParams p = {};
+  if ((rc = make_src_maps(&ms, &p.nmaps, a, Fi, (uint64_t)B * Ti, st, k.PBf, k.RBf))) return rc;
+  if ((rc = make_tmap_2d_bf16(&tw, wt, (uint64_t)KT * KF * CW_C, CW_C, (uint64_t)KT * KF * CW_C, 64, CW_C))) return rc;
   fill_common(p, KT, KF, st);
-  p.out = y; p.bias = bias; p.n_tiles = B * To; p.Rout = To; p.Rsrc = Ti; p.Pout = Fo; p.win0 = 0; p.dgrad = 0;
+  p.PB = k.PBf; p.RB = k.RBf; p.np = k.npf; p.G = (To + k.RBf - 1) / k.RBf; p.ncls = 1;
+  p.out = y; p.bias = bias; p.n_tiles = B * p.G * p.np; p.Rout = To; p.Rsrc = Ti; p.Pout = Fo; p.win0 = 0; p.dgrad = 0;
   const int grid = p.n_tiles < num_sms() ? p.n_tiles : num_sms();
-  conv_window_kernel<<<grid, CW_THREADS, CW_SMEM, static_cast<cudaStream_t>(stream)>>>(ts, tw, p);
+  conv_window_kernel<<<grid, CW_THREADS, CW_SMEM, static_cast<cudaStream_t>(stream)>>>(ms, tw, p);
   DS2_LAUNCH_CHECK("conv_window_kernel<fwd>");
   count_launch();
   return DS2_OK;
@@ -469,15 +571,20 @@ extern "C" int ds2_conv_window_dgrad(const void* dyp, const void* wd, float* da,
   int rc = window_shape_ok("ds2_conv_window_dgrad", B, Ti, Fi, CW_C, CW_C, KT, KF, st, 1);
   if (rc) return rc;
   if ((rc = window_attr())) return rc;
-  const int To = (Ti - KT) / st + 1, Fo = Fi - KF + 1, Pp = Fo + 2 * (KF - 1);
-  CUtensorMap ts, tw;
-  if ((rc = make_tmap_window(&ts, dyp, Pp, (uint64_t)B * To, (uint64_t)Pp * CW_C))) return rc;
+  const int Fo = Fi - KF + 1, Pp = Fo + 2 * (KF - 1);
+  const Pack k = pack_for(Ti, Fi, KT, KF, st);
+  WinMaps ms = {};
+  CUtensorMap tw;
+  if ((rc = make_tmap_window(&ms.m[0], dyp, Pp, (uint64_t)B * k.Rdy, (uint64_t)Pp * CW_C, k.PBd, k.RBd))) return rc;
+  for (int i = 1; i < CW_MAXST; ++i) ms.m[i] = ms.m[0];
   if ((rc = make_tmap_2d_bf16(&tw, wd, (uint64_t)KT * KF * CW_C, CW_C, (uint64_t)KT * KF * CW_C, 64, CW_C))) return rc;
   WinParams p = {};
   fill_common(p, KT, KF, st);
-  p.out = da; p.bias = nullptr; p.n_tiles = B * Ti; p.Rout = Ti; p.Rsrc = To; p.Pout = Fi; p.win0 = 0; p.dgrad = 1;
+  const int rows_per_class = (Ti + st - 1) / st;
+  p.PB = k.PBd; p.RB = k.RBd; p.np = k.npd; p.G = (rows_per_class + k.RBd - 1) / k.RBd; p.ncls = st; p.nmaps = 1; p.ptop = k.ptop;
+  p.out = da; p.bias = nullptr; p.n_tiles = B * st * p.G * p.np; p.Rout = Ti; p.Rsrc = k.Rdy; p.Pout = Fi; p.win0 = 0; p.dgrad = 1;
   const int grid = p.n_tiles < num_sms() ? p.n_tiles : num_sms();
-  conv_window_kernel<<<grid, CW_THREADS, CW_SMEM, static_cast<cudaStream_t>(stream)>>>(ts, tw, p);
+  conv_window_kernel<<<grid, CW_THREADS, CW_SMEM, static_cast<cudaStream_t>(stream)>>>(ms, tw, p);
   DS2_LAUNCH_CHECK("conv_window_kernel<dgrad>");
   count_launch();
   return DS2_OK;
@@ -490,16 +597,19 @@ extern "C" int ds2_conv_window_wgrad(const void* a, const void* dyp, float* dw, 
   if (rc) return rc;
   if ((rc = window_attr())) return rc;
   const int To = (Ti - KT) / st + 1, Fo = Fi - KF + 1, Pp = Fo + 2 * (KF - 1);
+  const Pack k = pack_for(Ti, Fi, KT, KF, st);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   DS2_CUDA(cudaMemsetAsync(dw, 0, (size_t)KT * KF * CW_C * CW_C * sizeof(float), s));
-  CUtensorMap ta, td;
-  if ((rc = make_tmap_window(&ta, a, Fi, (uint64_t)B * Ti, (uint64_t)Fi * CW_C))) return rc;
-  if ((rc = make_tmap_window(&td, dyp, Pp, (uint64_t)B * To, (uint64_t)Pp * CW_C))) return rc;
+  WinMaps ms = {};
+  CUtensorMap td;
   WinParams p = {};
+  if ((rc = make_src_maps(&ms, &p.nmaps, a, Fi, (uint64_t)B * Ti, st, k.PBf, k.RBf))) return rc;
+  if ((rc = make_tmap_window(&td, dyp, Pp, (uint64_t)B * k.Rdy, (uint64_t)Pp * CW_C, k.PBf, k.RBf))) return rc;
   fill_common(p, KT, KF, st);
-  p.out = dw; p.bias = nullptr; p.n_tiles = B * To; p.Rout = To; p.Rsrc = Ti; p.Pout = Fo; p.win0 = KF - 1; p.dgrad = 0;
+  p.PB = k.PBf; p.RB = k.RBf; p.np = k.npf; p.G = (To + k.RBf - 1) / k.RBf; p.ncls = 1; p.ptop = k.ptop; p.Rdy = k.Rdy;
+  p.out = dw; p.bias = nullptr; p.n_tiles = B * p.G * p.np; p.Rout = To; p.Rsrc = Ti; p.Pout = Fo; p.win0 = KF - 1; p.dgrad = 0;
   const int grid = p.n_tiles < num_sms() ? p.n_tiles : num_sms();
-  conv_window_wgrad_kernel<<<grid, CW_THREADS, CWG_SMEM, s>>>(ta, td, p);
+  conv_window_wgrad_kernel<<<grid, CW_THREADS, CWG_SMEM, s>>>(ms, td, p);
   DS2_LAUNCH_CHECK("conv_window_wgrad_kernel");
   count_launch();
   return DS2_OK;

@@ -364,6 +364,16 @@ def _slack_bf16(shape, device):
     return flat[:n].view(shape)
 
 
+def conv_window_padded_dy(dy, B, Ti, Fi, KT, KF, st):
+    """dL/dy fp32 [B,To,Fo,32] -> the zero-bordered bf16 copy ds2_conv_window_dgrad / _wgrad read (layout: include/ds2_b200.h)."""
+    import ctypes
+    ptop, rdy = ctypes.c_int(0), ctypes.c_int(0)
+    check(lib.ds2_conv_window_dy_layout(Ti, Fi, KT, KF, st, ctypes.byref(ptop), ctypes.byref(rdy)), "ds2_conv_window_dy_layout")
+    dyp = _slack_bf16((B, rdy.value, Fi - KF + 1 + 2 * (KF - 1), 32), dy.device)
+    check(lib.ds2_conv_window_pad_cast(_p(dy), _p(dyp), B, Ti, Fi, KT, KF, st, _stream()), "ds2_conv_window_pad_cast")
+    return dyp
+
+
 class _ConvWindowFn(torch.autograd.Function):
     """Same contract as _ConvGemmFn, without a patch matrix: a = f(x) is written once in bf16 and the tensor cores read
     overlapping filter windows of it through a strided TMA view (ds2_conv_window_*; 32 channels in and out, sf = 1)."""
@@ -404,9 +414,7 @@ class _ConvWindowFn(torch.autograd.Function):
         eps, cap, has_bn, has_bias, wshape = ctx.misc
         dev = x.device
         dy = cast(dy.contiguous(), torch.float32)
-        pad = KF - 1
-        dyp = _slack_bf16((B * To, Fo + 2 * pad, Co), dev)
-        check(lib.ds2_conv_window_pad_cast(_p(dy), _p(dyp), B * To, Fo, pad, _stream()), "ds2_conv_window_pad_cast")
+        dyp = conv_window_padded_dy(dy, B, Ti, Fi, KT, KF, st)
         dw = torch.empty(wshape, dtype=torch.float32, device=dev)
         check(lib.ds2_conv_window_wgrad(_p(a), _p(dyp), _p(dw), B, Ti, Fi, KT, KF, st, _stream()), "ds2_conv_window_wgrad")
         db = colsum(dy.view(B * To * Fo, Co), B * To * Fo, Co, Co) if has_bias else None

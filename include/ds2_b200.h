@@ -182,13 +182,17 @@ int ds2_col2im(const void* dP, long ldp, float* dx, int B, int Ti, int Fi, int C
  *                             must extend 64 bytes past its last element (the last window reads them, unused);
  *   wt   bf16 [32][KT*KF*32] - filters as wt[co][(kt,kf,ci)],  wd bf16 [32][KT*KF*32] - wd[ci][(kt,KF-1-kf,co)],
  *                             both made from the HWIO fp32 filter by ds2_conv_window_weights;
- *   dyp  bf16 [B*To, Fo+2*(KF-1), 32] - dL/dy with KF-1 zero positions on both sides of every row
- *                             (ds2_conv_window_pad_cast), 64 bytes of slack after the last element as for `a`;
+ *   dyp  bf16 [B, Rdy, Fo+2*(KF-1), 32] - dL/dy with KF-1 zero positions on both sides of every row, `ptop` zero rows
+ *                             above the To rows of every batch item and zero rows below them up to Rdy rows per item
+ *                             (both from ds2_conv_window_dy_layout; written by ds2_conv_window_pad_cast): the kernels
+ *                             pack several rows into one 128-row MMA tile and read the rows a filter tap reaches
+ *                             outside [0,To) as zeros; 64 bytes of slack after the last element as for `a`;
  *   y    f32 [B,To,Fo,32], da f32 [B,Ti,Fi,32] (every element written), dw f32 HWIO [KT,KF,32,32].
  * ds2_conv_window_supported tells whether a shape is taken. */
 int ds2_conv_window_supported(int Ci, int Co, int Fi, int KT, int KF, int sf);
 int ds2_conv_window_weights(const float* w, void* wt, void* wd, int KT, int KF, void* stream);
-int ds2_conv_window_pad_cast(const float* dy, void* dyp, long R, int P, int pad, void* stream);
+int ds2_conv_window_dy_layout(int Ti, int Fi, int KT, int KF, int st, int* ptop, int* rows_per_item);
+int ds2_conv_window_pad_cast(const float* dy, void* dyp, int B, int Ti, int Fi, int KT, int KF, int st, void* stream);
 int ds2_conv_window_fwd(const void* a, const void* wt, const float* bias, float* y, int B, int Ti, int Fi, int KT, int KF, int st,
                         void* stream);
 int ds2_conv_window_dgrad(const void* dyp, const void* wd, float* da, int B, int Ti, int Fi, int KT, int KF, int st, void* stream);

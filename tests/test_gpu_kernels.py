@@ -226,9 +226,7 @@ def test_conv_window_kernels_vs_fp64(B, Ti, Fi, KT, KF, st):
     check(lib.ds2_conv_window_weights(p(w), p(wt), p(wd), KT, KF, st_()), "weights")
     y = torch.full((B, To, Fo, C), float("nan"), dtype=torch.float32, device="cuda")
     check(lib.ds2_conv_window_fwd(p(a), p(wt), p(bias), p(y), B, Ti, Fi, KT, KF, st, st_()), "fwd")
-    dyp = ops._slack_bf16((B * To, Fo + 2 * (KF - 1), C), "cuda")
-    dyp.fill_(float("nan"))
-    check(lib.ds2_conv_window_pad_cast(p(dy), p(dyp), B * To, Fo, KF - 1, st_()), "pad")
+    dyp = ops.conv_window_padded_dy(dy, B, Ti, Fi, KT, KF, st)
     dw = torch.full((KT, KF, C, C), float("nan"), dtype=torch.float32, device="cuda")
     check(lib.ds2_conv_window_wgrad(p(a), p(dyp), p(dw), B, Ti, Fi, KT, KF, st, st_()), "wgrad")
     da = torch.full((B, Ti, Fi, C), float("nan"), dtype=torch.float32, device="cuda")

@@ -24,8 +24,7 @@ p, s = ops._p, ops._stream
 check(lib.ds2_conv_window_weights(p(w), p(wt), p(wd), KT, KF, s()), "w")
 y = torch.empty((B, To, Fo, C), device=dev)
 dy = torch.randn(B, To, Fo, C, device=dev)
-dyp = ops._slack_bf16((B * To, Fo + 2 * (KF - 1), C), dev)
-check(lib.ds2_conv_window_pad_cast(p(dy), p(dyp), B * To, Fo, KF - 1, s()), "pad")
+dyp = ops.conv_window_padded_dy(dy, B, Ti, Fi, KT, KF, st)
 dw = torch.empty((KT, KF, C, C), device=dev)
 da = torch.empty((B, Ti, Fi, C), device=dev)
 
