@@ -34,12 +34,17 @@ static constexpr int CW_THREADS = 256;
 static constexpr int CW_C = 32;                  // channels in and out
 static constexpr int CW_BOX = 128 * 128;         // one window box: 128 positions x 64 elements bf16
 static constexpr int CW_WBOX = 32 * 128;         // weight tile: 32 rows x 64 elements
-static constexpr int CW_STAGES = 8;
-static constexpr int CW_STAGE_BYTES = CW_BOX + CW_WBOX;
-static constexpr int CW_SMEM = CW_STAGES * CW_STAGE_BYTES + 1024 + 256;
-static constexpr int CWG_STAGES = 4;             // wgrad: two window boxes + one dy box per stage
-static constexpr int CWG_STAGE_BYTES = 3 * CW_BOX;
-static constexpr int CWG_SMEM = CWG_STAGES * CWG_STAGE_BYTES + 1024 + 256;
+static constexpr int CW_STAGES = 6;              // window boxes in flight; the filters stay resident behind them
+static constexpr int CW_STAGE_BYTES = CW_BOX;
+static constexpr int CW_MAX_WBOXES = 32;         // KT x chunks per filter row
+static constexpr int CW_W_OFF = CW_STAGES * CW_STAGE_BYTES;
+static constexpr int CW_BUF_BYTES = CW_W_OFF + CW_MAX_WBOXES * CW_WBOX;
+static constexpr int CW_SMEM = CW_BUF_BYTES + 1024 + 256;
+static constexpr int CWG_STAGES = 5;             // wgrad: two window boxes per stage; the tile's dy box in one of two slots
+static constexpr int CWG_STAGE_BYTES = 2 * CW_BOX;
+static constexpr int CWG_DY_OFF = CWG_STAGES * CWG_STAGE_BYTES;
+static constexpr int CWG_BUF_BYTES = CWG_DY_OFF + 2 * CW_BOX;
+static constexpr int CWG_SMEM = CWG_BUF_BYTES + 1024 + 256;
 
 static constexpr int CW_MAXST = 4;               // row packing needs one source map per residue modulo the time stride
 struct WinMaps {
@@ -96,10 +101,10 @@ __global__ void __launch_bounds__(CW_THREADS, 1)
 conv_window_kernel(const __grid_constant__ WinMaps maps, const __grid_constant__ CUtensorMap tmap_w, WinParams p) {
   extern __shared__ __align__(1024) uint8_t cw_smem_raw[];
   const uint32_t sbase = (smem_u32(cw_smem_raw) + 1023u) & ~1023u;
-  const uint32_t bars = sbase + CW_STAGES * CW_STAGE_BYTES;
+  const uint32_t bars = sbase + CW_BUF_BYTES;
   const uint32_t full_bar = bars, empty_bar = bars + 8 * CW_STAGES, tfull_bar = bars + 16 * CW_STAGES,
-                 tempty_bar = tfull_bar + 16;
-  const uint32_t slot_addr = tempty_bar + 16;
+                 tempty_bar = tfull_bar + 16, w_bar = tempty_bar + 16;
+  const uint32_t slot_addr = w_bar + 8;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(cw_smem_raw + (slot_addr - smem_u32(cw_smem_raw)));
   const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const int nch = p.nfull + p.half;
@@ -118,6 +123,7 @@ conv_window_kernel(const __grid_constant__ WinMaps maps, const __grid_constant__
       asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(tfull_bar + 8 * i), "r"(1));
       asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(tempty_bar + 8 * i), "r"(4));
     }
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(w_bar), "r"(1));
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, 64);
@@ -129,6 +135,16 @@ conv_window_kernel(const __grid_constant__ WinMaps maps, const __grid_constant__
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one_sync()) {
+      // all filter boxes once: [32 filters x 64 window elements] per (filter row, chunk)
+      mbar_arrive_expect_tx(w_bar, (uint32_t)(p.KT * nch) * CW_WBOX);
+      for (int i = 0; i < p.KT * nch; ++i) {
+        const int kt = i / nch, c = i - kt * nch;
+        asm volatile(
+            "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+            ::"r"(sbase + CW_W_OFF + i * CW_WBOX), "l"(reinterpret_cast<uint64_t>(&tmap_w)), "r"(w_bar),
+            "r"(kt * p.kstride + c * 64), "r"(0)
+            : "memory");
+      }
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
@@ -139,16 +155,11 @@ conv_window_kernel(const __grid_constant__ WinMaps maps, const __grid_constant__
           for (int c = 0; c < nch; ++c) {
             mbar_wait(empty_bar + 8 * stage, phase ^ 1, 100 + stage);
             const uint32_t sa = sbase + stage * CW_STAGE_BYTES;
-            mbar_arrive_expect_tx(full_bar + 8 * stage, box_bytes + CW_WBOX);
+            mbar_arrive_expect_tx(full_bar + 8 * stage, box_bytes);
             asm volatile(
                 "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
                 ::"r"(sa), "l"(reinterpret_cast<uint64_t>(&maps.m[mi])), "r"(full_bar + 8 * stage), "r"(0),
                 "r"(p.win0 + t.q * p.PB + 2 * c), "r"(src_row)
-                : "memory");
-            asm volatile(
-                "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-                ::"r"(sa + CW_BOX), "l"(reinterpret_cast<uint64_t>(&tmap_w)), "r"(full_bar + 8 * stage),
-                "r"(kt * p.kstride + c * 64), "r"(0)
                 : "memory");
             if (++stage == CW_STAGES) { stage = 0; phase ^= 1; }
           }
@@ -162,6 +173,7 @@ conv_window_kernel(const __grid_constant__ WinMaps maps, const __grid_constant__
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
+    mbar_wait(w_bar, 0, 250);          // the filters are resident
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
       const TileId t = tile_decode(p, tile);
       mbar_wait(tempty_bar + 8 * acc, acc_phase ^ 1, 200 + acc);
@@ -176,7 +188,7 @@ conv_window_kernel(const __grid_constant__ WinMaps maps, const __grid_constant__
           tc_fence_after();
           if (elect_one_sync()) {
             const uint32_t sa = sbase + stage * CW_STAGE_BYTES;
-            const uint32_t sb = sa + CW_BOX;
+            const uint32_t sb = sbase + CW_W_OFF + (kt * nch + c) * CW_WBOX;
             const int ksteps = c < p.nfull ? 4 : 2;
             for (int k = 0; k < ksteps; ++k) {
               umma_bf16(d_tmem, umma_smem_desc_sw128(sa + k * 32, 16, 1024), umma_smem_desc_sw128(sb + k * 32, 16, 1024), idesc,
@@ -249,9 +261,10 @@ __global__ void __launch_bounds__(CW_THREADS, 1)
 conv_window_wgrad_kernel(const __grid_constant__ WinMaps maps, const __grid_constant__ CUtensorMap tmap_dy, WinParams p) {
   extern __shared__ __align__(1024) uint8_t cwg_smem_raw[];
   const uint32_t sbase = (smem_u32(cwg_smem_raw) + 1023u) & ~1023u;
-  const uint32_t bars = sbase + CWG_STAGES * CWG_STAGE_BYTES;
+  const uint32_t bars = sbase + CWG_BUF_BYTES;
   const uint32_t full_bar = bars, empty_bar = bars + 8 * CWG_STAGES, done_bar = bars + 16 * CWG_STAGES;
-  const uint32_t slot_addr = done_bar + 8;
+  const uint32_t dyfull_bar = done_bar + 8, dyempty_bar = done_bar + 24;
+  const uint32_t slot_addr = done_bar + 40;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(cwg_smem_raw + (slot_addr - smem_u32(cwg_smem_raw)));
   const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const int nch = p.nfull + p.half;
@@ -265,7 +278,7 @@ conv_window_wgrad_kernel(const __grid_constant__ WinMaps maps, const __grid_cons
     tma_prefetch_desc(&tmap_dy);
   }
   // rows of a stage buffer that no box writes are part of the contraction: zero once
-  for (uint32_t o = threadIdx.x * 16u; o < (uint32_t)(CWG_STAGES * CWG_STAGE_BYTES); o += CW_THREADS * 16u)
+  for (uint32_t o = threadIdx.x * 16u; o < (uint32_t)CWG_BUF_BYTES; o += CW_THREADS * 16u)
     sts_v4(sbase + o, make_uint4(0u, 0u, 0u, 0u));
   fence_proxy_async();
   if (warp == 1 && lane == 0) {
@@ -274,6 +287,10 @@ conv_window_wgrad_kernel(const __grid_constant__ WinMaps maps, const __grid_cons
       asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(empty_bar + 8 * i), "r"(1));
     }
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(done_bar), "r"(1));
+    for (int i = 0; i < 2; ++i) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dyfull_bar + 8 * i), "r"(1));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dyempty_bar + 8 * i), "r"(1));
+    }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, 512);
@@ -287,13 +304,24 @@ conv_window_wgrad_kernel(const __grid_constant__ WinMaps maps, const __grid_cons
     if (elect_one_sync()) {
       int stage = 0;
       uint32_t phase = 0;
+      int dslot = 0;
+      uint32_t dphase = 0;
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
         const TileId t = tile_decode(p, tile);
+        // the tile's dy rows: loaded once, the B operand of all its blocks
+        mbar_wait(dyempty_bar + 8 * dslot, dphase ^ 1, 150 + dslot);
+        mbar_arrive_expect_tx(dyfull_bar + 8 * dslot, box_bytes);
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+            ::"r"(sbase + CWG_DY_OFF + dslot * CW_BOX), "l"(reinterpret_cast<uint64_t>(&tmap_dy)), "r"(dyfull_bar + 8 * dslot), "r"(0),
+            "r"(p.win0 + t.q * p.PB), "r"(t.b * p.Rdy + p.ptop + t.g * p.RB)
+            : "memory");
+        if (++dslot == 2) { dslot = 0; dphase ^= 1; }
         for (int blk = 0; blk < nblocks; ++blk) {
           mbar_wait(empty_bar + 8 * stage, phase ^ 1, 100 + stage);
           const uint32_t sa = sbase + stage * CWG_STAGE_BYTES;
           const int ng = min(2, ngroups - 2 * blk);
-          mbar_arrive_expect_tx(full_bar + 8 * stage, (ng + 1) * box_bytes);
+          mbar_arrive_expect_tx(full_bar + 8 * stage, ng * box_bytes);
           for (int g = 0; g < ng; ++g) {
             const int gi = 2 * blk + g, kt = gi / nch, c = gi - kt * nch;
             int mi, src_row;
@@ -304,11 +332,6 @@ conv_window_wgrad_kernel(const __grid_constant__ WinMaps maps, const __grid_cons
                 "r"(t.q * p.PB + 2 * c), "r"(src_row)
                 : "memory");
           }
-          asm volatile(
-              "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-              ::"r"(sa + 2 * CW_BOX), "l"(reinterpret_cast<uint64_t>(&tmap_dy)), "r"(full_bar + 8 * stage), "r"(0),
-              "r"(p.win0 + t.q * p.PB), "r"(t.b * p.Rdy + p.ptop + t.g * p.RB)
-              : "memory");
           if (++stage == CWG_STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -318,13 +341,16 @@ conv_window_wgrad_kernel(const __grid_constant__ WinMaps maps, const __grid_cons
     int stage = 0;
     uint32_t phase = 0;
     bool first_tile = true;
+    int dslot = 0;
+    uint32_t dphase = 0;
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      mbar_wait(dyfull_bar + 8 * dslot, dphase, 350 + dslot);
+      const uint32_t sb = sbase + CWG_DY_OFF + dslot * CW_BOX;
       for (int blk = 0; blk < nblocks; ++blk) {
         mbar_wait(full_bar + 8 * stage, phase, 300 + stage);
         tc_fence_after();
         if (elect_one_sync()) {
           const uint32_t sa = sbase + stage * CWG_STAGE_BYTES;
-          const uint32_t sb = sa + 2 * CW_BOX;
           for (int k = 0; k < ksteps; ++k) {
             // contraction over the packed (row, position) pairs of the tile: 16 of them (16 x 128 B) per K step
             umma_bf16(tmem_base + blk * CW_C, umma_smem_desc_sw128(sa + k * 2048, CW_BOX, 1024),
@@ -336,6 +362,9 @@ conv_window_wgrad_kernel(const __grid_constant__ WinMaps maps, const __grid_cons
         if (++stage == CWG_STAGES) { stage = 0; phase ^= 1; }
       }
       first_tile = false;
+      if (elect_one_sync()) umma_commit(dyempty_bar + 8 * dslot);     // the tile's MMAs have read its dy slot
+      __syncwarp();
+      if (++dslot == 2) { dslot = 0; dphase ^= 1; }
     }
     if (elect_one_sync()) umma_commit(done_bar);
     __syncwarp();
