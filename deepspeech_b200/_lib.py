@@ -60,6 +60,10 @@ _SIGS = {
     "ds2_conv2d_fwd": (I, [P, I, P, P, P, I, I, I, I, I, I, I, I, I, P]),
     "ds2_conv2d_dgrad": (I, [P, P, P, I, I, I, I, I, I, I, I, I, P]),
     "ds2_conv2d_wgrad": (I, [P, I, P, P, P, I, I, I, I, I, I, I, I, I, P]),
+    "ds2_conv1_fused_supported": (I, [I, I, I, I, I, I, I, I]),
+    "ds2_conv1_fused_fwd": (I, [P, P, P, P, P, I, I, I, I, I, I, I, P]),
+    "ds2_conv1_fused_wgrad": (I, [P, P, P, P, I, I, I, I, I, I, I, P]),
+    "ds2_bn_finalize": (I, [P, D, I, F, P, P, P]),
     "ds2_conv_window_supported": (I, [I, I, I, I, I, I]),
     "ds2_conv_window_weights": (I, [P, P, P, I, I, P]),
     "ds2_conv_window_dy_layout": (I, [I, I, I, I, I, P, P]),

@@ -722,6 +722,15 @@ extern "C" int ds2_bn_stats(const float* x, long R, int C, float eps, double* su
   return DS2_OK;
 }
 
+// mean / rstd from per-channel sums a producer kernel accumulated (sums[c] = sum x, sums[C + c] = sum x^2 over `count` values)
+extern "C" int ds2_bn_finalize(const double* sums, double count, int C, float eps, float* mean, float* rstd, void* stream) {
+  DS2_REQUIRE(sums && mean && rstd && count > 0 && C > 0 && C <= 256, DS2_ERR_BAD_ARG, "ds2_bn_finalize: bad argument");
+  bn_finalize_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(sums, count, eps, C, mean, rstd);
+  DS2_LAUNCH_CHECK("bn_finalize_kernel");
+  count_launch();
+  return DS2_OK;
+}
+
 extern "C" int ds2_bn_clip_fwd(const float* x, int B, int T, int F, int C, const float* mean, const float* rstd,
                                const float* gamma, const float* beta, float cap, int clip, void* out, int out_dtype, long sb,
                                long st, long sf, long sc, void* stream) {

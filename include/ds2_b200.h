@@ -175,6 +175,19 @@ int ds2_im2col(const float* x, const float* mean, const float* rstd, const float
 int ds2_col2im(const void* dP, long ldp, float* dx, int B, int Ti, int Fi, int Ci, int KT, int KF, int st, int sf,
                void* stream);
 
+/* Fused implicit-GEMM convolution of a one-channel input into 32 feature maps (the reference's conv1: filter
+ * [20,5,1,32], strides (2,2), src/deepSpeech_NCHW.py:110-119) - no patch matrix: the CTA builds the patch rows of a
+ * 128-position tile in shared memory as the tcgen05 A operand (deepspeech_b200/csrc/ds2_conv1_fused.cu).
+ *   x f32 [B,Ti,Fi], w f32 HWIO [KT,KF,1,32], bias f32 [32] or NULL, y f32 [B,To,Fo,32];
+ *   sums (optional) f64 [64]: per-channel sum and sum of squares of y from the epilogue, for ds2_bn_finalize;
+ *   wgrad: dy f32 [B,To,Fo,32] -> dw f32 HWIO (every element written), db f32 [32] (optional) = column sums of dy.
+ * Operands are rounded to bf16, accumulation is fp32. */
+int ds2_conv1_fused_supported(int Ci, int Co, int Ti, int Fi, int KT, int KF, int st, int sf);
+int ds2_conv1_fused_fwd(const float* x, const float* w, const float* bias, float* y, double* sums, int B, int Ti, int Fi, int KT, int KF,
+                        int st, int sf, void* stream);
+int ds2_conv1_fused_wgrad(const float* x, const float* dy, float* dw, float* db, int B, int Ti, int Fi, int KT, int KF, int st, int sf,
+                          void* stream);
+
 /* Implicit-GEMM form of the same convolution for 32-channel layers with unit frequency stride (the reference's
  * conv2: filter [10,5,32,32], strides (2,1)): no patch matrix, the tensor cores read overlapping windows of the
  * channel-last activation through a strided TMA view (deepspeech_b200/csrc/ds2_conv_window.cu).
@@ -205,6 +218,9 @@ int ds2_conv_window_wgrad(const void* a, const void* dyp, float* dw, int B, int 
  * written straight into the RNN layout [T,B,C*F] (src/deepSpeech_NCHW.py:166-168) or [T,B,F*C]
  * (src/deepSpeech.py:162-164). */
 int ds2_bn_stats(const float* x, long R, int C, float eps, double* sums_scratch, float* mean, float* rstd, void* stream);
+/* mean / rstd from per-channel sums a producer kernel accumulated in its epilogue (sums[c] = sum of x, sums[C + c] = sum
+ * of x^2 over `count` values per channel): what ds2_bn_stats computes, without its pass over x. */
+int ds2_bn_finalize(const double* sums, double count, int C, float eps, float* mean, float* rstd, void* stream);
 int ds2_bn_clip_fwd(const float* x, int B, int T, int F, int C, const float* mean, const float* rstd, const float* gamma,
                     const float* beta, float cap, int clip, void* out, int out_dtype, long sb, long st, long sf, long sc,
                     void* stream);

@@ -241,6 +241,47 @@ def test_conv_window_kernels_vs_fp64(B, Ti, Fi, KT, KF, st):
     assert relerr(da.cpu().permute(0, 3, 1, 2).numpy(), xr.grad.numpy()) < 1e-4
 
 
+@pytest.mark.parametrize("B,Ti,Fi,KT,KF,st,sf", [(2, 60, 161, 20, 5, 2, 2), (1, 25, 40, 5, 3, 2, 1), (3, 23, 17, 4, 8, 1, 2), (2, 300, 161, 20, 5, 2, 2),
+                                                 (1, 9, 9, 9, 1, 3, 3), (2, 41, 12, 11, 2, 2, 1)])
+def test_conv1_fused_vs_fp64(B, Ti, Fi, KT, KF, st, sf):
+    """Fused one-channel convolution (patch rows built in shared memory, BN sums from the epilogue, weight + bias gradient)
+    against an fp64 convolution of the SAME bf16-rounded operands: only fp32 accumulation order differs."""
+    ops = _ops()
+    from deepspeech_b200._lib import check, lib
+    C = 32
+    assert lib.ds2_conv1_fused_supported(1, C, Ti, Fi, KT, KF, st, sf) == 1
+    rng = np.random.default_rng(Ti * 7 + KF)
+    To, Fo = (Ti - KT) // st + 1, (Fi - KF) // sf + 1
+    bf = lambda t: t.to(torch.bfloat16).float()
+    x = bf(torch.tensor(rng.standard_normal((B, Ti, Fi)), dtype=torch.float32, device="cuda"))
+    w = bf(torch.tensor(rng.standard_normal((KT, KF, 1, C)) * 0.2, dtype=torch.float32, device="cuda"))
+    bias = torch.tensor(rng.standard_normal(C), dtype=torch.float32, device="cuda")
+    dy = bf(torch.tensor(rng.standard_normal((B, To, Fo, C)), dtype=torch.float32, device="cuda"))
+    p, st_ = ops._p, ops._stream
+    y = torch.full((B, To, Fo, C), float("nan"), dtype=torch.float32, device="cuda")
+    sums = torch.full((2 * C,), float("nan"), dtype=torch.float64, device="cuda")
+    check(lib.ds2_conv1_fused_fwd(p(x), p(w), p(bias), p(y), p(sums), B, Ti, Fi, KT, KF, st, sf, st_()), "fwd")
+    dw = torch.full((KT, KF, 1, C), float("nan"), dtype=torch.float32, device="cuda")
+    db = torch.full((C,), float("nan"), dtype=torch.float32, device="cuda")
+    check(lib.ds2_conv1_fused_wgrad(p(x), p(dy), p(dw), p(db), B, Ti, Fi, KT, KF, st, sf, st_()), "wgrad")
+    mean = torch.empty(C, device="cuda")
+    rstd = torch.empty(C, device="cuda")
+    check(lib.ds2_bn_finalize(p(sums), float(B * To * Fo), C, 1e-3, p(mean), p(rstd), st_()), "finalize")
+    torch.cuda.synchronize()
+    xr = x.double().cpu().view(B, 1, Ti, Fi)
+    wr = w.double().cpu().requires_grad_(True)
+    br = bias.double().cpu().requires_grad_(True)
+    yr = torch.nn.functional.conv2d(xr, wr.permute(3, 2, 0, 1), br, stride=(st, sf))
+    (yr * dy.double().cpu().permute(0, 3, 1, 2)).sum().backward()
+    yn = yr.detach().permute(0, 2, 3, 1)
+    assert relerr(y.cpu().numpy(), yn.numpy()) < 1e-4
+    assert relerr(dw.cpu().numpy(), wr.grad.numpy()) < 1e-4
+    assert relerr(db.cpu().numpy(), br.grad.numpy()) < 1e-4
+    flat = yn.reshape(-1, C)
+    assert np.allclose(mean.cpu().numpy(), flat.mean(0).numpy(), rtol=1e-4, atol=1e-4)
+    assert np.allclose(rstd.cpu().numpy(), (1.0 / torch.sqrt(flat.var(0, unbiased=False) + 1e-3)).numpy(), rtol=1e-4)
+
+
 def test_conv_window_route_matches_patch_matrix_route():
     """The autograd wrappers: window form and explicit patch-matrix form of conv2 (with the fused BN1 + clip) agree to
     bf16 rounding of the operands (both round the same values; only summation order differs)."""
