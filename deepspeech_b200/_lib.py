@@ -68,7 +68,7 @@ _SIGS = {
     "ds2_conv_window_weights": (I, [P, P, P, I, I, P]),
     "ds2_conv_window_dy_layout": (I, [I, I, I, I, I, P, P]),
     "ds2_conv_window_pad_cast": (I, [P, P, I, I, I, I, I, I, P]),
-    "ds2_conv_window_fwd": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "ds2_conv_window_fwd": (I, [P, P, P, P, P, I, I, I, I, I, I, P]),
     "ds2_conv_window_dgrad": (I, [P, P, P, I, I, I, I, I, I, P]),
     "ds2_conv_window_wgrad": (I, [P, P, P, I, I, I, I, I, I, P]),
     "ds2_bn_stats": (I, [P, L, I, F, P, P, P, P]),

@@ -39,7 +39,7 @@ static constexpr int CW_STAGE_BYTES = CW_BOX;
 static constexpr int CW_MAX_WBOXES = 32;         // KT x chunks per filter row
 static constexpr int CW_W_OFF = CW_STAGES * CW_STAGE_BYTES;
 static constexpr int CW_BUF_BYTES = CW_W_OFF + CW_MAX_WBOXES * CW_WBOX;
-static constexpr int CW_SMEM = CW_BUF_BYTES + 1024 + 256;
+static constexpr int CW_SMEM = CW_BUF_BYTES + 1024 + 256 + 1024;   // + the epilogue warps' partial channel sums
 static constexpr int CWG_STAGES = 5;             // wgrad: two window boxes per stage; the tile's dy box in one of two slots
 static constexpr int CWG_STAGE_BYTES = 2 * CW_BOX;
 static constexpr int CWG_DY_OFF = CWG_STAGES * CWG_STAGE_BYTES;
@@ -53,6 +53,7 @@ struct WinMaps {
 struct WinParams {
   float* out;            // fwd: y [B,Rout,Pout,32] ; dgrad: da [B,Rout,Pout,32] ; wgrad: dW [KT*KF*32][32]
   const float* bias;     // fwd only
+  double* sums;          // fwd, optional: [64] per-channel sum and sum of squares of the output (batch-norm statistics), zeroed by the host
   int n_tiles;           // B * classes * G * np
   int Rout, Rsrc;        // rows per batch item of the output / of the source (dgrad, wgrad dy: padded rows per item)
   int Pout;              // valid positions per output row
@@ -216,6 +217,9 @@ conv_window_kernel(const __grid_constant__ WinMaps maps, const __grid_constant__
     // accumulator row of this thread -> packed row and position inside the box
     const int mrow = wq * 32 + lane;
     const int pi = mrow / p.PB, pp = mrow - pi * p.PB;
+    float s1[CW_C], s2[CW_C];            // running per-channel sums of this thread's outputs (p.sums)
+#pragma unroll
+    for (int j = 0; j < CW_C; ++j) { s1[j] = 0.f; s2[j] = 0.f; }
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
       const TileId t = tile_decode(p, tile);
       bool any = false;
@@ -243,9 +247,32 @@ conv_window_kernel(const __grid_constant__ WinMaps maps, const __grid_constant__
           o.z = (any ? __uint_as_float(v[j + 2]) : 0.f) + bias[j + 2];
           o.w = (any ? __uint_as_float(v[j + 3]) : 0.f) + bias[j + 3];
           dst[j / 4] = o;
+          if (p.sums) {
+            s1[j] += o.x; s1[j + 1] += o.y; s1[j + 2] += o.z; s1[j + 3] += o.w;
+            s2[j] = fmaf(o.x, o.x, s2[j]); s2[j + 1] = fmaf(o.y, o.y, s2[j + 1]);
+            s2[j + 2] = fmaf(o.z, o.z, s2[j + 2]); s2[j + 3] = fmaf(o.w, o.w, s2[j + 3]);
+          }
         }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    if (p.sums) {
+      float* red = reinterpret_cast<float*>(cw_smem_raw + (slot_addr + 16 - smem_u32(cw_smem_raw)));
+#pragma unroll
+      for (int j = 0; j < CW_C; ++j) {
+        s1[j] = warp_sum(s1[j]);
+        s2[j] = warp_sum(s2[j]);
+      }
+      if (lane == 0) {
+#pragma unroll
+        for (int j = 0; j < CW_C; ++j) {
+          red[wq * 64 + j] = s1[j];
+          red[wq * 64 + 32 + j] = s2[j];
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");      // the four epilogue warps
+      const int e = threadIdx.x - 128;
+      if (e >= 0 && e < 64) atomicAdd(p.sums + e, (double)red[e] + (double)red[64 + e] + (double)red[128 + e] + (double)red[192 + e]);
     }
   }
   tc_fence_before();
@@ -571,8 +598,8 @@ static int window_attr() {
   return DS2_OK;
 }
 
-extern "C" int ds2_conv_window_fwd(const void* a, const void* wt, const float* bias, float* y, int B, int Ti, int Fi, int KT, int KF,
-                                   int st, void* stream) {
+extern "C" int ds2_conv_window_fwd(const void* a, const void* wt, const float* bias, float* y, double* sums, int B, int Ti, int Fi, int KT,
+                                   int KF, int st, void* stream) {
   DS2_REQUIRE(a && wt && y, DS2_ERR_BAD_ARG, "ds2_conv_window_fwd: null pointer");
   int rc = window_shape_ok("ds2_conv_window_fwd", B, Ti, Fi, CW_C, CW_C, KT, KF, st, 1);
   if (rc) return rc;
@@ -587,6 +614,8 @@ extern "C" int ds2_conv_window_fwd(const void* a, const void* wt, const float* b
   fill_common(p, KT, KF, st);
   p.PB = k.PBf; p.RB = k.RBf; p.np = k.npf; p.G = (To + k.RBf - 1) / k.RBf; p.ncls = 1;
   p.out = y; p.bias = bias; p.n_tiles = B * p.G * p.np; p.Rout = To; p.Rsrc = Ti; p.Pout = Fo; p.win0 = 0; p.dgrad = 0;
+  p.sums = sums;
+  if (sums) DS2_CUDA(cudaMemsetAsync(sums, 0, 2 * CW_C * sizeof(double), static_cast<cudaStream_t>(stream)));
   const int grid = p.n_tiles < num_sms() ? p.n_tiles : num_sms();
   conv_window_kernel<<<grid, CW_THREADS, CW_SMEM, static_cast<cudaStream_t>(stream)>>>(ms, tw, p);
   DS2_LAUNCH_CHECK("conv_window_kernel<fwd>");

@@ -110,8 +110,15 @@ class DeepSpeech2(torch.nn.Module):
         odt = torch.bfloat16 if self.use_bf16 else torch.float32
         if self.use_bf16 and self.nf % 8 == 0:
             # tensor-core route: patches gathered in bf16 (BN1 + clip fused into conv2's gather), tcgen05 GEMMs
-            y1 = ops.conv2d_gemm(x, self.conv1_w, self.conv1_b, 2, 2)
-            y2 = ops.conv2d_gemm(y1, self.conv2_w, self.conv2_b, 2, 1, self.conv1_gamma, self.conv1_beta, self.eps, ops.RELU_CAP)
+            # (conv1: patch rows built in shared memory; both convolutions hand the batch-norm sums of their output on)
+            if ops.conv1_fused_takes(x, self.conv1_w, 2, 2):
+                y1, s1 = ops.conv1_fused(x, self.conv1_w, self.conv1_b, 2, 2)
+            else:
+                y1, s1 = ops.conv2d_gemm(x, self.conv1_w, self.conv1_b, 2, 2), None
+            y2, s2 = ops.conv2d_gemm(y1, self.conv2_w, self.conv2_b, 2, 1, self.conv1_gamma, self.conv1_beta, self.eps, ops.RELU_CAP,
+                                     sums_in=s1, want_sums=True)
+            return ops.bn_clip_to_rnn_layout(y2, self.conv2_gamma, self.conv2_beta, self.eps, ops.RELU_CAP,
+                                             "cf" if self.layout == "NCHW" else "fc", odt, sums=s2)
         else:
             y1 = ops.conv2d_nhwc(x, self.conv1_w, self.conv1_b, 2, 2)
             a1 = ops.bn_clip_nhwc(y1, self.conv1_gamma, self.conv1_beta, self.eps, ops.RELU_CAP)

@@ -203,15 +203,23 @@ def bn_stats(x: torch.Tensor, C: int, eps: float) -> Tuple[torch.Tensor, torch.T
     return mean, rstd
 
 
+def bn_stats_from_sums(sums: torch.Tensor, count: int, C: int, eps: float) -> Tuple[torch.Tensor, torch.Tensor]:
+    """mean / rstd from the per-channel sums a producer kernel accumulated in its epilogue (f64 [2C]: sum, sum of squares)."""
+    mean = torch.empty(C, dtype=torch.float32, device=sums.device)
+    rstd = torch.empty(C, dtype=torch.float32, device=sums.device)
+    check(lib.ds2_bn_finalize(_p(sums), float(count), C, eps, _p(mean), _p(rstd), _stream()), "ds2_bn_finalize")
+    return mean, rstd
+
+
 class _BnClipFn(torch.autograd.Function):
     """y = clip(gamma * (x - mean_batch) * rstd_batch + beta) over a channel-last [B,T,F,C] tensor;
     the output is written with element strides `omap` = (sb, st, sf, sc) into a tensor of shape
     `oshape` / dtype `odtype` (NHWC itself, or the RNN layout)."""
 
     @staticmethod
-    def forward(ctx, x, gamma, beta, eps, cap, oshape, omap, odtype):
+    def forward(ctx, x, gamma, beta, eps, cap, oshape, omap, odtype, sums=None):
         B, T, Fq, C = x.shape
-        mean, rstd = bn_stats(x, C, eps)
+        mean, rstd = bn_stats(x, C, eps) if sums is None else bn_stats_from_sums(sums, B * T * Fq, C, eps)
         out = torch.empty(oshape, dtype=odtype, device=x.device)
         clip = cap is not None
         check(lib.ds2_bn_clip_fwd(_p(x), B, T, Fq, C, _p(mean), _p(rstd), _p(gamma), _p(beta), float(cap or 0.0), int(clip),
@@ -231,23 +239,23 @@ class _BnClipFn(torch.autograd.Function):
         check(lib.ds2_bn_clip_bwd(_p(x), B, T, Fq, C, _p(mean), _p(rstd), _p(gamma), _p(beta), float(ctx.cap or 0.0),
                                   int(ctx.cap is not None), _p(dout), _dt(dout), *ctx.omap, _p(_bn_scratch(x.device)),
                                   _p(dx), _p(dgamma), _p(dbeta), _stream()), "ds2_bn_clip_bwd")
-        return dx, dgamma, dbeta, None, None, None, None, None
+        return dx, dgamma, dbeta, None, None, None, None, None, None
 
 
 def bn_clip_nhwc(x, gamma, beta, eps, cap=None):
     """channel-last in, channel-last out (fp32)."""
     B, T, Fq, C = x.shape
     omap = (T * Fq * C, Fq * C, C, 1)
-    return _BnClipFn.apply(x.contiguous(), gamma, beta, eps, cap, tuple(x.shape), omap, torch.float32)
+    return _BnClipFn.apply(x.contiguous(), gamma, beta, eps, cap, tuple(x.shape), omap, torch.float32, None)
 
 
-def bn_clip_to_rnn_layout(x, gamma, beta, eps, cap, feature_order: str, odtype):
+def bn_clip_to_rnn_layout(x, gamma, beta, eps, cap, feature_order: str, odtype, sums=None):
     """channel-last [B,T,F,C] in, time-major [T,B,C*F] out; feature = c*F+f ('cf', NCHW model,
     src/deepSpeech_NCHW.py:166-168) or f*C+c ('fc', NHWC model, src/deepSpeech.py:162-164)."""
     B, T, Fq, C = x.shape
     feat = C * Fq
     omap = (feat, B * feat, 1, Fq) if feature_order == "cf" else (feat, B * feat, C, 1)
-    return _BnClipFn.apply(x.contiguous(), gamma, beta, eps, cap, (T, B, feat), omap, odtype)
+    return _BnClipFn.apply(x.contiguous(), gamma, beta, eps, cap, (T, B, feat), omap, odtype, sums)
 
 
 # ------------------------------------------------------------------------------------ conv2d (channel-last, HWIO)
@@ -379,7 +387,7 @@ class _ConvWindowFn(torch.autograd.Function):
     overlapping filter windows of it through a strided TMA view (ds2_conv_window_*; 32 channels in and out, sf = 1)."""
 
     @staticmethod
-    def forward(ctx, x, w, bias, st, gamma, beta, eps, cap):
+    def forward(ctx, x, w, bias, st, gamma, beta, eps, cap, sums_in, want_sums):
         B, Ti, Fi, Ci = x.shape
         KT, KF, _, Co = w.shape
         To, Fo = (Ti - KT) // st + 1, Fi - KF + 1
@@ -390,7 +398,7 @@ class _ConvWindowFn(torch.autograd.Function):
         mean = rstd = None
         a = _slack_bf16((B, Ti, Fi, Ci), dev)
         if has_bn:
-            mean, rstd = bn_stats(x, Ci, eps)
+            mean, rstd = bn_stats(x, Ci, eps) if sums_in is None else bn_stats_from_sums(sums_in, B * Ti * Fi, Ci, eps)
             omap = (Ti * Fi * Ci, Fi * Ci, Ci, 1)
             check(lib.ds2_bn_clip_fwd(_p(x), B, Ti, Fi, Ci, _p(mean), _p(rstd), _p(gamma), _p(beta), float(cap or 0.0),
                                       int(cap is not None), _p(a), DS2_BF16, *omap, _stream()), "ds2_bn_clip_fwd")
@@ -401,14 +409,18 @@ class _ConvWindowFn(torch.autograd.Function):
         wd = torch.empty((Ci, K), dtype=torch.bfloat16, device=dev)
         check(lib.ds2_conv_window_weights(_p(w), _p(wt), _p(wd), KT, KF, _stream()), "ds2_conv_window_weights")
         y = torch.empty((B, To, Fo, Co), dtype=torch.float32, device=dev)
-        check(lib.ds2_conv_window_fwd(_p(a), _p(wt), _p(bias), _p(y), B, Ti, Fi, KT, KF, st, _stream()), "ds2_conv_window_fwd")
+        sums = torch.empty(2 * Co, dtype=torch.float64, device=dev) if want_sums else None
+        check(lib.ds2_conv_window_fwd(_p(a), _p(wt), _p(bias), _p(y), _p(sums), B, Ti, Fi, KT, KF, st, _stream()), "ds2_conv_window_fwd")
         ctx.save_for_backward(x, gamma, beta, mean, rstd, a, wd)
         ctx.geom = (B, Ti, Fi, Ci, KT, KF, st, To, Fo, Co)
         ctx.misc = (eps, cap, has_bn, bias is not None, tuple(w.shape))
+        if want_sums:
+            ctx.mark_non_differentiable(sums)
+            return y, sums
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, *_unused):
         x, gamma, beta, mean, rstd, a, wd = ctx.saved_tensors
         B, Ti, Fi, Ci, KT, KF, st, To, Fo, Co = ctx.geom
         eps, cap, has_bn, has_bias, wshape = ctx.misc
@@ -432,22 +444,68 @@ class _ConvWindowFn(torch.autograd.Function):
                                           _p(dbeta), _stream()), "ds2_bn_clip_bwd")
             else:
                 dx = da
-        return dx, dw, db, None, dgamma, dbeta, None, None
+        return dx, dw, db, None, dgamma, dbeta, None, None, None, None
+
+
+class _Conv1FusedFn(torch.autograd.Function):
+    """y = conv(x, w) + bias for a one-channel input and 32 filters, the patch rows built in shared memory
+    (ds2_conv1_fused_*); also returns the per-channel sums of y and y^2 its epilogue accumulated (for the batch norm that
+    follows).  x fp32 [B,Ti,Fi,1]; no gradient flows into x."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias, st, sf):
+        B, Ti, Fi, _ = x.shape
+        KT, KF, _, Co = w.shape
+        To, Fo = (Ti - KT) // st + 1, (Fi - KF) // sf + 1
+        y = torch.empty((B, To, Fo, Co), dtype=torch.float32, device=x.device)
+        sums = torch.empty(2 * Co, dtype=torch.float64, device=x.device)
+        check(lib.ds2_conv1_fused_fwd(_p(x), _p(w), _p(bias), _p(y), _p(sums), B, Ti, Fi, KT, KF, st, sf, _stream()), "ds2_conv1_fused_fwd")
+        ctx.save_for_backward(x)
+        ctx.geom = (B, Ti, Fi, KT, KF, st, sf)
+        ctx.misc = (tuple(w.shape), bias is not None)
+        ctx.mark_non_differentiable(sums)
+        return y, sums
+
+    @staticmethod
+    def backward(ctx, dy, _dsums):
+        (x,) = ctx.saved_tensors
+        wshape, has_bias = ctx.misc
+        dy = cast(dy.contiguous(), torch.float32)
+        dw = torch.empty(wshape, dtype=torch.float32, device=x.device)
+        db = torch.empty(wshape[3], dtype=torch.float32, device=x.device) if has_bias else None
+        check(lib.ds2_conv1_fused_wgrad(_p(x), _p(dy), _p(dw), _p(db), *ctx.geom, _stream()), "ds2_conv1_fused_wgrad")
+        return None, dw, db, None, None
 
 
 USE_CONV_WINDOW = True
+USE_CONV1_FUSED = True
 
 
-def conv2d_gemm(x, w, bias, st, sf, gamma=None, beta=None, eps=1e-3, cap=None):
+def conv1_fused_takes(x, w, st, sf) -> bool:
+    KT, KF, Ci, Co = w.shape
+    return bool(USE_CONV1_FUSED and x.dtype == torch.float32 and x.is_cuda and
+                lib.ds2_conv1_fused_supported(Ci, Co, x.shape[1], x.shape[2], KT, KF, st, sf))
+
+
+def conv1_fused(x, w, bias, st, sf):
+    """-> (y fp32 [B,To,Fo,32], sums f64 [64]) ; x fp32 [B,Ti,Fi,1]."""
+    _need_cuda(x, w)
+    return _Conv1FusedFn.apply(x.contiguous(), w.contiguous(), bias, st, sf)
+
+
+def conv2d_gemm(x, w, bias, st, sf, gamma=None, beta=None, eps=1e-3, cap=None, sums_in=None, want_sums=False):
     """Tensor-core convolution of f(x): f = clip(BN(x)) when gamma/beta are given, identity otherwise.
-    32-channel layers with sf = 1 take the implicit (window) form, everything else the explicit patch matrix."""
+    32-channel layers with sf = 1 take the implicit (window) form, everything else the explicit patch matrix.
+    sums_in: per-channel sums of x from its producer's epilogue (instead of a statistics pass over x); want_sums: also
+    return the sums of the output (window form only: -> (y, sums); the patch-matrix form returns (y, None))."""
     _need_cuda(x, w)
     if x.dtype != torch.float32:
         raise ValueError("conv2d_gemm: fp32 input expected")
     KT, KF, Ci, Co = w.shape
     if USE_CONV_WINDOW and lib.ds2_conv_window_supported(Ci, Co, x.shape[2], KT, KF, sf):
-        return _ConvWindowFn.apply(x.contiguous(), w.contiguous(), bias, st, gamma, beta, eps, cap)
-    return _ConvGemmFn.apply(x.contiguous(), w.contiguous(), bias, st, sf, gamma, beta, eps, cap)
+        return _ConvWindowFn.apply(x.contiguous(), w.contiguous(), bias, st, gamma, beta, eps, cap, sums_in, want_sums)
+    y = _ConvGemmFn.apply(x.contiguous(), w.contiguous(), bias, st, sf, gamma, beta, eps, cap)
+    return (y, None) if want_sums else y
 
 
 # ------------------------------------------------------------------------------------ recurrent stack

@@ -200,14 +200,15 @@ int ds2_conv1_fused_wgrad(const float* x, const float* dy, float* dw, float* db,
  *                             (both from ds2_conv_window_dy_layout; written by ds2_conv_window_pad_cast): the kernels
  *                             pack several rows into one 128-row MMA tile and read the rows a filter tap reaches
  *                             outside [0,To) as zeros; 64 bytes of slack after the last element as for `a`;
- *   y    f32 [B,To,Fo,32], da f32 [B,Ti,Fi,32] (every element written), dw f32 HWIO [KT,KF,32,32].
+ *   y    f32 [B,To,Fo,32], da f32 [B,Ti,Fi,32] (every element written), dw f32 HWIO [KT,KF,32,32];
+ *   sums (optional) f64 [64]: per-channel sum and sum of squares of y from the forward epilogue, for ds2_bn_finalize.
  * ds2_conv_window_supported tells whether a shape is taken. */
 int ds2_conv_window_supported(int Ci, int Co, int Fi, int KT, int KF, int sf);
 int ds2_conv_window_weights(const float* w, void* wt, void* wd, int KT, int KF, void* stream);
 int ds2_conv_window_dy_layout(int Ti, int Fi, int KT, int KF, int st, int* ptop, int* rows_per_item);
 int ds2_conv_window_pad_cast(const float* dy, void* dyp, int B, int Ti, int Fi, int KT, int KF, int st, void* stream);
-int ds2_conv_window_fwd(const void* a, const void* wt, const float* bias, float* y, int B, int Ti, int Fi, int KT, int KF, int st,
-                        void* stream);
+int ds2_conv_window_fwd(const void* a, const void* wt, const float* bias, float* y, double* sums, int B, int Ti, int Fi, int KT, int KF,
+                        int st, void* stream);
 int ds2_conv_window_dgrad(const void* dyp, const void* wd, float* da, int B, int Ti, int Fi, int KT, int KF, int st, void* stream);
 int ds2_conv_window_wgrad(const void* a, const void* dyp, float* dw, int B, int Ti, int Fi, int KT, int KF, int st, void* stream);
 

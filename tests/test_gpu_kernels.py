@@ -225,7 +225,8 @@ def test_conv_window_kernels_vs_fp64(B, Ti, Fi, KT, KF, st):
     wd = torch.empty((C, K), dtype=torch.bfloat16, device="cuda")
     check(lib.ds2_conv_window_weights(p(w), p(wt), p(wd), KT, KF, st_()), "weights")
     y = torch.full((B, To, Fo, C), float("nan"), dtype=torch.float32, device="cuda")
-    check(lib.ds2_conv_window_fwd(p(a), p(wt), p(bias), p(y), B, Ti, Fi, KT, KF, st, st_()), "fwd")
+    sums = torch.full((64,), float("nan"), dtype=torch.float64, device="cuda")
+    check(lib.ds2_conv_window_fwd(p(a), p(wt), p(bias), p(y), p(sums), B, Ti, Fi, KT, KF, st, st_()), "fwd")
     dyp = ops.conv_window_padded_dy(dy, B, Ti, Fi, KT, KF, st)
     dw = torch.full((KT, KF, C, C), float("nan"), dtype=torch.float32, device="cuda")
     check(lib.ds2_conv_window_wgrad(p(a), p(dyp), p(dw), B, Ti, Fi, KT, KF, st, st_()), "wgrad")
@@ -239,6 +240,10 @@ def test_conv_window_kernels_vs_fp64(B, Ti, Fi, KT, KF, st):
     assert relerr(y.cpu().permute(0, 3, 1, 2).numpy(), yr.detach().numpy()) < 1e-4
     assert relerr(dw.cpu().numpy(), wr.grad.numpy()) < 1e-4
     assert relerr(da.cpu().permute(0, 3, 1, 2).numpy(), xr.grad.numpy()) < 1e-4
+    # batch-norm sums from the forward epilogue
+    flat = yr.detach().permute(0, 2, 3, 1).reshape(-1, C)
+    assert np.allclose(sums[:C].cpu().numpy(), flat.sum(0).numpy(), rtol=1e-4, atol=1e-5 * float(flat.abs().sum(0).max()))
+    assert np.allclose(sums[C:].cpu().numpy(), (flat * flat).sum(0).numpy(), rtol=1e-4)
 
 
 @pytest.mark.parametrize("B,Ti,Fi,KT,KF,st,sf", [(2, 60, 161, 20, 5, 2, 2), (1, 25, 40, 5, 3, 2, 1), (3, 23, 17, 4, 8, 1, 2), (2, 300, 161, 20, 5, 2, 2),

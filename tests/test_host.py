@@ -51,7 +51,7 @@ def test_c_abi_argument_validation_without_gpu():
     assert lib.ds2_adam_ema_chunk() > 0
     assert lib.ds2_adam_ema_step(None, 1, 1, 1e-3, 0.9, 0.999, 1e-8, 1, 0.99, 1.0, None) == 1
     assert lib.ds2_ctc_greedy_decode(None, 4, 1, 29, None, None, None, None) == 1
-    assert lib.ds2_conv_window_fwd(None, None, None, None, 1, 20, 20, 3, 3, 1, None) == 1
+    assert lib.ds2_conv_window_fwd(None, None, None, None, None, 1, 20, 20, 3, 3, 1, None) == 1
 
 
 def test_no_cpu_fallback():

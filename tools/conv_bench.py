@@ -42,7 +42,7 @@ def timeit(fn, n=5):
 
 
 flops = 2.0 * B * To * Fo * K * C
-for name, fn in (("fwd", lambda: check(lib.ds2_conv_window_fwd(p(a), p(wt), p(bias), p(y), B, Ti, Fi, KT, KF, st, s()), "f")),
+for name, fn in (("fwd", lambda: check(lib.ds2_conv_window_fwd(p(a), p(wt), p(bias), p(y), None, B, Ti, Fi, KT, KF, st, s()), "f")),
                  ("dgrad", lambda: check(lib.ds2_conv_window_dgrad(p(dyp), p(wd), p(da), B, Ti, Fi, KT, KF, st, s()), "d")),
                  ("wgrad", lambda: check(lib.ds2_conv_window_wgrad(p(a), p(dyp), p(dw), B, Ti, Fi, KT, KF, st, s()), "w"))):
     ms = timeit(fn)
