@@ -50,36 +50,57 @@ __host__ __device__ inline Smem smem_layout(int nslab_alloc, int stage_floats, b
   s.w_off = s.a_off + nslab_alloc * SLAB;                        // fwd: filters; wgrad: unused
   s.dy_off = s.w_off + (wgrad ? 0 : nslab_alloc * WSLAB);        // wgrad: the tile's dy rows [128 x 128 B]
   s.stage_off = s.dy_off + (wgrad ? SLAB : 0);
-  s.red_off = s.stage_off + ((stage_floats * 4 + 127) & ~127);
+  s.red_off = s.stage_off + 2 * ((stage_floats * 4 + 127) & ~127);     // two buffers: the next tile's rows load during this tile
   s.bar_off = s.red_off + 8 * 64 * 4;                            // per-warp partial channel sums
   s.total = s.bar_off + 64;
   return s;
 }
 
-// the input rows a tile touches -> shared memory (coalesced scalar loads: rows of Fi floats are not 16-byte aligned)
-__device__ __forceinline__ void stage_rows(const Params& p, float* stage, int b, int t0, int nrows) {
-  const float* src = p.x + ((size_t)b * p.Ti + (size_t)t0 * p.st) * p.Fi;
-  const int rows_avail = p.Ti - t0 * p.st;
-  const int nr = nrows < rows_avail ? nrows : rows_avail;
-  for (int r = threadIdx.x >> 5; r < nr; r += THREADS / 32) {
-    const float* s = src + (size_t)r * p.Fi;
-    float* d = stage + r * p.stage_pitch;
-    for (int c = threadIdx.x & 31; c < p.Fi; c += 32) d[c] = __ldg(s + c);
+// the input rows tile `tile` touches -> shared memory, asynchronously (4-byte cp.async: rows of Fi floats are not 16-byte
+// aligned); the caller waits with stage_wait() one tile later
+__device__ __forceinline__ void stage_rows_async(const Params& p, uint32_t stage_addr, int tile) {
+  if (tile < p.n_tiles) {
+    const int b = tile / p.tiles_per_item, pos0 = (tile - b * p.tiles_per_item) * 128;
+    const int t0 = pos0 / p.Fo;
+    const int last = min(pos0 + 127, p.To * p.Fo - 1);
+    const int nrows = (last / p.Fo - t0) * p.st + p.KT;
+    const float* src = p.x + ((size_t)b * p.Ti + (size_t)t0 * p.st) * p.Fi;
+    for (int r = threadIdx.x >> 5; r < nrows; r += THREADS / 32) {
+      const float* s = src + (size_t)r * p.Fi;
+      const uint32_t d = stage_addr + r * p.stage_pitch * 4;
+      for (int c = threadIdx.x & 31; c < p.Fi; c += 32)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + c * 4), "l"(s + c) : "memory");
+    }
   }
+  asm volatile("cp.async.commit_group;" ::: "memory");
 }
+__device__ __forceinline__ void stage_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-// patch rows of the tile as the 128B-swizzled K-major operand: row m, 16-byte chunk kt = the KF taps of filter row kt
-__device__ __forceinline__ void build_patches(const Params& p, const float* stage, uint32_t sA, int pos0, int t0, int npos_item) {
+// patch rows of the tile as the 128B-swizzled K-major operand: row m, 16-byte chunk kt = the KF taps of filter row kt.
+// KFT > 0: the tap count at compile time (unrolled shared-space loads); 0: p.KF at run time.
+template <int KFT>
+__device__ __forceinline__ void build_patches(const Params& p, uint32_t stage_addr, uint32_t sA, int pos0, int t0, int npos_item) {
   const int m = threadIdx.x & 127;
   const int pos = pos0 + m;
   const bool valid = pos < npos_item;
   const int t = valid ? pos / p.Fo : t0, f = valid ? pos - t * p.Fo : 0;
-  const float* base = stage + ((t - t0) * p.st) * p.stage_pitch + f * p.sf;
+  const uint32_t base = stage_addr + (((t - t0) * p.st) * p.stage_pitch + f * p.sf) * 4;
   const uint32_t row_addr = sA + m * 128;
+  const uint32_t pitch_b = p.stage_pitch * 4;
+  const int KF = KFT > 0 ? KFT : p.KF;
+  const bool wide = KFT == 5 && (p.sf & 1) == 0;      // taps start at an even column: 8-byte aligned, two 64-bit loads + one
   for (int kt = threadIdx.x >> 7; kt < p.KT; kt += THREADS / 128) {
     float v[MAX_KF];
+    if (wide) {
+      const uint32_t a = base + kt * pitch_b;
+      asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v[0]), "=f"(v[1]) : "r"(a) : "memory");
+      asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v[2]), "=f"(v[3]) : "r"(a + 8) : "memory");
+      v[4] = lds_f32(a + 16);
+      v[5] = v[6] = v[7] = 0.f;
+    } else {
 #pragma unroll
-    for (int k = 0; k < MAX_KF; ++k) v[k] = (valid && k < p.KF) ? base[kt * p.stage_pitch + k] : 0.f;
+      for (int k = 0; k < MAX_KF; ++k) v[k] = (k < KF) ? lds_f32(base + kt * pitch_b + k * 4) : 0.f;
+    }
     uint4 pk;
     __nv_bfloat162 h0 = __floats2bfloat162_rn(v[0], v[1]), h1 = __floats2bfloat162_rn(v[2], v[3]);
     __nv_bfloat162 h2 = __floats2bfloat162_rn(v[4], v[5]), h3 = __floats2bfloat162_rn(v[6], v[7]);
@@ -87,10 +108,12 @@ __device__ __forceinline__ void build_patches(const Params& p, const float* stag
     pk.y = *reinterpret_cast<uint32_t*>(&h1);
     pk.z = *reinterpret_cast<uint32_t*>(&h2);
     pk.w = *reinterpret_cast<uint32_t*>(&h3);
+    if (!valid) pk = make_uint4(0u, 0u, 0u, 0u);
     sts_v4(row_addr + (kt >> 3) * SLAB + (((kt & 7) ^ (m & 7)) << 4), pk);
   }
 }
 
+template <int KFT>
 __global__ void __launch_bounds__(THREADS, 2)
 conv1_fwd_kernel(Params p) {
   extern __shared__ __align__(1024) uint8_t c1_smem_raw[];
@@ -98,7 +121,7 @@ conv1_fwd_kernel(Params p) {
   uint8_t* gbase = c1_smem_raw + (sbase - smem_u32(c1_smem_raw));
   const Smem L = smem_layout(p.nslab, p.stage_rows * p.stage_pitch, false);
   const uint32_t sA = sbase + L.a_off, sW = sbase + L.w_off;
-  float* stage = reinterpret_cast<float*>(gbase + L.stage_off);
+  const uint32_t stage_bytes = (uint32_t)((p.stage_rows * p.stage_pitch * 4 + 127) & ~127);
   float* red = reinterpret_cast<float*>(gbase + L.red_off);
   const uint32_t mma_bar = sbase + L.bar_off;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + L.bar_off + 16);
@@ -108,7 +131,8 @@ conv1_fwd_kernel(Params p) {
     mbar_init(reinterpret_cast<uint64_t*>(gbase + L.bar_off), 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 32);
+  if (warp == 1) tmem_alloc(tmem_slot, 64);
+  stage_rows_async(p, sbase + L.stage_off, blockIdx.x);
   // zero the operand buffers once (chunks of filter rows beyond KT are part of the contraction), then the filters:
   // row co, chunk kt = w[kt][0..KF-1][co]
   for (uint32_t o = threadIdx.x * 16u; o < (uint32_t)(p.nslab * (SLAB + WSLAB)); o += THREADS * 16u) sts_v4(sbase + o, make_uint4(0u, 0u, 0u, 0u));
@@ -138,34 +162,15 @@ conv1_fwd_kernel(Params p) {
   const int npos_item = p.To * p.Fo;
   const int ksteps = (p.KT + 1) / 2;                  // 16 K columns = two filter rows per MMA
   const uint32_t idesc = umma_idesc_bf16(128, CO, 0, 0);
-  uint32_t ph = 0;
-  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+  // the epilogue of one tile: accumulators (+ bias) -> y, running channel sums
+  auto epilogue = [&](int tile, int acc) {
     const int b = tile / p.tiles_per_item, pos0 = (tile - b * p.tiles_per_item) * 128;
-    const int t0 = pos0 / p.Fo;
-    const int last = min(pos0 + 127, npos_item - 1);
-    const int nrows = (last / p.Fo - t0) * p.st + p.KT;
-    stage_rows(p, stage, b, t0, nrows);
-    __syncthreads();
-    build_patches(p, stage, sA, pos0, t0, npos_item);
-    fence_proxy_async();
-    __syncthreads();
-    if (warp == 0 && elect_one_sync()) {
-      tc_fence_after();
-      for (int ks = 0; ks < ksteps; ++ks)
-        umma_bf16(tmem_base, umma_smem_desc_sw128(sA + (ks >> 2) * SLAB + (ks & 3) * 32, 16, 1024),
-                  umma_smem_desc_sw128(sW + (ks >> 2) * WSLAB + (ks & 3) * 32, 16, 1024), idesc, ks > 0 ? 1u : 0u);
-      umma_commit(mma_bar);
-    }
-    __syncwarp();
-    mbar_wait(mma_bar, ph, 500);
-    ph ^= 1;
-    tc_fence_after();
     uint32_t v[16];
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
           "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-        : "r"(tmem_base + half * 16 + (static_cast<uint32_t>(q * 32) << 16))
+        : "r"(tmem_base + acc * CO + half * 16 + (static_cast<uint32_t>(q * 32) << 16))
         : "memory");
     tmem_ld_wait();
     tc_fence_before();
@@ -182,7 +187,41 @@ conv1_fwd_kernel(Params p) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) dst[j] = make_float4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
     }
-    __syncthreads();      // the accumulators and the operand buffers are free again
+  };
+  // Per tile: wait for its staged rows, start the next tile's, build the patch rows, issue the MMAs into one of two
+  // accumulators, and while they run take the PREVIOUS tile's accumulator through the epilogue.
+  uint32_t ph = 0;
+  int buf = 0, it = 0, prev_tile = -1;
+  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, buf ^= 1, ++it) {
+    const int b = tile / p.tiles_per_item, pos0 = (tile - b * p.tiles_per_item) * 128;
+    const int t0 = pos0 / p.Fo;
+    (void)b;
+    stage_wait();
+    if (prev_tile >= 0) {              // the previous tile's MMAs have read the patch buffer (and filled its accumulator)
+      mbar_wait(mma_bar, ph, 500);
+      ph ^= 1;
+      tc_fence_after();
+    }
+    __syncthreads();
+    stage_rows_async(p, sbase + L.stage_off + (buf ^ 1) * stage_bytes, tile + gridDim.x);
+    build_patches<KFT>(p, sbase + L.stage_off + buf * stage_bytes, sA, pos0, t0, npos_item);
+    fence_proxy_async();
+    __syncthreads();
+    if (warp == 0 && elect_one_sync()) {
+      tc_fence_after();
+      for (int ks = 0; ks < ksteps; ++ks)
+        umma_bf16(tmem_base + (it & 1) * CO, umma_smem_desc_sw128(sA + (ks >> 2) * SLAB + (ks & 3) * 32, 16, 1024),
+                  umma_smem_desc_sw128(sW + (ks >> 2) * WSLAB + (ks & 3) * 32, 16, 1024), idesc, ks > 0 ? 1u : 0u);
+      umma_commit(mma_bar);
+    }
+    __syncwarp();
+    if (prev_tile >= 0) epilogue(prev_tile, (it - 1) & 1);
+    prev_tile = tile;
+  }
+  if (prev_tile >= 0) {
+    mbar_wait(mma_bar, ph, 501);
+    tc_fence_after();
+    epilogue(prev_tile, (it - 1) & 1);
   }
   if (p.sums) {
     // per-channel sums: lanes -> warp, the four quarter warps of a half -> one double atomic per channel and moment
@@ -210,20 +249,23 @@ conv1_fwd_kernel(Params p) {
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 32);
+    tmem_dealloc(tmem_base, 64);
   }
 }
 
 // ------------------------------------------------------------------ weight and bias gradient
+template <int KFT>
 __global__ void __launch_bounds__(THREADS, 2)
 conv1_wgrad_kernel(Params p) {
   extern __shared__ __align__(1024) uint8_t c1_smem_raw[];
   const uint32_t sbase = (smem_u32(c1_smem_raw) + 1023u) & ~1023u;
   uint8_t* gbase = c1_smem_raw + (sbase - smem_u32(c1_smem_raw));
   const int nblk = (p.nslab + 1) / 2;                 // MMA blocks of two 64-wide slabs (M = 128 window elements)
-  const Smem L = smem_layout(2 * nblk, p.stage_rows * p.stage_pitch, true);
+  // with an odd slab count the last block's second half reads whatever follows the last slab (the dy tile): rows 64..127
+  // of that block's accumulators are never used
+  const Smem L = smem_layout(p.nslab, p.stage_rows * p.stage_pitch, true);
   const uint32_t sA = sbase + L.a_off, sDy = sbase + L.dy_off;
-  float* stage = reinterpret_cast<float*>(gbase + L.stage_off);
+  const uint32_t stage_bytes = (uint32_t)((p.stage_rows * p.stage_pitch * 4 + 127) & ~127);
   float* red = reinterpret_cast<float*>(gbase + L.red_off);
   const uint32_t mma_bar = sbase + L.bar_off;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + L.bar_off + 16);
@@ -234,7 +276,8 @@ conv1_wgrad_kernel(Params p) {
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 64);
-  for (uint32_t o = threadIdx.x * 16u; o < (uint32_t)(2 * nblk * SLAB + SLAB); o += THREADS * 16u) sts_v4(sbase + o, make_uint4(0u, 0u, 0u, 0u));
+  stage_rows_async(p, sbase + L.stage_off, blockIdx.x);
+  for (uint32_t o = threadIdx.x * 16u; o < (uint32_t)(p.nslab * SLAB + SLAB); o += THREADS * 16u) sts_v4(sbase + o, make_uint4(0u, 0u, 0u, 0u));
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -249,12 +292,10 @@ conv1_wgrad_kernel(Params p) {
   uint32_t ph = 0;
   bool first = true;
   const bool has_tiles = (int)blockIdx.x < p.n_tiles;
-  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+  int buf = 0;
+  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, buf ^= 1) {
     const int b = tile / p.tiles_per_item, pos0 = (tile - b * p.tiles_per_item) * 128;
     const int t0 = pos0 / p.Fo;
-    const int last = min(pos0 + 127, npos_item - 1);
-    const int nrows = (last / p.Fo - t0) * p.st + p.KT;
-    stage_rows(p, stage, b, t0, nrows);
     // this thread's half row of dy (issued before the wait: the loads overlap the previous tile's MMAs)
     const int pos = pos0 + m;
     float4 g[4];
@@ -269,8 +310,10 @@ conv1_wgrad_kernel(Params p) {
       mbar_wait(mma_bar, ph, 510);
       ph ^= 1;
     }
+    stage_wait();
     __syncthreads();
-    build_patches(p, stage, sA, pos0, t0, npos_item);
+    stage_rows_async(p, sbase + L.stage_off + (buf ^ 1) * stage_bytes, tile + gridDim.x);
+    build_patches<KFT>(p, sbase + L.stage_off + buf * stage_bytes, sA, pos0, t0, npos_item);
     {
       const float* gf = reinterpret_cast<const float*>(g);
       uint32_t h[8];
@@ -358,8 +401,8 @@ static int conv1_geometry(int Ti, int Fi, int KT, int KF, int st, int sf, Params
   const int rows = (nt_max - 1) * st + KT;
   const int pitch = (Fi + 3) & ~3;
   const size_t sf_bytes = smem_layout(nslab, rows * pitch, false).total + 1024;
-  const size_t sw_bytes = smem_layout(2 * ((nslab + 1) / 2), rows * pitch, true).total + 1024;
-  if (sf_bytes > 110 * 1024 || sw_bytes > 110 * 1024) return 0;  // two CTAs per SM
+  const size_t sw_bytes = smem_layout(nslab, rows * pitch, true).total + 1024;
+  if (sf_bytes > 112 * 1024 || sw_bytes > 112 * 1024) return 0;  // two CTAs per SM
   if (p) {
     p->To = To; p->Fo = Fo; p->nslab = nslab; p->stage_rows = rows; p->stage_pitch = pitch;
     p->tiles_per_item = (To * Fo + 127) / 128;
@@ -376,8 +419,10 @@ extern "C" int ds2_conv1_fused_supported(int Ci, int Co, int Ti, int Fi, int KT,
 static int conv1_attr() {
   static unsigned long long done_devs = 0;
   if (first_use_on_device(&done_devs)) {
-    DS2_CUDA(cudaFuncSetAttribute(conv1_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
-    DS2_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+    DS2_CUDA(cudaFuncSetAttribute(conv1_fwd_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+    DS2_CUDA(cudaFuncSetAttribute(conv1_fwd_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+    DS2_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+    DS2_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
   }
   return DS2_OK;
 }
@@ -397,7 +442,8 @@ extern "C" int ds2_conv1_fused_fwd(const float* x, const float* w, const float* 
   p.B = B; p.Ti = Ti; p.Fi = Fi; p.KT = KT; p.KF = KF; p.st = st; p.sf = sf;
   p.n_tiles = B * p.tiles_per_item;
   const int grid = p.n_tiles < 2 * num_sms() ? p.n_tiles : 2 * num_sms();
-  conv1_fwd_kernel<<<grid, THREADS, smem, cs>>>(p);
+  if (KF == 5) conv1_fwd_kernel<5><<<grid, THREADS, smem, cs>>>(p);      // the reference's [20,5] filter
+  else conv1_fwd_kernel<0><<<grid, THREADS, smem, cs>>>(p);
   DS2_LAUNCH_CHECK("conv1_fwd_kernel");
   count_launch();
   return DS2_OK;
@@ -419,7 +465,8 @@ extern "C" int ds2_conv1_fused_wgrad(const float* x, const float* dy, float* dw,
   p.B = B; p.Ti = Ti; p.Fi = Fi; p.KT = KT; p.KF = KF; p.st = st; p.sf = sf;
   p.n_tiles = B * p.tiles_per_item;
   const int grid = p.n_tiles < 2 * num_sms() ? p.n_tiles : 2 * num_sms();
-  conv1_wgrad_kernel<<<grid, THREADS, smem, cs>>>(p);
+  if (KF == 5) conv1_wgrad_kernel<5><<<grid, THREADS, smem, cs>>>(p);
+  else conv1_wgrad_kernel<0><<<grid, THREADS, smem, cs>>>(p);
   DS2_LAUNCH_CHECK("conv1_wgrad_kernel");
   count_launch();
   return DS2_OK;

@@ -47,3 +47,19 @@ for name, fn in (("fwd", lambda: check(lib.ds2_conv_window_fwd(p(a), p(wt), p(bi
                  ("wgrad", lambda: check(lib.ds2_conv_window_wgrad(p(a), p(dyp), p(dw), B, Ti, Fi, KT, KF, st, s()), "w"))):
     ms = timeit(fn)
     print("conv2 %-5s B=%d: %.3f ms  (%.0f TFLOP/s of the %.0f GFLOP)" % (name, B, ms, flops / ms / 1e9, flops / 1e9))
+
+# conv1 (one input channel, filter [20,5], strides (2,2)) through the fused kernels
+Ti1, Fi1 = 1500, 161
+To1, Fo1 = (Ti1 - 20) // 2 + 1, (Fi1 - 5) // 2 + 1
+x1 = torch.randn(B, Ti1, Fi1, device=dev)
+w1 = torch.randn(20, 5, 1, C, device=dev) * 0.1
+y1 = torch.empty(B, To1, Fo1, C, device=dev)
+dy1 = torch.randn(B, To1, Fo1, C, device=dev)
+sums = torch.empty(64, dtype=torch.float64, device=dev)
+dw1 = torch.empty(20, 5, 1, C, device=dev)
+db1 = torch.empty(C, device=dev)
+mb = B * To1 * Fo1 * C * 4 / 1e6
+for name, fn in (("fwd", lambda: check(lib.ds2_conv1_fused_fwd(p(x1), p(w1), p(bias), p(y1), p(sums), B, Ti1, Fi1, 20, 5, 2, 2, s()), "f")),
+                 ("wgrad", lambda: check(lib.ds2_conv1_fused_wgrad(p(x1), p(dy1), p(dw1), p(db1), B, Ti1, Fi1, 20, 5, 2, 2, s()), "w"))):
+    ms = timeit(fn)
+    print("conv1 %-5s B=%d: %.3f ms  (%.0f MB of y / dy -> %.2f TB/s)" % (name, B, ms, mb, mb / ms / 1e3))
