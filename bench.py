@@ -312,6 +312,7 @@ def main():
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(B * T * 161 * 4), "d2h_bytes_per_step": 4,
                 "ms_per_step": e2e_ms},
         "gpu_launches": int(launches),
+        "dp": ({"all_reduces": reducer.launched, "gradients_copied_after_reduce": reducer.copied} if reducer is not None else None),
         "loss": final_loss,
         "step_tflops": total_flops / (ms_step * 1e-3) / 1e12 / 1.0,
         # whole step against the SUSTAINED bf16 peak (the step is long; the burst figure applies to a kernel timed alone)

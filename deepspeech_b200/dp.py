@@ -8,8 +8,24 @@ from __future__ import annotations
 
 from typing import Iterable, List
 
+import os
+
 import torch
 import torch.distributed as dist
+
+# timing experiments only (gradients stay local, results are wrong): what the step costs without any communication
+_DEBUG_NO_COMM = bool(os.environ.get("DS2_DP_DEBUG_NO_COMM"))
+
+
+class _Done(object):
+    def wait(self):
+        return True
+
+
+def _all_reduce(t, group):
+    if _DEBUG_NO_COMM:
+        return _Done()
+    return dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group, async_op=True)
 
 
 def shard_batch(n_items: int, rank: int, world: int) -> slice:
@@ -41,12 +57,14 @@ class GradAllReducer(object):
         self._seen = 0
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
         self.launched = 0
+        self.copied = 0             # gradients copied out of a reduced buffer (autograd had cloned them)
         # The recurrent stack is one autograd node: its gradients reach the hooks only when the whole stack has been
         # back-propagated.  It offers them layer by layer instead (ops.STACK_GRAD_HOOK); they are all-reduced right
         # there; when autograd later installs its own copy as .grad, finish() overwrites that copy with the reduced
         # tensor.  This relies on .grad being a fresh tensor of this backward pass, i.e. on gradients having been reset
         # with zero_grad(set_to_none=True): accumulating into an older .grad would add the not-yet-reduced values.
         self._early = {}            # id(parameter) -> (work handle, reduced tensor)
+        self._taken = set()         # ids of parameters whose .grad this reducer installed itself (autograd still runs their hooks)
         self._keep = []             # flat buffers whose views are in flight
         self.prescaled = prescaled
         if self.world > 1:
@@ -65,16 +83,22 @@ class GradAllReducer(object):
             if p.grad is not None:
                 raise RuntimeError("GradAllReducer: reset gradients with zero_grad(set_to_none=True) before backward")
         if flat is not None and sum(t.numel() for t, _ in live) == flat.numel():
-            w = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            # The views of the flat buffer become the parameters' .grad right here and the stack's backward returns no
+            # gradient for them (return value True): autograd neither clones nor accumulates, the in-place all-reduce
+            # lands in .grad, finish() only waits.
+            w = _all_reduce(flat, self.group)
             for t, p in live:
-                self._early[id(p)] = (w, t)
+                p.grad = t
+                self._taken.add(id(p))
+            self._pending.append((w, None, [p for _, p in live]))
             self._keep.append(flat)
             self.launched += 1
-            return
+            return True
         for t, p in live:
-            w = dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
-            self._early[id(p)] = (w, t)
+            w = _all_reduce(t, self.group)
+            self._early[id(p)] = (w, t, 0, t.numel())
             self.launched += 1
+        return False
 
     @property
     def loss_scale(self) -> float:
@@ -86,11 +110,11 @@ class GradAllReducer(object):
             return
         ps, self._bucket, self._bucket_size = self._bucket, [], 0
         if len(ps) == 1:
-            w = dist.all_reduce(ps[0].grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            w = _all_reduce(ps[0].grad, self.group)
             self._pending.append((w, None, ps))
         else:
             flat = torch.cat([p.grad.reshape(-1) for p in ps])
-            w = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            w = _all_reduce(flat, self.group)
             self._pending.append((w, flat, ps))
         self.launched += 1
 
@@ -98,9 +122,12 @@ class GradAllReducer(object):
         if self.world == 1:
             return
         self._seen += 1
+        if id(p) in self._taken:                # installed and reduced from inside the stack's backward
+            self._taken.discard(id(p))
+            return
         e = self._early.pop(id(p), None)
         if e is not None:                       # already on its way (offered by the recurrent stack's backward)
-            self._pending.append((e[0], e[1], [p]))
+            self._pending.append((e[0], e[1][e[2]:e[2] + e[3]], [p]))
             return
         nbytes = p.grad.numel() * p.grad.element_size()
         if nbytes >= self.bucket_bytes:
@@ -128,14 +155,16 @@ class GradAllReducer(object):
                 off = 0
                 for p in ps:
                     n = p.grad.numel()
-                    if p.grad.data_ptr() != flat.data_ptr() or n != flat.numel():
+                    if p.grad.data_ptr() != flat.data_ptr() + off * flat.element_size():
                         p.grad.copy_(flat[off:off + n].view_as(p.grad))
+                        self.copied += 1
                     off += n
             if not self.prescaled:
                 for p in ps:
                     _scale_(p.grad, inv)
         self._pending = []
         self._keep = []
+        self._taken = set()
         self._seen = 0
 
     def remove(self):

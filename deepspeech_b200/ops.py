@@ -880,9 +880,11 @@ class _RecStackFn(torch.autograd.Function):
                 outs = [dW, dU, db]
                 if gru:
                     outs.append(dbu)
+                taken = False
                 if STACK_GRAD_HOOK is not None:
-                    # on the stream that produced them: the reducer orders itself after it
-                    STACK_GRAD_HOOK(l, outs, ctx.param_objs[l * npl:(l + 1) * npl], flat)
+                    # on the stream that produced them: the reducer orders itself after it.  True: the hook has installed
+                    # them as the parameters' .grad itself, autograd gets None for them
+                    taken = bool(STACK_GRAD_HOOK(l, outs, ctx.param_objs[l * npl:(l + 1) * npl], flat))
                 if STACK_TRACE is not None:
                     ev3 = torch.cuda.Event(enable_timing=True)
                     ev3.record()
@@ -893,7 +895,7 @@ class _RecStackFn(torch.autograd.Function):
                 side_done[l].record(side)
                 for t in outs:
                     t.record_stream(main)
-            grads[l * npl:l * npl + npl] = outs
+            grads[l * npl:l * npl + npl] = [None] * len(outs) if taken else outs
         if overlap:
             main.wait_stream(side)
             main.wait_stream(rec)
