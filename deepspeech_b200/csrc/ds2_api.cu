@@ -72,6 +72,10 @@ void reload_env() {
   e.rnn_slab_f32 = env_flag("DS2_RNN_SLAB_F32");
   e.rnn_prof = env_flag("DS2_RNN_PROF");
   e.rnn_v1 = env_flag("DS2_RNN_V1");
+  {
+    const char* m = getenv("DS2_RNN_POLL_MARGIN");
+    e.rnn_poll_margin = m ? atoi(m) : 800;
+  }
   e.gru_no_bulk = env_flag("DS2_GRU_NO_BULK");
   e.gemm_no_pair = env_flag("DS2_GEMM_NO_PAIR");
   e.ctc_ns = env_int("DS2_CTC_NS", 0);

@@ -64,6 +64,7 @@ struct Params {
   float scale, cap;
   int exp;                 // DS2_RNN_EXP bit 0: the image check reports 'stale' once on every 5th step (exercises the re-fetch path)
   int slab16;              // partial sums cross the cluster as bf16 (default) or fp32
+  int poll_margin;         // clk before the predicted completion of a step at which its counter is first read (0: from the start)
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -258,6 +259,8 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
       unsigned int round = 0;                    // fetches issued so far = id of the last one (0: none yet)
       const unsigned int* poll = ctr;            // the counter copy this thread polls
       long long best_rt = 0x7fffffffffffffffll;
+      long long seen1 = 0, seen2 = 0;              // when the counter was seen complete in the last two steps
+      long long pmin = 1ll << 40;                  // shortest step period so far
       long long wait_sum = 0, fetch_sum = 0;       // DS2_RNN_PROF: per-CTA totals (waiting for the others / fetch + MMA issue)
       // fetch the operand image at `src`, issue the step's MMAs, hand the accumulators over
       auto fetch_and_issue = [&]() {
@@ -282,6 +285,16 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
           const long long t0 = dev_clock();
           int npoll = 1;
           SpinGuard g;
+          if (p.poll_margin > 0 && step > 2 * NCOPY + 2) {
+            // No polling while the step cannot be complete yet: 2 x 112 threads reading the counter lines back to back
+            // slow down the increments that everybody is waiting for (measured: -4..5 % per step).  Polling starts
+            // poll_margin clk before the moment the last period predicts - the estimate capped at 1.1 x the shortest
+            // period seen, so that a late start (which lengthens that period) cannot feed back into later estimates.
+            long long pe = seen1 - seen2;
+            if (pe > pmin + pmin / 10) pe = pmin + pmin / 10;
+            const long long start = seen1 + pe - (long long)p.poll_margin;
+            while (dev_clock() < start) {}
+          }
           while (ld_relaxed_gpu_u32(q) < need) {
             ++npoll;
             if (round > 0 && lds_u32(flag_a + 4 * (round & 1)) == round) {
@@ -294,6 +307,9 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
             }
             g.check(20);
           }
+          seen2 = seen1;
+          seen1 = dev_clock();
+          if (step > 2 * NCOPY + 1 && seen1 - seen2 < pmin) pmin = seen1 - seen2;   // a late start can lengthen a period, never shorten it
           if (calib) {
             const long long rt = (dev_clock() - t0) / npoll;
             if (rt < best_rt) { best_rt = rt; poll = q; }
@@ -636,6 +652,7 @@ static int common_setup(Params& p, Geom& g, int T, int B, int H, int ND, void* w
   p.ctr = reinterpret_cast<unsigned int*>((reinterpret_cast<uintptr_t>(p.ring) + g.ring_bytes + 4095) & ~uintptr_t(4095));
   p.exp = env().rnn_exp;
   p.slab16 = env().rnn_slab_f32 ? 0 : 1;
+  p.poll_margin = env().rnn_poll_margin;
   p.prof = env().rnn_prof ? reinterpret_cast<long long*>(static_cast<char*>(ws) + WS_CTR_BYTES) : nullptr;
   const long n_units = (long)(g.ring_bytes / 16);
   int blocks = (int)((n_units + 255) / 256);
