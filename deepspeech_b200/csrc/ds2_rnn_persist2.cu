@@ -487,15 +487,15 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
           pk.x = scrub_fill2(pk.x);       // a NaN gradient must not look like the sentinel
           pk.y = scrub_fill2(pk.y);
         }
-        // the exchange ring first (the other CTAs wait for it) and the slot two steps ahead back to the sentinel
+        // the exchange ring first: the other CTAs wait for it
         st_relaxed_b64(ring_cell + (size_t)(step % RING) * slot_stride, pk.x, pk.y);
-        st_relaxed_b64(ring_cell + (size_t)((step + 2) % RING) * slot_stride, 0xFFFFFFFFu, 0xFFFFFFFFu);
       }
       // publish: one relaxed increment per counter copy after the warp's stores (no fence: the image validates itself)
       __syncwarp();
       if (lane < NCOPY) red_relaxed_gpu_add(ctr + lane * CTR_COPY_STRIDE, 1u);
-      // the caller's tensors afterwards: nobody inside the kernel waits for them
+      // afterwards what nobody inside the kernel waits for: the slot two steps ahead back to the sentinel, the caller's tensors
       if (jvalid) {
+        st_relaxed_b64(ring_cell + (size_t)((step + 2) % RING) * slot_stride, 0xFFFFFFFFu, 0xFFFFFFFFu);
         *reinterpret_cast<uint2*>(out_ptr) = pk;
         if (!BWD && out32_ptr) {
           *reinterpret_cast<float4*>(out32_ptr) = make_float4(o[0], o[1], o[2], o[3]);
