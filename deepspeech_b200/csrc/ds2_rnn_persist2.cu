@@ -141,7 +141,7 @@ __host__ __device__ inline int image_offset(int n, int k) {
 struct Smem {
   uint32_t a_off, b_off, slab_off, bar_off, flag_off, total;
 };
-static constexpr int BARS_PER_INST = 4;   // copy (tx), ok (4 warps), mma (commit), slab (tx)
+static constexpr int BARS_PER_INST = 5;   // copy (tx), ok (4 warps), mma (commit), slab (tx), second half of the copy (tx)
 __host__ __device__ inline Smem smem_layout(int nbox, int NI) {
   Smem s;
   s.a_off = 0;                                            // nbox x [128 x 64] bf16 staging of the U slice
@@ -154,6 +154,17 @@ __host__ __device__ inline Smem smem_layout(int nbox, int NI) {
 }
 
 // all MMAs of one step: D[128 x 16] (+)= U_slice[128 x ksl] (TMEM) . h_slice^T (operand image in shared memory)
+// boxes [B0, B1) of the image, unrolled (the image is fetched in two halves: the first half's MMAs issue while the second lands)
+template <int B0, int B1>
+__device__ __forceinline__ void issue_box_mmas(uint32_t d_tmem, uint32_t tmem_base, uint32_t sB_addr, uint32_t idesc) {
+#pragma unroll
+  for (int i = B0; i < B1; ++i) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      umma_bf16_ts(d_tmem, tmem_base + (i * 4 + k) * 8, umma_smem_desc_sw128(sB_addr + i * BOX_BYTES + k * 32, 16, 1024), idesc,
+                   (i > 0 || k > 0) ? 1u : 0u);
+  }
+}
 template <int NBOX>
 __device__ __forceinline__ void issue_step_mmas(uint32_t d_tmem, uint32_t tmem_base, uint32_t sB_addr, uint32_t idesc, int nbox_rt) {
   if (NBOX > 0) {
@@ -195,6 +206,7 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
   const uint32_t ok_bar_a = copy_bar_a + 8;                                          // the 4 epilogue warps have checked it
   const uint32_t mma_bar_a = copy_bar_a + 16;                                        // accumulators ready
   const uint32_t slab_bar_a = copy_bar_a + 24;                                       // partial slabs of this step arrived
+  const uint32_t copy2_bar_a = copy_bar_a + 32;                                      // second half of the operand image landed
   const uint32_t flag_a = keep_reg(smem_u32(smem + L.flag_off + 16 + inst * 8));     // [id & 1] = id of a fetch found stale
   const uint32_t sB_addr = keep_reg(smem_u32(smem + L.b_off + inst * nbox * BOX_BYTES));
   const uint32_t slab_local = keep_reg(smem_u32(smem + L.slab_off + inst * KS * 32 * BP * 4));
@@ -222,6 +234,7 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
       mbar_init(bb + 1, 4);        // one arrive per epilogue warp
       mbar_init(bb + 2, 1);        // tcgen05.commit
       mbar_init(bb + 3, 1);        // arrive.expect_tx per use + the st.async bytes
+      mbar_init(bb + 4, 1);        // second half of the image
       uint32_t* fl = reinterpret_cast<uint32_t*>(smem + L.flag_off + 16 + i * 8);
       fl[0] = 0u;
       fl[1] = 0u;
@@ -264,12 +277,28 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
       long long wait_sum = 0, fetch_sum = 0;       // DS2_RNN_PROF: per-CTA totals (waiting for the others / fetch + MMA issue)
       // fetch the operand image at `src`, issue the step's MMAs, hand the accumulators over
       auto fetch_and_issue = [&]() {
-        mbar_arrive_expect_tx(copy_bar_a, img_bytes);
-        bulk_g2s(sB_addr, src, img_bytes, copy_bar_a);
-        mbar_wait(copy_bar_a, phc, 30);
-        phc ^= 1;
-        tc_fence_after();
-        issue_step_mmas<NBOX>(d_tmem, tmem_base, sB_addr, idesc, nbox);
+        if (NBOX > 1) {
+          // two halves on two barriers: the MMAs of the first boxes are issued while the rest of the image lands
+          constexpr int H0 = NBOX > 1 ? (NBOX + 1) / 2 : 1, NB = NBOX > 1 ? NBOX : 2;
+          mbar_arrive_expect_tx(copy_bar_a, H0 * BOX_BYTES);
+          bulk_g2s(sB_addr, src, H0 * BOX_BYTES, copy_bar_a);
+          mbar_arrive_expect_tx(copy2_bar_a, (NB - H0) * BOX_BYTES);
+          bulk_g2s(sB_addr + H0 * BOX_BYTES, src + H0 * BOX_BYTES, (NB - H0) * BOX_BYTES, copy2_bar_a);
+          mbar_wait(copy_bar_a, phc, 30);
+          tc_fence_after();
+          issue_box_mmas<0, H0>(d_tmem, tmem_base, sB_addr, idesc);
+          mbar_wait(copy2_bar_a, phc, 30);
+          tc_fence_after();
+          issue_box_mmas<H0, NB>(d_tmem, tmem_base, sB_addr, idesc);
+          phc ^= 1;
+        } else {
+          mbar_arrive_expect_tx(copy_bar_a, img_bytes);
+          bulk_g2s(sB_addr, src, img_bytes, copy_bar_a);
+          mbar_wait(copy_bar_a, phc, 30);
+          phc ^= 1;
+          tc_fence_after();
+          issue_step_mmas<NBOX>(d_tmem, tmem_base, sB_addr, idesc, nbox);
+        }
         umma_commit(mma_bar_a);
         ++round;
       };
@@ -389,6 +418,7 @@ rnn2_kernel(const __grid_constant__ CUtensorMap tm_a, Params p) {
         bool force_stale = (p.exp & 1) && step % 5 == 0;
         for (;;) {
           mbar_wait(copy_bar_a, phc, 40);
+          if (NBOX > 1) mbar_wait(copy2_bar_a, phc, 43);
           phc ^= 1;
           ++vround;
           if (pr) p.prof[step * 16 + 13] = dev_clock();
