@@ -319,7 +319,7 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
       if (step > 0) {
         if (et == 0) mbar_arrive_expect_tx(slab_bar_a, p.slab16 ? 128 * NG * GBP * 2 : 128 * NG * GBP * 4);
         if (et == 0) {
-          const unsigned int need = ctas_per_dir * (unsigned int)step;
+          const unsigned int need = (p.fenced ? 1u : 4u) * ctas_per_dir * (unsigned int)step;   // unfenced: every epilogue warp publishes
           if (p.fenced) {
             if (g_ld_acquire_u32(ctr) < need) {
               SpinGuard sg;
@@ -445,6 +445,7 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
             }
         ph ^= 1;
       }
+      uint2 late[4];
       if (jvalid) {
         const bool live = t < len_b;
         // h of the previous step in forward order (zero before the first step)
@@ -471,11 +472,8 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
           const uint2 hpk = g_pack4(ho);
           g_unpack4(hpk, carry);
           *reinterpret_cast<uint2*>(p.hs + (((size_t)d * T + t) * Bn + b) * H + j) = hpk;
-          __nv_bfloat16* gp = p.gates + (((size_t)d * T + t) * Bn + b) * 4 * H + j;
-          *reinterpret_cast<uint2*>(gp) = g_pack4(ro);
-          *reinterpret_cast<uint2*>(gp + (size_t)H) = g_pack4(zo);
-          *reinterpret_cast<uint2*>(gp + (size_t)2 * H) = g_pack4(no);
-          *reinterpret_cast<uint2*>(gp + (size_t)3 * H) = g_pack4(go);
+          // (r, z, n, U_n h + b) are only read by the backward pass: stored after the publication
+          late[0] = g_pack4(ro); late[1] = g_pack4(zo); late[2] = g_pack4(no); late[3] = g_pack4(go);
         } else {
           float r4[4], z4[4], n4[4], gh4[4];
           g_unpack4(g4[0], r4); g_unpack4(g4[1], z4); g_unpack4(g4[2], n4); g_unpack4(g4[3], gh4);
@@ -493,19 +491,36 @@ gru_persist_kernel(const __grid_constant__ CUtensorMap tm_a, GruParams p) {
           }
           __nv_bfloat16* gip = p.dgi + ((size_t)t * Bn + b) * ND * 3 * H + (size_t)d * 3 * H + j;
           __nv_bfloat16* ghp = p.dgh + ((size_t)t * Bn + b) * ND * 3 * H + (size_t)d * 3 * H + j;
-          *reinterpret_cast<uint2*>(gip) = g_pack4(dr);
-          *reinterpret_cast<uint2*>(gip + (size_t)H) = g_pack4(dz);
-          *reinterpret_cast<uint2*>(gip + (size_t)2 * H) = g_pack4(dn);
-          *reinterpret_cast<uint2*>(ghp) = g_pack4(dr);
-          *reinterpret_cast<uint2*>(ghp + (size_t)H) = g_pack4(dz);
+          // dgh is what the other CTAs wait for; dgi (read by the GEMMs after the kernel) follows the publication
+          late[0] = g_pack4(dr); late[1] = g_pack4(dz); late[2] = g_pack4(dn);
+          *reinterpret_cast<uint2*>(ghp) = late[0];
+          *reinterpret_cast<uint2*>(ghp + (size_t)H) = late[1];
           *reinterpret_cast<uint2*>(ghp + (size_t)2 * H) = g_pack4(dnr);
+          (void)gip;
         }
       }
       if (pr && step < 1024) p.prof[step * 8 + 6] = dev_clock();
-      asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
-      if (et == 0) {
-        if (p.fenced) g_red_release_add(ctr, 1u);
-        else red_relaxed_gpu_add(ctr, 1u);
+      if (p.fenced) {
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + inst) : "memory");
+        if (et == 0) g_red_release_add(ctr, 1u);
+      } else {
+        // no CTA barrier: every warp publishes its own rows (the data validates itself, common.cuh)
+        __syncwarp();
+        if (lane == 0) red_relaxed_gpu_add(ctr, 1u);
+      }
+      if (jvalid) {
+        if (!BWD) {
+          __nv_bfloat16* gp = p.gates + (((size_t)d * T + t) * Bn + b) * 4 * H + j;
+          *reinterpret_cast<uint2*>(gp) = late[0];
+          *reinterpret_cast<uint2*>(gp + (size_t)H) = late[1];
+          *reinterpret_cast<uint2*>(gp + (size_t)2 * H) = late[2];
+          *reinterpret_cast<uint2*>(gp + (size_t)3 * H) = late[3];
+        } else {
+          __nv_bfloat16* gip = p.dgi + ((size_t)t * Bn + b) * ND * 3 * H + (size_t)d * 3 * H + j;
+          *reinterpret_cast<uint2*>(gip) = late[0];
+          *reinterpret_cast<uint2*>(gip + (size_t)H) = late[1];
+          *reinterpret_cast<uint2*>(gip + (size_t)2 * H) = late[2];
+        }
       }
       if (pr && step < 1024) p.prof[step * 8 + 7] = dev_clock();
     }
