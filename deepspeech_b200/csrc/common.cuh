@@ -39,7 +39,7 @@ struct EnvSwitches {
   int rnn_slab_f32;     // DS2_RNN_SLAB_F32: fp32 partial sums across the cluster
   int rnn_prof;         // DS2_RNN_PROF: in-kernel stage stamps
   int rnn_v1;           // DS2_RNN_V1: round-1 exchange protocol of the ReLU recurrence (A/B runs)
-  int rnn_poll_margin;  // DS2_RNN_POLL_MARGIN: clk before a step's predicted completion at which the counter polling starts (default 800, 0: always poll)
+  int rnn_poll_margin;  // DS2_RNN_POLL_MARGIN: clk before a step's predicted completion at which the counter polling starts (default: per batch size, 725-900; 0: always poll)
   int gru_no_bulk;      // DS2_GRU_NO_BULK
   int gemm_no_pair;     // DS2_GEMM_NO_PAIR
   int ctc_ns;           // DS2_CTC_NS

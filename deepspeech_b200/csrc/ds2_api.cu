@@ -74,7 +74,7 @@ void reload_env() {
   e.rnn_v1 = env_flag("DS2_RNN_V1");
   {
     const char* m = getenv("DS2_RNN_POLL_MARGIN");
-    e.rnn_poll_margin = m ? atoi(m) : 800;
+    e.rnn_poll_margin = m ? atoi(m) : -1;       // -1: the kernel's own table
   }
   e.gru_no_bulk = env_flag("DS2_GRU_NO_BULK");
   e.gemm_no_pair = env_flag("DS2_GEMM_NO_PAIR");
