@@ -397,10 +397,10 @@ def extras(args, dev, model, ops, _lib, B, T2, H, L, peak_tf, peak_hbm, peak_src
                            "bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
                            # dram__bytes_read+write of one launch of this kernel, read from the committed ncu --set full
                            # extract of the same shape (profiles/r2_rnn2_ncu.json); null for any other shape / kernel
-                           "traffic": _profiled_traffic(dom_gemm, T2, B, H), "traffic_source": "profiles/r2_rnn2_ncu.json",
+                           "traffic": _profiled_traffic(dom_gemm, T2, B, H), "traffic_source": "profiles/r2_rnn2_ncu.json (extract: r2_rnn2_final_ncu.txt)",
                            "algorithmic_bytes": 4.0 * T2 * B * 2 * H + 2.0 * 2 * H * H + 2.0 * 2 * T2 * B * H,
                            "peak_source": peak_src,
-                           "note": "latency-bound T-step dependency chain (4 chains x %d steps); stage cycles in profiles/r2_rnn_stage_cycles_v2.txt" % T2}
+                           "note": "latency-bound T-step dependency chain (4 chains x %d steps); stage cycles in profiles/r2_rnn_stage_cycles_v3.txt" % T2}
     total_flops, rnn_flops, _ = step_flops(B, args.frames, H, L, 32, args.cell)
     out["rnn_tflops_in_step"] = {"note": "all RNN-stack GEMM FLOPs (fwd+bwd) / whole step time (lower bound)",
                                  "value": rnn_flops / (ms_step * 1e-3) / 1e12,
