@@ -63,7 +63,9 @@ for r in range(world):
     g, _ = grads_of(list(range(s.start, s.stop)), None)
     ref = g if ref is None else [a + b for a, b in zip(ref, g)]
 ref = [a / world for a in ref]
-tol = 2e-2 if use_bf16 else 1e-5          # bf16 path: split-K atomics reorder fp32 sums from run to run
+# bf16 path: split-K atomics reorder fp32 sums from run to run.  fp32 path: fp32 round-off - its weight-gradient and batch-norm
+# reductions are atomic sums too (6e-6 is typical, 1e-5 has been seen once in a full-suite run)
+tol = 2e-2 if use_bf16 else 5e-5
 worst = 0.0
 gmax = max(float(b.abs().max()) for b in ref)
 for (name, _), a, b in zip(m.named_parameters(), g_dp, ref):

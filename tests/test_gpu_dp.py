@@ -1,6 +1,6 @@
 """Data-parallel gradient parity on hardware: 2 NCCL ranks, each with a shard of the batch, against the
 average of the per-shard gradients computed on one GPU - the reference's sketched tower averaging
-(src/deepSpeech_train.py:193-228), batch-norm statistics per tower.  fp32 path to fp32 round-off (1e-5), bf16 tensor-core
+(src/deepSpeech_train.py:193-228), batch-norm statistics per tower.  fp32 path to fp32 round-off (5e-5; 6e-6 typical), bf16 tensor-core
 path to 2e-2 (its split-K reductions are not bit-reproducible).  Skipped on a box with fewer than 2 GPUs."""
 import os
 import socket
