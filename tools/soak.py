@@ -45,6 +45,36 @@ for (T, B, H) in [(366, 32, 1760), (1500, 32, 1760), (366, 64, 800), (200, 16, 3
         n += 1
     print("recurrence T=%d B=%d H=%d: all runs bit-identical (%d launches so far)" % (T, B, H, 2 * n), flush=True)
 
+# the GRU recurrence (per-warp publication since late round 2): same check
+for (T, B, H) in [(366, 32, 800), (366, 64, 800), (200, 32, 1760)]:
+    if not lib.ds2_gru_persistent_supported(B, H, 2):
+        continue
+    wx = torch.randn((T, B, 6 * H), device=dev, generator=g) * 0.5
+    U = (torch.randn((2, 3 * H, H), device=dev, generator=g) * (0.5 / H ** 0.5)).to(torch.bfloat16)
+    bw = torch.randn((2, 3 * H), device=dev, generator=g) * 0.1
+    bu = torch.randn((2, 3 * H), device=dev, generator=g) * 0.1
+    lens = torch.randint(T // 2, T + 1, (B,), device=dev, generator=g, dtype=torch.int32)
+    dout = torch.randn((T, B, H), device=dev, generator=g)
+    wsb = lib.ds2_gru_workspace_bytes(T, B, H, 2)
+    ws = torch.zeros(wsb, dtype=torch.uint8, device=dev)
+    ref, k = None, 0
+    t_shape = time.time() + minutes * 60.0 * 0.25 / 3
+    while time.time() < t_shape:
+        hs = torch.empty((2, T, B, H), dtype=torch.bfloat16, device=dev)
+        gates = torch.empty((2, T, B, 4 * H), dtype=torch.bfloat16, device=dev)
+        dgi = torch.empty((T, B, 6 * H), dtype=torch.bfloat16, device=dev)
+        dgh = torch.empty((T, B, 6 * H), dtype=torch.bfloat16, device=dev)
+        check(lib.ds2_gru_persistent_fwd(p(wx), 1.0, p(U), p(bw), p(bu), p(lens), p(hs), p(gates), T, B, H, 2, 2, p(ws), wsb, st()), "gru fwd")
+        check(lib.ds2_gru_persistent_bwd(p(dout), p(U), p(lens), p(hs), p(gates), p(dgi), p(dgh), None, None, T, B, H, 2, 2, p(ws), wsb, st()), "gru bwd")
+        torch.cuda.synchronize()
+        if ref is None:
+            ref = (hs, gates, dgi, dgh)
+        else:
+            for a_, b_ in zip((hs, gates, dgi, dgh), ref):
+                assert torch.equal(a_, b_), "GRU run %d of T=%d B=%d H=%d differs from the first" % (k, T, B, H)
+        k += 1
+    print("GRU recurrence T=%d B=%d H=%d: %d runs bit-identical" % (T, B, H, k), flush=True)
+
 params = SimpleNamespace(use_fp16=True, num_filters=32, batch_size=32, num_hidden=1760, num_rnn_layers=7, engine="mkl",
                          rnn_type="bi-dir", wiring="stacked", seed=1234)
 m = ds.model(params)
